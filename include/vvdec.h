@@ -1,0 +1,153 @@
+/*
+ * vvdec.h — C ABI of the B200-native VibeVoice acoustic-tokenizer decoder (libvvdec_b200.so).
+ *
+ * Drop-in boundary for ONE path of beecave-homelab/VibeVoice-ROCm:
+ *   VibeVoiceAcousticTokenizerModel.decode(latents, cache, sample_indices, use_cache, debug)
+ *     reference: vibevoice/modular/modular_vibevoice_tokenizer.py:1099-1108
+ *   called by the generation loop at vibevoice/modular/modeling_vibevoice_inference.py:635-641.
+ *
+ * The reference is pure Python/PyTorch and has no FFI of its own; this header is the interface a
+ * maintainer binds with ctypes (see INTEGRATION.md, and vibevoice-rocm_b200/vvdec/_capi.py which is
+ * exactly that binding).  Plain C types only: device pointers, sizes, a cudaStream_t passed as
+ * void*.  No C++ exceptions cross the boundary; every entry point returns a vv_status.
+ *
+ * All device pointers must live on the device the decoder was created on.  Calls enqueue work on
+ * the given stream and never synchronise it (except vv_decoder_finalize and vv_state_export/import,
+ * which are set-up / checkpoint operations).
+ */
+#ifndef VVDEC_H_
+#define VVDEC_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define VVDEC_ABI_VERSION 1
+#define VV_MAX_STAGES 8
+
+typedef enum vv_status {
+  VV_OK = 0,
+  VV_ERR_INVALID_ARG = -1,    /* null pointer, negative size, bad enum                         */
+  VV_ERR_BAD_SHAPE = -2,      /* tensor shape does not match the geometry                       */
+  VV_ERR_BAD_DTYPE = -3,
+  VV_ERR_UNSUPPORTED = -4,    /* geometry / config variant outside the path (see vv_config)     */
+  VV_ERR_NOT_FINALIZED = -5,  /* decode before vv_decoder_finalize, or a weight is missing      */
+  VV_ERR_WORKSPACE = -6,      /* workspace too small                                            */
+  VV_ERR_SLOT = -7,           /* stream slot out of range                                       */
+  VV_ERR_CUDA = -8,           /* a CUDA call failed; see vv_last_error()                        */
+  VV_ERR_NO_DEVICE = -9,      /* no CUDA device / not an sm_100 device                          */
+  VV_ERR_UNKNOWN_TENSOR = -10 /* vv_decoder_load_tensor: name is not a decoder parameter        */
+} vv_status;
+
+typedef enum vv_dtype { VV_F32 = 0, VV_BF16 = 1 } vv_dtype;
+
+/* latents layout, mirroring the reference's shape sniffing at :1102-1105 */
+typedef enum vv_layout {
+  VV_LAYOUT_BTD = 0,          /* [B, T, vae_dim]  (what generate() passes, :634-641)            */
+  VV_LAYOUT_BDT = 1           /* [B, vae_dim, T]                                                */
+} vv_layout;
+
+/*
+ * Geometry = the fields of VibeVoiceAcousticTokenizerConfig that fix shapes on the decode path
+ * (vibevoice/modular/configuration_vibevoice.py:16-44; parsed at modular_vibevoice_tokenizer.py:
+ * 1011-1058).  Variants the path does not implement are rejected with VV_ERR_UNSUPPORTED by the
+ * host wrapper before this struct is built: non-causal, LayerNorm, mixer_layer != depthwise_conv,
+ * weight/spectral norm, non-constant padding.
+ */
+typedef struct vv_config {
+  int32_t vae_dim;                    /* 64                                                     */
+  int32_t n_filters;                  /* decoder_n_filters, 32                                  */
+  int32_t n_stages;                   /* len(depths) = len(ratios) + 1, 7                       */
+  int32_t ratios[VV_MAX_STAGES];      /* decoder_ratios, [8,5,5,4,2,2]                          */
+  int32_t depths[VV_MAX_STAGES];      /* decoder order (already reversed, :1028): [8,3,3,3,3,3,3] */
+  int32_t kernel_size;                /* 7 (depthwise mixer, stem, head)                        */
+  float   eps;                        /* layernorm_eps 1e-5                                     */
+  int32_t device;                     /* CUDA device ordinal                                    */
+  int32_t gemm_path;                  /* 0 = auto (tcgen05 where the shape allows), 1 = force the
+                                         CUDA-core GEMM everywhere (validation / debugging)     */
+} vv_config;
+
+typedef struct vv_decoder vv_decoder; /* opaque: packed weights + launch plan                    */
+typedef struct vv_state vv_state;     /* opaque: device-resident per-stream conv state            */
+
+/* ---- library ------------------------------------------------------------------------------- */
+int32_t     vv_abi_version(void);
+const char* vv_status_string(int32_t status);
+/* Last CUDA / validation message recorded on this thread ("" if none). */
+const char* vv_last_error(void);
+
+/* ---- decoder life cycle (replaces TokenizerDecoder.__init__, :823-912, + from_pretrained) -- */
+int32_t vv_decoder_create(const vv_config* cfg, vv_decoder** out);
+int32_t vv_decoder_destroy(vv_decoder* dec);
+
+/*
+ * Hand one reference state-dict tensor to the decoder.  `name` is the key under the tokenizer model
+ * ("decoder.upsample_layers.0.0.conv.conv.weight", "decoder.stages.3.1.ffn.linear1.bias", ... —
+ * SURVEY.md Appendix B).  `data` may be a host or a device pointer (is_device says which); it is
+ * copied, the caller keeps ownership.  shape is the PyTorch shape.
+ */
+int32_t vv_decoder_load_tensor(vv_decoder* dec, const char* name, const void* data, int32_t dtype,
+                               const int64_t* shape, int32_t ndim, int32_t is_device);
+/* Pack weights into kernel-native layouts (bf16 K-major GEMM operands, polyphase-split transposed
+ * convs).  Fails with VV_ERR_NOT_FINALIZED and names the first missing tensor in vv_last_error(). */
+int32_t vv_decoder_finalize(vv_decoder* dec);
+int64_t vv_decoder_param_count(const vv_decoder* dec);
+/* samples produced per latent frame (prod(ratios) = 3200) and causal receptive field in frames (58) */
+int32_t vv_decoder_hop(const vv_decoder* dec);
+int32_t vv_decoder_halo_frames(const vv_decoder* dec);
+
+/* ---- decode (replaces VibeVoiceAcousticTokenizerModel.decode, :1099-1108) ------------------- */
+/* Scratch bytes vv_decode needs for a [B, T] call (activations ping-pong + GEMM operand staging). */
+int64_t vv_decoder_workspace_bytes(const vv_decoder* dec, int32_t B, int32_t T);
+
+/*
+ * latents : device, [B,T,vae_dim] or [B,vae_dim,T] per `layout`, dtype lat_dtype.
+ * audio   : device, [B, 1, T*hop] contiguous, dtype out_dtype.
+ * state   : NULL for offline decode (use_cache=False / cache=None, :317,:469).  Otherwise the
+ *           per-stream conv state; slot_ids (device int32 [B], one distinct slot per row — the
+ *           reference's sample_indices, :322-323) selects each row's stream.  State is read as the
+ *           causal left context and updated in place (SConv1d._forward_streaming :327-382,
+ *           SConvTranspose1d._forward_streaming :478-549); a zeroed slot reproduces the reference's
+ *           "first chunk" zeros context (:337-346, :488-492).
+ * Any T >= 1 is accepted in both modes.
+ */
+int32_t vv_decode(vv_decoder* dec, const void* latents, int32_t lat_dtype, int32_t layout,
+                  int32_t B, int32_t T, void* audio, int32_t out_dtype,
+                  void* workspace, int64_t workspace_bytes,
+                  vv_state* state, const int32_t* slot_ids, void* cuda_stream);
+
+/* Number of kernels vv_decode enqueued since the counter was last read (bench.py's gpu_launches). */
+int64_t vv_decoder_take_launch_count(vv_decoder* dec);
+
+/* ---- streaming state (replaces VibeVoiceTokenizerStreamingCache, :193-256) ------------------ */
+int32_t vv_state_create(const vv_decoder* dec, int32_t n_slots, vv_state** out);   /* zero-filled */
+int32_t vv_state_destroy(vv_state* st);
+int32_t vv_state_n_slots(const vv_state* st);
+int64_t vv_state_bytes_per_slot(const vv_state* st);
+/* set_to_zero(sample_indices) (:234-241): slot_ids is a device int32 [n] array; n<0 zeroes all. */
+int32_t vv_state_zero(vv_state* st, const int32_t* slot_ids, int32_t n, void* cuda_stream);
+/* checkpoint one slot to / from host memory (vv_state_bytes_per_slot bytes); synchronises. */
+int32_t vv_state_export(const vv_state* st, int32_t slot, void* host_dst, int64_t bytes);
+int32_t vv_state_import(vv_state* st, int32_t slot, const void* host_src, int64_t bytes);
+
+/* ---- per-kernel entry points (tests and bench.py's roofline leg time these in isolation) ---- */
+/* Fused Block1D mixer half on a channels-last fp32 activation [B, T, C]:
+ *   y = x + gamma * (dwconv7(RMSNorm(x) * norm_w) + bias);  a = bf16|f32( RMSNorm(y) * ffn_norm_w )
+ * (modular_vibevoice_tokenizer.py:927-932, :936).  stage/block pick the packed weights. */
+int32_t vv_kernel_mixer(vv_decoder* dec, int32_t stage, int32_t block, const float* x, float* y,
+                        void* a_out, int32_t B, int32_t T, void* cuda_stream);
+/* Fused Block1D FFN half: y = x + ffn_gamma * (W2 gelu(W1 a + b1) + b2)  (:937-942).
+ * hidden is scratch of B*T*4C elements (bf16 on the tcgen05 path, f32 on the CUDA-core path). */
+int32_t vv_kernel_ffn(vv_decoder* dec, int32_t stage, int32_t block, const void* a, const float* x,
+                      float* y, void* hidden, int32_t B, int32_t T, void* cuda_stream);
+/* Polyphase transposed conv into stage `stage` (1..n_stages-1): [B,T,Cin] -> [B,T*r,Cout] (:875-878). */
+int32_t vv_kernel_upsample(vv_decoder* dec, int32_t stage, const float* x, float* y, void* a_stage,
+                           int32_t B, int32_t T, void* cuda_stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VVDEC_H_ */
