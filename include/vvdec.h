@@ -133,19 +133,24 @@ int32_t vv_state_zero(vv_state* st, const int32_t* slot_ids, int32_t n, void* cu
 int32_t vv_state_export(const vv_state* st, int32_t slot, void* host_dst, int64_t bytes);
 int32_t vv_state_import(vv_state* st, int32_t slot, const void* host_src, int64_t bytes);
 
-/* ---- per-kernel entry points (tests and bench.py's roofline leg time these in isolation) ---- */
-/* Fused Block1D mixer half on a channels-last fp32 activation [B, T, C]:
- *   y = x + gamma * (dwconv7(RMSNorm(x) * norm_w) + bias);  a = bf16|f32( RMSNorm(y) * ffn_norm_w )
+/* ---- per-kernel entry points (offline form; tests and bench.py's roofline leg time these alone) -- */
+/* Fused Block1D mixer half on a channels-last fp32 activation x [B, rows, C]:
+ *   y = x + gamma * (dwconv7(RMSNorm(x) * norm_w) + bias);   a = bf16( RMSNorm(y) * ffn_norm_w )
  * (modular_vibevoice_tokenizer.py:927-932, :936).  stage/block pick the packed weights. */
 int32_t vv_kernel_mixer(vv_decoder* dec, int32_t stage, int32_t block, const float* x, float* y,
-                        void* a_out, int32_t B, int32_t T, void* cuda_stream);
-/* Fused Block1D FFN half: y = x + ffn_gamma * (W2 gelu(W1 a + b1) + b2)  (:937-942).
- * hidden is scratch of B*T*4C elements (bf16 on the tcgen05 path, f32 on the CUDA-core path). */
-int32_t vv_kernel_ffn(vv_decoder* dec, int32_t stage, int32_t block, const void* a, const float* x,
-                      float* y, void* hidden, int32_t B, int32_t T, void* cuda_stream);
-/* Polyphase transposed conv into stage `stage` (1..n_stages-1): [B,T,Cin] -> [B,T*r,Cout] (:875-878). */
-int32_t vv_kernel_upsample(vv_decoder* dec, int32_t stage, const float* x, float* y, void* a_stage,
-                           int32_t B, int32_t T, void* cuda_stream);
+                        void* a_out, int32_t B, int32_t rows, void* cuda_stream);
+/* Fused Block1D FFN half: out = resid + ffn_gamma * (W2 gelu(W1 a + b1) + b2)  (:937-942).
+ * a: bf16 [B*rows, C]; hidden: bf16 scratch [B*rows, 4C]; resid/out: fp32 [B*rows, C] (may alias). */
+int32_t vv_kernel_ffn(vv_decoder* dec, int32_t stage, int32_t block, const void* a, const float* resid,
+                      float* out, void* hidden, int32_t B, int32_t rows, void* cuda_stream);
+/* Polyphase transposed conv INTO stage `stage` (1..n_stages-1), (:875-878 + trim :563-571):
+ * xb: bf16 [B, rows+1, Cin], rows 1..rows = input, row 0 = causal context (zeroed by this call);
+ * y: fp32 [B, rows*ratio, Cout]. */
+int32_t vv_kernel_upsample(vv_decoder* dec, int32_t stage, void* xb, float* y, int32_t B, int32_t rows,
+                           void* cuda_stream);
+/* Head SConv1d(C_last -> 1, k7) (:912, :950): x fp32 [B, rows, C_last] -> out [B, rows] (f32 | bf16). */
+int32_t vv_kernel_head(vv_decoder* dec, const float* x, void* out, int32_t out_dtype, int32_t B,
+                       int32_t rows, void* cuda_stream);
 
 #ifdef __cplusplus
 }

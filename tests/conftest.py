@@ -48,3 +48,17 @@ def weight_cache():
             cache[key] = make_weights(geom, init, seed)
         return cache[key]
     return get
+
+
+@pytest.fixture(scope="session")
+def full_decoder(weight_cache):
+    """(B200AcousticDecoder with the golden fixtures' stress weights, the weight dict).  GPU only."""
+    import torch
+    if not torch.cuda.is_available():
+        pytest.skip("needs a CUDA device")
+    import vvdec
+    from oracle.geometry import FULL
+    w = weight_cache(FULL, "stress", 1234)
+    dec = vvdec.B200AcousticDecoder(vvdec.Geometry(), device=0)
+    dec.load_state_dict({k: torch.from_numpy(v) for k, v in w.items()})
+    return dec, w

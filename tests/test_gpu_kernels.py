@@ -1,0 +1,110 @@
+"""Per-kernel parity: each CUDA kernel class, called alone through the C ABI, against the numpy oracle
+of the same reference op on the same seeded inputs (GPU box only)."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from oracle.geometry import FULL
+from oracle import vv_oracle as O
+from oracle.weights import round_to_bf16
+
+pytestmark = pytest.mark.gpu
+torch = pytest.importorskip("torch")
+
+
+def _rng(seed):
+    return np.random.Generator(np.random.Philox(key=[np.uint64(99), np.uint64(seed)]))
+
+
+def _ptr(t):
+    return C.c_void_p(t.data_ptr())
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _check(dec_pair, rc, what):
+    from vvdec import _capi
+    _capi.check(rc, what)
+
+
+@pytest.mark.parametrize("stage,B,rows", [(6, 2, 300), (5, 1, 129), (4, 3, 50), (3, 2, 40), (2, 1, 33), (1, 2, 9),
+                                          (0, 3, 5), (6, 1, 1), (6, 2, 6), (4, 1, 7)])
+def test_mixer_half(full_decoder, stage, B, rows):
+    dec, w = full_decoder
+    Cc = FULL.stage_channels(stage)
+    x = (_rng(stage * 100 + rows).standard_normal((B, rows, Cc)).astype(np.float32) * 1.7)
+    p = f"decoder.stages.{stage}.0."
+    xc = x.transpose(0, 2, 1)
+    h = O.rms_norm_channels(xc, w[p + "norm.weight"], FULL.eps)
+    h, _ = O.sconv1d(h, w[p + "mixer.conv.conv.conv.weight"], w[p + "mixer.conv.conv.conv.bias"], groups=Cc)
+    y_ref = xc + h * w[p + "gamma"][None, :, None]
+    a_ref = O.rms_norm_channels(y_ref, w[p + "ffn_norm.weight"], FULL.eps)
+    xt = torch.from_numpy(x).cuda()
+    y = torch.empty_like(xt)
+    a = torch.empty((B, rows, Cc), dtype=torch.bfloat16, device="cuda")
+    rc = dec._lib.vv_kernel_mixer(dec._h, stage, 0, _ptr(xt), _ptr(y), _ptr(a), B, rows, _stream())
+    _check(dec, rc, "vv_kernel_mixer")
+    torch.cuda.synchronize()
+    my = O.parity_metrics(y.cpu().numpy().transpose(0, 2, 1), y_ref)
+    ma = O.parity_metrics(a.float().cpu().numpy().transpose(0, 2, 1), a_ref)
+    assert my["rel_max"] < 1e-5, my                      # fp32 in, fp32 out: summation order only
+    assert ma["rel_max"] < 8e-3 and ma["snr_db"] > 50, ma   # one bf16 rounding (2^-9 relative)
+
+
+@pytest.mark.parametrize("stage,B,rows", [(6, 2, 300), (5, 1, 129), (4, 2, 200), (3, 1, 130), (2, 1, 70), (1, 1, 20),
+                                          (0, 1, 7), (6, 1, 1)])
+def test_ffn_half(full_decoder, stage, B, rows):
+    dec, w = full_decoder
+    Cc = FULL.stage_channels(stage)
+    g = _rng(7000 + stage * 10 + rows)
+    a = round_to_bf16(g.standard_normal((B * rows, Cc)).astype(np.float32))
+    resid = g.standard_normal((B * rows, Cc)).astype(np.float32)
+    p = f"decoder.stages.{stage}.0."
+    f = O.ffn(a[None], w[p + "ffn.linear1.weight"], w[p + "ffn.linear1.bias"], w[p + "ffn.linear2.weight"],
+              w[p + "ffn.linear2.bias"])[0]
+    ref = resid + f * w[p + "ffn_gamma"][None, :]
+    at = torch.from_numpy(a).cuda().to(torch.bfloat16)
+    rt = torch.from_numpy(resid).cuda()
+    out = torch.empty_like(rt)
+    hid = torch.empty((B * rows, 4 * Cc), dtype=torch.bfloat16, device="cuda")
+    rc = dec._lib.vv_kernel_ffn(dec._h, stage, 0, _ptr(at), _ptr(rt), _ptr(out), _ptr(hid), B, rows, _stream())
+    _check(dec, rc, "vv_kernel_ffn")
+    torch.cuda.synchronize()
+    m = O.parity_metrics(out.cpu().numpy(), ref)
+    # the only rounding is the bf16 hidden activation (rel 2^-9 per element, averaged over 4C terms)
+    assert m["snr_db"] > 50 and m["rel_max"] < 5e-3, m
+
+
+@pytest.mark.parametrize("stage,B,rows", [(1, 2, 5), (2, 1, 17), (3, 2, 40), (4, 1, 130), (5, 2, 200), (6, 1, 300),
+                                          (6, 3, 1), (1, 130, 1)])
+def test_polyphase_upsample(full_decoder, stage, B, rows):
+    dec, w = full_decoder
+    Cin, Cout, r = FULL.stage_channels(stage - 1), FULL.stage_channels(stage), FULL.ratios[stage - 1]
+    x = round_to_bf16(_rng(500 + stage * 7 + rows).standard_normal((B, rows, Cin)).astype(np.float32))
+    p = f"decoder.upsample_layers.{stage}.0.convtr.convtr."
+    ref, _ = O.sconv_transpose1d(x.transpose(0, 2, 1), w[p + "weight"], w[p + "bias"], r)     # [B, Cout, rows*r]
+    xb = torch.full((B, rows + 1, Cin), 7.0, dtype=torch.bfloat16, device="cuda")              # row 0: garbage on entry
+    xb[:, 1:] = torch.from_numpy(x).cuda().to(torch.bfloat16)
+    y = torch.empty((B, rows * r, Cout), dtype=torch.float32, device="cuda")
+    rc = dec._lib.vv_kernel_upsample(dec._h, stage, _ptr(xb), _ptr(y), B, rows, _stream())
+    _check(dec, rc, "vv_kernel_upsample")
+    torch.cuda.synchronize()
+    m = O.parity_metrics(y.cpu().numpy().transpose(0, 2, 1), ref)
+    assert m["rel_max"] < 2e-5, m                          # bf16 products are exact in fp32; order only
+
+
+@pytest.mark.parametrize("B,rows,dt", [(2, 500, "f32"), (1, 3, "f32"), (3, 64, "bf16")])
+def test_head_fir(full_decoder, B, rows, dt):
+    dec, w = full_decoder
+    x = _rng(900 + rows).standard_normal((B, rows, 32)).astype(np.float32)
+    ref, _ = O.sconv1d(x.transpose(0, 2, 1), w["decoder.head.conv.conv.weight"], w["decoder.head.conv.conv.bias"])
+    xt = torch.from_numpy(x).cuda()
+    out = torch.empty((B, rows), dtype=torch.float32 if dt == "f32" else torch.bfloat16, device="cuda")
+    rc = dec._lib.vv_kernel_head(dec._h, _ptr(xt), _ptr(out), 0 if dt == "f32" else 1, B, rows, _stream())
+    _check(dec, rc, "vv_kernel_head")
+    torch.cuda.synchronize()
+    m = O.parity_metrics(out.float().cpu().numpy(), ref[:, 0])
+    assert m["rel_max"] < (1e-5 if dt == "f32" else 8e-3), m

@@ -1,0 +1,870 @@
+// vvdec.cu — C ABI of the B200-native VibeVoice acoustic-tokenizer decoder (include/vvdec.h):
+// weight packing, workspace planning, the launch schedule of one decode pass, streaming state.
+// Replaces TokenizerDecoder.forward / forward_features (modular_vibevoice_tokenizer.py:914-951) behind
+// VibeVoiceAcousticTokenizerModel.decode (:1099-1108).  No CPU fallback: every path below launches CUDA.
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+#include <algorithm>
+#include <cmath>
+#include "vvdec_internal.h"
+#include "rowops.cuh"
+
+namespace vv {
+
+static thread_local char g_err[512] = "";
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+const char* get_error() { return g_err; }
+
+// ---- TMA tensor maps (driver entry point fetched through the runtime: no link against libcuda) ---------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (fn == nullptr) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  }
+  return fn;
+}
+
+// bf16 tensor [d2][d1][d0] (d0 contiguous), box (b0, b1, b2); swizzle span = b0 * 2 bytes (128 or 64).
+static int encode_map(CUtensorMap* tm, const void* ptr, int rank, const uint64_t* dims, const uint64_t* strides_b,
+                      const uint32_t* box) {
+  EncodeTiledFn fn = get_encode_fn();
+  if (fn == nullptr) {
+    set_error("cuTensorMapEncodeTiled entry point unavailable");
+    return VV_ERR_CUDA;
+  }
+  cuuint64_t gd[3], gs[2];
+  cuuint32_t bx[3], es[3] = {1, 1, 1};
+  for (int i = 0; i < rank; ++i) { gd[i] = dims[i]; bx[i] = box[i]; }
+  for (int i = 0; i + 1 < rank; ++i) gs[i] = strides_b[i];
+  const CUtensorMapSwizzle sw = (box[0] * 2 == 128) ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B;
+  CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(ptr), gd, gs, bx, es,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeTiled failed (%d) rank=%d dims=%llu,%llu box=%u,%u", (int)r, rank,
+              (unsigned long long)dims[0], (unsigned long long)dims[1], box[0], box[1]);
+    return VV_ERR_CUDA;
+  }
+  return VV_OK;
+}
+
+static inline uint16_t f32_to_bf16_rne(float f) {
+  uint32_t u;
+  memcpy(&u, &f, 4);
+  if ((u & 0x7fffffffu) > 0x7f800000u) return (uint16_t)((u >> 16) | 0x40);
+  u += 0x7fffu + ((u >> 16) & 1u);
+  return (uint16_t)(u >> 16);
+}
+
+static inline long long align_up(long long v, long long a) { return (v + a - 1) / a * a; }
+
+}  // namespace vv
+
+using namespace vv;
+
+// =====================================================================================================
+// library
+// =====================================================================================================
+extern "C" int32_t vv_abi_version(void) { return VVDEC_ABI_VERSION; }
+extern "C" const char* vv_last_error(void) { return get_error(); }
+extern "C" const char* vv_status_string(int32_t s) {
+  switch (s) {
+    case VV_OK: return "ok";
+    case VV_ERR_INVALID_ARG: return "invalid argument";
+    case VV_ERR_BAD_SHAPE: return "bad shape";
+    case VV_ERR_BAD_DTYPE: return "bad dtype";
+    case VV_ERR_UNSUPPORTED: return "unsupported configuration";
+    case VV_ERR_NOT_FINALIZED: return "decoder not finalized / weight missing";
+    case VV_ERR_WORKSPACE: return "workspace too small";
+    case VV_ERR_SLOT: return "stream slot out of range";
+    case VV_ERR_CUDA: return "CUDA error";
+    case VV_ERR_NO_DEVICE: return "no sm_100 CUDA device";
+    case VV_ERR_UNKNOWN_TENSOR: return "unknown tensor name";
+    default: return "unknown status";
+  }
+}
+
+// =====================================================================================================
+// decoder life cycle
+// =====================================================================================================
+static int stage_channels(const vv_config& c, int i) { return c.n_filters << (c.n_stages - 1 - i); }
+
+extern "C" int32_t vv_decoder_create(const vv_config* cfg, vv_decoder** out) {
+  if (cfg == nullptr || out == nullptr) { set_error("null argument"); return VV_ERR_INVALID_ARG; }
+  *out = nullptr;
+  if (cfg->n_stages < 2 || cfg->n_stages > VV_MAX_STAGES || cfg->kernel_size != 7) {
+    set_error("unsupported geometry: n_stages=%d kernel_size=%d (path implements k=7, 2..%d stages)",
+              cfg->n_stages, cfg->kernel_size, VV_MAX_STAGES);
+    return VV_ERR_UNSUPPORTED;
+  }
+  const int c_last = stage_channels(*cfg, cfg->n_stages - 1);
+  if (c_last != 32 || cfg->vae_dim % 32 != 0 || cfg->vae_dim > 256) {
+    set_error("unsupported geometry: n_filters=%d vae_dim=%d (kernels are specialised for n_filters=32, "
+              "vae_dim a multiple of 32)", cfg->n_filters, cfg->vae_dim);
+    return VV_ERR_UNSUPPORTED;
+  }
+  if (stage_channels(*cfg, 0) > 2048) { set_error("stage-0 channels > 2048 unsupported"); return VV_ERR_UNSUPPORTED; }
+  for (int i = 0; i + 1 < cfg->n_stages; ++i)
+    if (cfg->ratios[i] < 1 || cfg->ratios[i] > 16) { set_error("ratio %d out of range", cfg->ratios[i]); return VV_ERR_UNSUPPORTED; }
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || cfg->device < 0 || cfg->device >= ndev) {
+    set_error("CUDA device %d not available (%d devices)", cfg->device, ndev);
+    return VV_ERR_NO_DEVICE;
+  }
+  cudaDeviceProp prop;
+  VV_CUDA(cudaGetDeviceProperties(&prop, cfg->device));
+  if (prop.major != 10) {
+    set_error("device %d is sm_%d%d; this library only contains sm_100a code", cfg->device, prop.major, prop.minor);
+    return VV_ERR_NO_DEVICE;
+  }
+  vv_decoder* d = new vv_decoder();
+  d->cfg = *cfg;
+  d->hop = 1;
+  for (int i = 0; i + 1 < cfg->n_stages; ++i) d->hop *= cfg->ratios[i];
+  // causal receptive field in latent frames: sum of left taps / layer input rate
+  double ctx = 6.0;
+  int rate = 1;
+  for (int i = 0; i < cfg->n_stages; ++i) {
+    if (i > 0) { ctx += 1.0 / rate; rate *= cfg->ratios[i - 1]; }
+    ctx += cfg->depths[i] * 6.0 / rate;
+  }
+  ctx += 6.0 / d->hop;
+  d->halo = (int)std::ceil(ctx - 1e-9);
+  *out = d;
+  return VV_OK;
+}
+
+extern "C" int32_t vv_decoder_destroy(vv_decoder* d) {
+  if (d == nullptr) return VV_OK;
+  cudaSetDevice(d->cfg.device);
+  for (void* p : d->allocs) cudaFree(p);
+  delete d;
+  return VV_OK;
+}
+
+extern "C" int64_t vv_decoder_param_count(const vv_decoder* d) { return d ? d->param_count : 0; }
+extern "C" int32_t vv_decoder_hop(const vv_decoder* d) { return d ? d->hop : 0; }
+extern "C" int32_t vv_decoder_halo_frames(const vv_decoder* d) { return d ? d->halo : 0; }
+extern "C" int64_t vv_decoder_take_launch_count(vv_decoder* d) {
+  if (!d) return 0;
+  int64_t n = d->launches;
+  d->launches = 0;
+  return n;
+}
+
+extern "C" int32_t vv_decoder_load_tensor(vv_decoder* d, const char* name, const void* data, int32_t dtype,
+                                          const int64_t* shape, int32_t ndim, int32_t is_device) {
+  if (!d || !name || !data || !shape || ndim < 1 || ndim > 3) { set_error("bad argument"); return VV_ERR_INVALID_ARG; }
+  if (dtype != VV_F32 && dtype != VV_BF16) { set_error("dtype %d", dtype); return VV_ERR_BAD_DTYPE; }
+  if (strncmp(name, "decoder.", 8) != 0) { set_error("'%s' is not a decoder parameter", name); return VV_ERR_UNKNOWN_TENSOR; }
+  int64_t n = 1;
+  for (int i = 0; i < ndim; ++i) n *= shape[i];
+  const size_t esz = dtype == VV_F32 ? 4 : 2;
+  std::vector<uint8_t> raw((size_t)n * esz);
+  if (is_device) {
+    cudaSetDevice(d->cfg.device);
+    VV_CUDA(cudaMemcpy(raw.data(), data, raw.size(), cudaMemcpyDeviceToHost));
+  } else {
+    memcpy(raw.data(), data, raw.size());
+  }
+  std::vector<float>& dst = d->staged[name];
+  dst.resize((size_t)n);
+  if (dtype == VV_F32) {
+    memcpy(dst.data(), raw.data(), raw.size());
+  } else {
+    const uint16_t* s = reinterpret_cast<const uint16_t*>(raw.data());
+    for (int64_t i = 0; i < n; ++i) {
+      uint32_t u = (uint32_t)s[i] << 16;
+      memcpy(&dst[(size_t)i], &u, 4);
+    }
+  }
+  d->staged_shape[name].assign(shape, shape + ndim);
+  d->finalized = false;
+  return VV_OK;
+}
+
+// =====================================================================================================
+// finalize: pack the reference state-dict into kernel-native layouts
+// =====================================================================================================
+namespace {
+
+struct Packer {
+  vv_decoder* d;
+  int status = VV_OK;
+
+  const std::vector<float>* get(const std::string& name, std::initializer_list<int64_t> shape) {
+    auto it = d->staged.find(name);
+    if (it == d->staged.end()) {
+      set_error("missing tensor '%s'", name.c_str());
+      status = VV_ERR_NOT_FINALIZED;
+      return nullptr;
+    }
+    const std::vector<int64_t>& got = d->staged_shape[name];
+    if (got.size() != shape.size() || !std::equal(got.begin(), got.end(), shape.begin())) {
+      set_error("tensor '%s' has the wrong shape for this geometry", name.c_str());
+      status = VV_ERR_BAD_SHAPE;
+      return nullptr;
+    }
+    d->param_count += (int64_t)it->second.size();
+    return &it->second;
+  }
+  template <typename T>
+  T* upload(const std::vector<T>& h) {
+    void* p = nullptr;
+    if (cudaMalloc(&p, std::max<size_t>(h.size() * sizeof(T), 16)) != cudaSuccess ||
+        cudaMemcpy(p, h.data(), h.size() * sizeof(T), cudaMemcpyHostToDevice) != cudaSuccess) {
+      set_error("weight upload failed: %s", cudaGetErrorString(cudaGetLastError()));
+      status = VV_ERR_CUDA;
+      return nullptr;
+    }
+    d->allocs.push_back(p);
+    return reinterpret_cast<T*>(p);
+  }
+  // bf16 [N, n_taps*Ktap] K-major GEMM weight + bias + TMA map
+  void dense(DenseW& w, const std::vector<uint16_t>& wp, const std::vector<float>& bias, int N, int Ktap,
+             int n_taps) {
+    if (status != VV_OK) return;
+    w.N = N; w.Ktap = Ktap; w.n_taps = n_taps; w.K = Ktap * n_taps;
+    w.BK = (Ktap % 64 == 0) ? 64 : 32;
+    w.BN = (N % 128 == 0) ? 128 : (N % 64 == 0) ? 64 : 32;
+    w.w = reinterpret_cast<__nv_bfloat16*>(upload(wp));
+    w.bias = upload(bias);
+    if (status != VV_OK) return;
+    const uint64_t dims[2] = {(uint64_t)w.K, (uint64_t)N};
+    const uint64_t strides[1] = {(uint64_t)w.K * 2};
+    const uint32_t box[2] = {(uint32_t)w.BK, (uint32_t)w.BN};
+    status = encode_map(&w.tm, w.w, 2, dims, strides, box);
+  }
+};
+
+std::vector<uint16_t> to_bf16(const std::vector<float>& v) {
+  std::vector<uint16_t> o(v.size());
+  for (size_t i = 0; i < v.size(); ++i) o[i] = f32_to_bf16_rne(v[i]);
+  return o;
+}
+
+}  // namespace
+
+extern "C" int32_t vv_decoder_finalize(vv_decoder* d) {
+  if (!d) { set_error("null decoder"); return VV_ERR_INVALID_ARG; }
+  if (d->finalized) return VV_OK;
+  VV_CUDA(cudaSetDevice(d->cfg.device));
+  for (void* p : d->allocs) cudaFree(p);
+  d->allocs.clear();
+  d->stages.clear();
+  d->param_count = 0;
+  const vv_config& c = d->cfg;
+  Packer pk{d};
+  const int D = c.vae_dim;
+  long long soff = 0;
+  int rate = 1;
+  for (int i = 0; i < c.n_stages && pk.status == VV_OK; ++i) {
+    StageW st;
+    st.C = stage_channels(c, i);
+    const int C = st.C;
+    if (i == 0) {
+      // stem SConv1d(D -> C, k7) (:864-867): Wp[co][j*D + ci] = w[co][ci][j]; tap j reads padded row t+j = x[t-6+j]
+      const auto* w = pk.get("decoder.upsample_layers.0.0.conv.conv.weight", {C, D, 7});
+      const auto* b = pk.get("decoder.upsample_layers.0.0.conv.conv.bias", {C});
+      if (!w || !b) break;
+      std::vector<uint16_t> wp((size_t)C * 7 * D);
+      for (int co = 0; co < C; ++co)
+        for (int ci = 0; ci < D; ++ci)
+          for (int j = 0; j < 7; ++j)
+            wp[(size_t)co * 7 * D + (size_t)j * D + ci] = f32_to_bf16_rne((*w)[((size_t)co * D + ci) * 7 + j]);
+      pk.dense(st.up, wp, *b, C, D, 7);
+      st.ratio = 1;
+      st.up_state_off = soff;
+      soff += align_up(6LL * D * 2, 16);
+    } else {
+      // SConvTranspose1d(Cin -> C, k=2r, stride r) (:875-878) in polyphase form:
+      //   out[q*r + rho][co] = b[co] + sum_ci W[ci][co][rho] x[q][ci] + W[ci][co][rho + r] x[q-1][ci]
+      // GEMM row n = rho*C + co; K = [tap 0: x[q-1] | tap 1: x[q]]  (tap = +row shift in the haloed buffer)
+      const int r = c.ratios[i - 1];
+      const int Cin = stage_channels(c, i - 1);
+      const std::string p = "decoder.upsample_layers." + std::to_string(i) + ".0.convtr.convtr.";
+      const auto* w = pk.get(p + "weight", {Cin, C, 2 * r});
+      const auto* b = pk.get(p + "bias", {C});
+      if (!w || !b) break;
+      const int N = r * C;
+      std::vector<uint16_t> wp((size_t)N * 2 * Cin);
+      std::vector<float> bias((size_t)N);
+      for (int rho = 0; rho < r; ++rho)
+        for (int co = 0; co < C; ++co) {
+          const size_t n = (size_t)rho * C + co;
+          bias[n] = (*b)[co];
+          for (int ci = 0; ci < Cin; ++ci) {
+            const size_t src = ((size_t)ci * C + co) * (2 * r);
+            wp[n * 2 * Cin + ci] = f32_to_bf16_rne((*w)[src + rho + r]);        // tap 0: x[q-1]
+            wp[n * 2 * Cin + Cin + ci] = f32_to_bf16_rne((*w)[src + rho]);      // tap 1: x[q]
+          }
+        }
+      pk.dense(st.up, wp, bias, N, Cin, 2);
+      st.ratio = r;
+      rate *= r;
+      st.up_state_off = soff;
+      soff += align_up((long long)Cin * 2, 16);
+    }
+    st.rate = rate;
+    for (int j = 0; j < c.depths[i] && pk.status == VV_OK; ++j) {
+      const std::string p = "decoder.stages." + std::to_string(i) + "." + std::to_string(j) + ".";
+      BlockW bw;
+      const auto* g = pk.get(p + "gamma", {C});
+      const auto* fg = pk.get(p + "ffn_gamma", {C});
+      const auto* nw = pk.get(p + "norm.weight", {C});
+      const auto* fnw = pk.get(p + "ffn_norm.weight", {C});
+      const auto* dw = pk.get(p + "mixer.conv.conv.conv.weight", {C, 1, 7});
+      const auto* db = pk.get(p + "mixer.conv.conv.conv.bias", {C});
+      const auto* w1 = pk.get(p + "ffn.linear1.weight", {4 * C, C});
+      const auto* b1 = pk.get(p + "ffn.linear1.bias", {4 * C});
+      const auto* w2 = pk.get(p + "ffn.linear2.weight", {C, 4 * C});
+      const auto* b2 = pk.get(p + "ffn.linear2.bias", {C});
+      if (pk.status != VV_OK) break;
+      std::vector<float> dwt((size_t)7 * C);                 // tap-major [7][C]
+      for (int ch = 0; ch < C; ++ch)
+        for (int t = 0; t < 7; ++t) dwt[(size_t)t * C + ch] = (*dw)[(size_t)ch * 7 + t];
+      bw.gamma = pk.upload(*g);
+      bw.ffn_gamma = pk.upload(*fg);
+      bw.norm_w = pk.upload(*nw);
+      bw.ffn_norm_w = pk.upload(*fnw);
+      bw.dw_w = pk.upload(dwt);
+      bw.dw_b = pk.upload(*db);
+      pk.dense(bw.lin1, to_bf16(*w1), *b1, 4 * C, C, 1);
+      pk.dense(bw.lin2, to_bf16(*w2), *b2, C, 4 * C, 1);
+      bw.state_off = soff;
+      soff += 6LL * C * 4;
+      st.blocks.push_back(bw);
+    }
+    d->stages.push_back(st);
+  }
+  if (pk.status == VV_OK) {
+    const int C = stage_channels(c, c.n_stages - 1);
+    const auto* w = pk.get("decoder.head.conv.conv.weight", {1, C, 7});
+    const auto* b = pk.get("decoder.head.conv.conv.bias", {1});
+    if (w && b) {
+      std::vector<float> hw((size_t)7 * C);
+      for (int ch = 0; ch < C; ++ch)
+        for (int t = 0; t < 7; ++t) hw[(size_t)t * C + ch] = (*w)[(size_t)ch * 7 + t];
+      d->head_w = pk.upload(hw);
+      d->head_bias = (*b)[0];
+      d->head_state_off = soff;
+      soff += 6LL * C * 4;
+    }
+  }
+  if (pk.status != VV_OK) return pk.status;
+  d->state_slot_bytes = align_up(soff, 256);
+  d->staged.clear();
+  d->staged_shape.clear();
+  d->finalized = true;
+  return VV_OK;
+}
+
+// =====================================================================================================
+// launch helpers
+// =====================================================================================================
+namespace {
+
+StateRef make_state_ref(vv_state* st, const int32_t* slot_ids, long long layer_off) {
+  StateRef r;
+  r.slot_ids = slot_ids;
+  r.parity = st ? st->parity : nullptr;
+  r.base = st ? st->base : nullptr;
+  r.bank_bytes = st ? st->bank_bytes : 0;
+  r.slot_bytes = st ? st->slot_bytes : 0;
+  r.layer_off = layer_off;
+  return r;
+}
+
+struct EpiOut {
+  int epi = EPI_BIAS_F32;
+  const float* gamma = nullptr;
+  const float* resid = nullptr;
+  float* out_f32 = nullptr;
+  __nv_bfloat16* out_bf16 = nullptr;
+  int bf16_halo = 0;            // out_bf16 rows per batch item = rows + bf16_halo, first bf16_halo rows skipped
+};
+
+template <int BN, int BK>
+int launch_gemm_inst(const CUtensorMap& tmA, const DenseW& w, const GemmArgs& g, dim3 grid, cudaStream_t s) {
+  static bool attr_set = false;
+  const size_t smem = gemm_smem_bytes<BN, BK>(g.stages);
+  if (!attr_set) {
+    constexpr int per_stage = GEMM_BM * BK * 2 + BN * BK * 2;
+    VV_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<BN, BK>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)gemm_smem_bytes<BN, BK>(std::min(GEMM_MAX_STAGES, (96 * 1024) / per_stage))));
+    attr_set = true;
+  }
+  gemm_tc_kernel<BN, BK><<<grid, GEMM_THREADS, smem, s>>>(tmA, w.tm, g);
+  return VV_OK;
+}
+
+// D = A (*) W with the fused epilogue.  A: bf16 [nbatch, a_rpb, Ktap] (a_rpb >= rows + n_taps - 1).
+int launch_gemm(vv_decoder* d, const __nv_bfloat16* A, long long a_rpb, int rows, int nbatch, const DenseW& w,
+                const EpiOut& e, cudaStream_t s) {
+  GemmArgs g;
+  memset(&g, 0, sizeof(g));
+  g.rows = rows; g.nbatch = nbatch; g.n_taps = w.n_taps; g.kb_per_tap = w.Ktap / w.BK; g.N = w.N;
+  g.epi = e.epi; g.bias = w.bias; g.gamma = e.gamma; g.resid = e.resid;
+  g.out_f32 = e.out_f32; g.of_rpb = rows; g.of_off = 0;
+  g.out_bf16 = e.out_bf16; g.ob_rpb = rows + e.bf16_halo; g.ob_off = e.bf16_halo;
+  const int nk = g.n_taps * g.kb_per_tap;
+  const int per_stage = GEMM_BM * w.BK * 2 + w.BN * w.BK * 2;
+  g.stages = std::max(1, std::min(std::min(nk, GEMM_MAX_STAGES), (96 * 1024) / per_stage));
+  // tile shape over (rows, batch): 2^k rows x 128/2^k items, whichever needs fewer tiles
+  int best_log2 = 7;
+  long long best_tiles = -1;
+  for (int k = 0; k <= 7; ++k) {
+    const int bt = 1 << k, bb = 128 >> k;
+    const long long tiles = (long long)((rows + bt - 1) / bt) * ((nbatch + bb - 1) / bb);
+    if (best_tiles < 0 || tiles <= best_tiles) { best_tiles = tiles; best_log2 = k; }
+  }
+  g.bt_log2 = best_log2;
+  d->launches++;
+  if (d->cfg.gemm_path == 1) {
+    GemmRefArgs r;
+    r.A = A; r.a_rpb = a_rpb; r.W = w.w; r.Ktap = w.Ktap; r.g = g;
+    const long long work = (long long)nbatch * rows * (w.N / 32);
+    gemm_ref_kernel<<<(unsigned)((work + 127) / 128), 128, 0, s>>>(r);
+    VV_CUDA(cudaGetLastError());
+    return VV_OK;
+  }
+  CUtensorMap tmA;
+  const uint64_t dims[3] = {(uint64_t)w.Ktap, (uint64_t)a_rpb, (uint64_t)nbatch};
+  const uint64_t strides[2] = {(uint64_t)w.Ktap * 2, (uint64_t)a_rpb * w.Ktap * 2};
+  const uint32_t box[3] = {(uint32_t)w.BK, 1u << best_log2, 128u >> best_log2};
+  int rc = encode_map(&tmA, A, 3, dims, strides, box);
+  if (rc != VV_OK) return rc;
+  const long long n_cta = best_tiles * (w.N / w.BN);
+  if (n_cta > 0x7fffffffLL) { set_error("internal: %lld tiles exceed the launch limit", n_cta); return VV_ERR_WORKSPACE; }
+  dim3 grid((unsigned)n_cta);
+  if (w.BN == 128 && w.BK == 64) rc = launch_gemm_inst<128, 64>(tmA, w, g, grid, s);
+  else if (w.BN == 64 && w.BK == 64) rc = launch_gemm_inst<64, 64>(tmA, w, g, grid, s);
+  else if (w.BN == 32 && w.BK == 64) rc = launch_gemm_inst<32, 64>(tmA, w, g, grid, s);
+  else if (w.BN == 128 && w.BK == 32) rc = launch_gemm_inst<128, 32>(tmA, w, g, grid, s);
+  else if (w.BN == 64 && w.BK == 32) rc = launch_gemm_inst<64, 32>(tmA, w, g, grid, s);
+  else if (w.BN == 32 && w.BK == 32) rc = launch_gemm_inst<32, 32>(tmA, w, g, grid, s);
+  else { set_error("no GEMM instance for BN=%d BK=%d", w.BN, w.BK); return VV_ERR_UNSUPPORTED; }
+  if (rc != VV_OK) return rc;
+  VV_CUDA(cudaGetLastError());
+  return VV_OK;
+}
+
+int pick_strip(long long total_rows, int rows) {
+  // longer strips amortise the 6 warm-up rows; shorter ones keep the machine full on small problems
+  int strip = 113;
+  while (strip > 15 && total_rows / strip < 148LL * 64) strip = (strip - 1) / 2 + 1;
+  return std::max(1, std::min(strip, rows));
+}
+
+int launch_mixer(vv_decoder* d, const BlockW& bw, int C, const float* x, float* y, __nv_bfloat16* a, int nbatch,
+                 int rows, vv_state* st, const int32_t* slots, cudaStream_t s) {
+  MixerArgs p;
+  p.x = x; p.y = y; p.a = a;
+  p.norm_w = bw.norm_w; p.dw_w = bw.dw_w; p.dw_b = bw.dw_b; p.gamma = bw.gamma; p.ffn_norm_w = bw.ffn_norm_w;
+  p.nbatch = nbatch; p.rows = rows; p.C = C; p.eps = d->cfg.eps;
+  p.strip = pick_strip((long long)nbatch * rows, rows);
+  p.strips_per_batch = (rows + p.strip - 1) / p.strip;
+  p.st = make_state_ref(st, slots, bw.state_off);
+  const long long groups = (long long)nbatch * p.strips_per_batch;
+  const int lpr = C / 4;
+  d->launches++;
+#define VV_MIXER_CASE(L)                                                                         \
+  case L:                                                                                        \
+    if (L <= 32) mixer_kernel<L><<<(unsigned)((groups * L + 127) / 128), 128, 0, s>>>(p);        \
+    else mixer_kernel<L><<<(unsigned)groups, L, 0, s>>>(p);                                      \
+    break;
+  switch (lpr) {
+    VV_MIXER_CASE(8) VV_MIXER_CASE(16) VV_MIXER_CASE(32) VV_MIXER_CASE(64) VV_MIXER_CASE(128)
+    VV_MIXER_CASE(256) VV_MIXER_CASE(512)
+    default: set_error("no mixer kernel for C=%d", C); return VV_ERR_UNSUPPORTED;
+  }
+#undef VV_MIXER_CASE
+  VV_CUDA(cudaGetLastError());
+  return VV_OK;
+}
+
+}  // namespace
+
+// =====================================================================================================
+// one decode pass over [nb, T] frames, everything resident in the workspace
+// =====================================================================================================
+namespace {
+
+struct StageBufs { long long x, y, a, h, xb, total; };
+
+// bytes of the per-stage buffers for nb items x T frames (all offsets 1 KB aligned)
+StageBufs stage_bufs(const vv_decoder* d, int i, long long nb, long long T) {
+  const StageW& st = d->stages[i];
+  const long long rows_pb = T * st.rate, R = nb * rows_pb, C = st.C;
+  StageBufs b;
+  long long off = 0;
+  b.x = off; off += align_up(R * C * 4, 1024);
+  b.y = off; off += align_up(R * C * 4, 1024);
+  b.a = off; off += align_up(R * C * 2, 1024);
+  b.h = off; off += align_up(R * C * 4 * 2, 1024);
+  b.xb = off; off += align_up(nb * (rows_pb + 1) * C * 2, 1024);
+  b.total = off;
+  return b;
+}
+
+long long pass_bytes(const vv_decoder* d, long long nb, long long T) {
+  long long arena = 0;
+  for (int i = 0; i < (int)d->stages.size(); ++i) arena = std::max(arena, stage_bufs(d, i, nb, T).total);
+  return align_up(nb * (T + 6) * d->cfg.vae_dim * 2, 1024) + 2 * arena + 1024;
+}
+
+struct LatView { const void* p; int is_bf16; long long sb, st, sd; };
+
+int run_pass(vv_decoder* d, const LatView& lat, int nb, int T, void* audio, int out_dtype, long long out_bstride,
+             uint8_t* ws, vv_state* st, const int32_t* slots, cudaStream_t s) {
+  const int D = d->cfg.vae_dim;
+  long long arena = 0;
+  const int S = (int)d->stages.size();
+  for (int i = 0; i < S; ++i) arena = std::max(arena, stage_bufs(d, i, nb, T).total);
+  __nv_bfloat16* LB = reinterpret_cast<__nv_bfloat16*>(ws);
+  uint8_t* ar[2];
+  ar[0] = ws + align_up((long long)nb * (T + 6) * D * 2, 1024);
+  ar[1] = ar[0] + arena;
+
+  {  // latents -> bf16 [nb, T+6, D] with the causal context rows
+    PrepArgs p;
+    p.lat = lat.p; p.lat_is_bf16 = lat.is_bf16; p.sb = lat.sb; p.st = lat.st; p.sd = lat.sd;
+    p.out = LB; p.nbatch = nb; p.T = T; p.D = D;
+    p.st_ref = make_state_ref(st, slots, d->stages[0].up_state_off);
+    const long long total = (long long)nb * (T + 6) * D;
+    prep_latents_kernel<<<(unsigned)std::min<long long>((total + 255) / 256, 148 * 16), 256, 0, s>>>(p);
+    d->launches++;
+    VV_CUDA(cudaGetLastError());
+  }
+  int rc;
+  for (int i = 0; i < S; ++i) {
+    const StageW& sw = d->stages[i];
+    const StageBufs bo = stage_bufs(d, i, nb, T);
+    uint8_t* base = ar[i & 1];
+    float* X = reinterpret_cast<float*>(base + bo.x);
+    float* Y = reinterpret_cast<float*>(base + bo.y);
+    __nv_bfloat16* A = reinterpret_cast<__nv_bfloat16*>(base + bo.a);
+    __nv_bfloat16* H = reinterpret_cast<__nv_bfloat16*>(base + bo.h);
+    __nv_bfloat16* XB = reinterpret_cast<__nv_bfloat16*>(base + bo.xb);
+    const int rows_pb = T * sw.rate;
+    const int C = sw.C;
+    if (i == 0) {
+      EpiOut e;
+      e.epi = EPI_BIAS_F32; e.out_f32 = X;
+      rc = launch_gemm(d, LB, T + 6, T, nb, sw.up, e, s);
+      if (rc != VV_OK) return rc;
+    } else {
+      // polyphase transposed conv from the previous stage's haloed bf16 copy
+      const StageW& pw = d->stages[i - 1];
+      const StageBufs pbo = stage_bufs(d, i - 1, nb, T);
+      __nv_bfloat16* PXB = reinterpret_cast<__nv_bfloat16*>(ar[(i - 1) & 1] + pbo.xb);
+      const int prow = T * pw.rate;
+      HaloArgs hp;
+      hp.xb = PXB; hp.nbatch = nb; hp.rows = prow; hp.C = pw.C;
+      hp.st_ref = make_state_ref(st, slots, sw.up_state_off);
+      upsample_halo_kernel<<<(unsigned)std::min((nb * pw.C + 255) / 256, 148 * 8), 256, 0, s>>>(hp);
+      d->launches++;
+      VV_CUDA(cudaGetLastError());
+      EpiOut e;
+      e.epi = EPI_BIAS_F32; e.out_f32 = X;
+      rc = launch_gemm(d, PXB, prow + 1, prow, nb, sw.up, e, s);
+      if (rc != VV_OK) return rc;
+    }
+    const int nblk = (int)sw.blocks.size();
+    for (int j = 0; j < nblk; ++j) {
+      const BlockW& bw = sw.blocks[j];
+      rc = launch_mixer(d, bw, C, X, Y, A, nb, rows_pb, st, slots, s);
+      if (rc != VV_OK) return rc;
+      EpiOut e1;
+      e1.epi = EPI_GELU_BF16; e1.out_bf16 = H;
+      rc = launch_gemm(d, A, (long long)nb * rows_pb, nb * rows_pb, 1, bw.lin1, e1, s);
+      if (rc != VV_OK) return rc;
+      EpiOut e2;
+      e2.epi = EPI_RESID; e2.gamma = bw.ffn_gamma; e2.resid = Y; e2.out_f32 = X;
+      const bool feeds_up = (j == nblk - 1) && (i + 1 < S);
+      if (feeds_up) {
+        e2.out_bf16 = XB; e2.bf16_halo = 1;
+        rc = launch_gemm(d, H, rows_pb, rows_pb, nb, bw.lin2, e2, s);
+      } else {
+        rc = launch_gemm(d, H, (long long)nb * rows_pb, nb * rows_pb, 1, bw.lin2, e2, s);
+      }
+      if (rc != VV_OK) return rc;
+    }
+    if (nblk == 0 && i + 1 < S) { set_error("stage %d has no blocks", i); return VV_ERR_UNSUPPORTED; }
+    if (i == S - 1) {
+      HeadArgs hp;
+      hp.x = X; hp.w = d->head_w; hp.bias = d->head_bias; hp.out = audio; hp.out_is_bf16 = (out_dtype == VV_BF16);
+      hp.out_batch_stride = out_bstride; hp.nbatch = nb; hp.rows = rows_pb;
+      hp.strip = pick_strip((long long)nb * rows_pb, rows_pb);
+      hp.strips_per_batch = (rows_pb + hp.strip - 1) / hp.strip;
+      hp.st = make_state_ref(st, slots, d->head_state_off);
+      const long long groups = (long long)nb * hp.strips_per_batch;
+      head_kernel<<<(unsigned)((groups * 8 + 127) / 128), 128, 0, s>>>(hp);
+      d->launches++;
+      VV_CUDA(cudaGetLastError());
+    }
+  }
+  if (st != nullptr) {
+    state_flip_kernel<<<(nb + 127) / 128, 128, 0, s>>>(slots, nb, st->parity);
+    d->launches++;
+    VV_CUDA(cudaGetLastError());
+  }
+  return VV_OK;
+}
+
+}  // namespace
+
+// =====================================================================================================
+// decode
+// =====================================================================================================
+extern "C" int64_t vv_decoder_workspace_bytes(const vv_decoder* d, int32_t B, int32_t T) {
+  if (!d || !d->finalized || B < 1 || T < 1) return 0;
+  return pass_bytes(d, B, T);
+}
+
+extern "C" int32_t vv_decode(vv_decoder* d, const void* latents, int32_t lat_dtype, int32_t layout, int32_t B,
+                             int32_t T, void* audio, int32_t out_dtype, void* workspace, int64_t workspace_bytes,
+                             vv_state* state, const int32_t* slot_ids, void* cuda_stream) {
+  if (!d || !latents || !audio || !workspace) { set_error("null argument"); return VV_ERR_INVALID_ARG; }
+  if (!d->finalized) { set_error("vv_decoder_finalize has not succeeded"); return VV_ERR_NOT_FINALIZED; }
+  if (B < 1 || T < 1) { set_error("B=%d T=%d", B, T); return VV_ERR_BAD_SHAPE; }
+  if ((lat_dtype != VV_F32 && lat_dtype != VV_BF16) || (out_dtype != VV_F32 && out_dtype != VV_BF16)) {
+    set_error("dtype must be f32 or bf16");
+    return VV_ERR_BAD_DTYPE;
+  }
+  if (layout != VV_LAYOUT_BTD && layout != VV_LAYOUT_BDT) { set_error("layout %d", layout); return VV_ERR_INVALID_ARG; }
+  if (state != nullptr && slot_ids == nullptr) { set_error("state given without slot_ids"); return VV_ERR_INVALID_ARG; }
+  if (state != nullptr && state->dec != d) { set_error("state belongs to another decoder"); return VV_ERR_INVALID_ARG; }
+  if (((uintptr_t)workspace & 1023) != 0) { set_error("workspace must be 1 KB aligned"); return VV_ERR_INVALID_ARG; }
+  VV_CUDA(cudaSetDevice(d->cfg.device));
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(cuda_stream);
+  const int D = d->cfg.vae_dim;
+  const long long hop = d->hop;
+  const size_t lsz = lat_dtype == VV_F32 ? 4 : 2, osz = out_dtype == VV_F32 ? 4 : 2;
+  LatView lv;
+  lv.is_bf16 = (lat_dtype == VV_BF16);
+  if (layout == VV_LAYOUT_BTD) { lv.sb = (long long)T * D; lv.st = D; lv.sd = 1; }
+  else { lv.sb = (long long)D * T; lv.st = 1; lv.sd = T; }
+  uint8_t* ws = reinterpret_cast<uint8_t*>(workspace);
+  const long long out_bstride = (long long)T * hop;
+
+  if (pass_bytes(d, B, T) <= workspace_bytes) {          // whole call in one pass
+    lv.p = latents;
+    return run_pass(d, lv, B, T, audio, out_dtype, out_bstride, ws, state, slot_ids, s);
+  }
+  if (pass_bytes(d, 1, T) <= workspace_bytes) {          // split by utterance (independent items)
+    int nb = 1;
+    while (nb < B && pass_bytes(d, nb + 1, T) <= workspace_bytes) ++nb;
+    for (int b0 = 0; b0 < B; b0 += nb) {
+      const int n = std::min(nb, B - b0);
+      lv.p = reinterpret_cast<const uint8_t*>(latents) + (size_t)b0 * lv.sb * lsz;
+      int rc = run_pass(d, lv, n, T, reinterpret_cast<uint8_t*>(audio) + (size_t)b0 * out_bstride * osz, out_dtype,
+                        out_bstride, ws, state, state ? slot_ids + b0 : nullptr, s);
+      if (rc != VV_OK) return rc;
+    }
+    return VV_OK;
+  }
+  // split in time, one item at a time, carrying the causal context in a state (the caller's, or a
+  // zero-initialised scratch one carved from the workspace: offline == streaming with zero context)
+  vv_state scratch;
+  long long reserve = 0;
+  if (state == nullptr) {
+    reserve = align_up(2 * d->state_slot_bytes + 1024, 1024);
+    if (reserve >= workspace_bytes) { set_error("workspace too small for time chunking"); return VV_ERR_WORKSPACE; }
+    scratch.dec = d; scratch.n_slots = 1; scratch.slot_bytes = d->state_slot_bytes;
+    scratch.bank_bytes = d->state_slot_bytes;
+    scratch.base = ws + workspace_bytes - reserve;
+    scratch.parity = reinterpret_cast<int*>(scratch.base + 2 * d->state_slot_bytes);   // [0]=parity, [1]=slot id 0
+  }
+  const long long avail = workspace_bytes - reserve;
+  int Tc = 0;
+  for (int lo = 1, hi = T; lo <= hi;) {                  // largest chunk that fits
+    const int mid = lo + (hi - lo) / 2;
+    if (pass_bytes(d, 1, mid) <= avail) { Tc = mid; lo = mid + 1; } else { hi = mid - 1; }
+  }
+  if (Tc < 1) {
+    set_error("workspace of %lld bytes cannot hold one frame (%lld needed)", (long long)workspace_bytes,
+              pass_bytes(d, 1, 1) + reserve);
+    return VV_ERR_WORKSPACE;
+  }
+  for (int b = 0; b < B; ++b) {
+    vv_state* stp = state;
+    const int32_t* sl = state ? slot_ids + b : nullptr;
+    if (state == nullptr) {
+      VV_CUDA(cudaMemsetAsync(scratch.base, 0, (size_t)(2 * d->state_slot_bytes + 16), s));
+      stp = &scratch;
+      sl = scratch.parity + 1;
+    }
+    for (int t0 = 0; t0 < T; t0 += Tc) {
+      const int n = std::min(Tc, T - t0);
+      lv.p = reinterpret_cast<const uint8_t*>(latents) + ((size_t)b * lv.sb + (size_t)t0 * lv.st) * lsz;
+      int rc = run_pass(d, lv, 1, n, reinterpret_cast<uint8_t*>(audio) + ((size_t)b * out_bstride + (size_t)t0 * hop) * osz,
+                        out_dtype, out_bstride, ws, stp, sl, s);
+      if (rc != VV_OK) return rc;
+    }
+  }
+  return VV_OK;
+}
+
+// =====================================================================================================
+// streaming state
+// =====================================================================================================
+extern "C" int32_t vv_state_create(const vv_decoder* d, int32_t n_slots, vv_state** out) {
+  if (!d || !out || n_slots < 1) { set_error("bad argument"); return VV_ERR_INVALID_ARG; }
+  if (!d->finalized) { set_error("decoder not finalized"); return VV_ERR_NOT_FINALIZED; }
+  VV_CUDA(cudaSetDevice(d->cfg.device));
+  vv_state* st = new vv_state();
+  st->dec = d; st->n_slots = n_slots; st->slot_bytes = d->state_slot_bytes;
+  st->bank_bytes = st->slot_bytes * n_slots;
+  void* p = nullptr;
+  cudaError_t e = cudaMalloc(&p, (size_t)(2 * st->bank_bytes));
+  if (e == cudaSuccess) { st->base = (uint8_t*)p; e = cudaMalloc(&p, sizeof(int) * n_slots); }
+  if (e == cudaSuccess) { st->parity = (int*)p; e = cudaMemset(st->base, 0, (size_t)(2 * st->bank_bytes)); }
+  if (e == cudaSuccess) e = cudaMemset(st->parity, 0, sizeof(int) * n_slots);
+  if (e != cudaSuccess) {
+    set_error("state allocation failed: %s", cudaGetErrorString(e));
+    cudaFree(st->base); cudaFree(st->parity);
+    delete st;
+    return VV_ERR_CUDA;
+  }
+  *out = st;
+  return VV_OK;
+}
+extern "C" int32_t vv_state_destroy(vv_state* st) {
+  if (!st) return VV_OK;
+  cudaFree(st->base);
+  cudaFree(st->parity);
+  delete st;
+  return VV_OK;
+}
+extern "C" int32_t vv_state_n_slots(const vv_state* st) { return st ? st->n_slots : 0; }
+extern "C" int64_t vv_state_bytes_per_slot(const vv_state* st) { return st ? st->slot_bytes : 0; }
+
+extern "C" int32_t vv_state_zero(vv_state* st, const int32_t* slot_ids, int32_t n, void* cuda_stream) {
+  if (!st) { set_error("null state"); return VV_ERR_INVALID_ARG; }
+  if (n == 0) return VV_OK;
+  if (n > 0 && !slot_ids) { set_error("slot_ids is null"); return VV_ERR_INVALID_ARG; }
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(cuda_stream);
+  const int ny = n < 0 ? st->n_slots : n;
+  dim3 grid(8, (unsigned)ny);
+  state_zero_kernel<<<grid, 256, 0, s>>>(st->base, st->bank_bytes, st->slot_bytes, n < 0 ? nullptr : slot_ids, ny,
+                                         st->parity);
+  VV_CUDA(cudaGetLastError());
+  return VV_OK;
+}
+
+static int state_slot_ptr(const vv_state* st, int slot, uint8_t** p) {
+  if (!st || slot < 0 || slot >= st->n_slots) { set_error("slot %d out of range", slot); return VV_ERR_SLOT; }
+  int par = 0;
+  VV_CUDA(cudaDeviceSynchronize());
+  VV_CUDA(cudaMemcpy(&par, st->parity + slot, sizeof(int), cudaMemcpyDeviceToHost));
+  *p = st->base + (long long)(par & 1) * st->bank_bytes + (long long)slot * st->slot_bytes;
+  return VV_OK;
+}
+extern "C" int32_t vv_state_export(const vv_state* st, int32_t slot, void* host_dst, int64_t bytes) {
+  uint8_t* p;
+  int rc = state_slot_ptr(st, slot, &p);
+  if (rc != VV_OK) return rc;
+  if (!host_dst || bytes != st->slot_bytes) { set_error("export needs %lld bytes", (long long)st->slot_bytes); return VV_ERR_INVALID_ARG; }
+  VV_CUDA(cudaMemcpy(host_dst, p, (size_t)bytes, cudaMemcpyDeviceToHost));
+  return VV_OK;
+}
+extern "C" int32_t vv_state_import(vv_state* st, int32_t slot, const void* host_src, int64_t bytes) {
+  uint8_t* p;
+  int rc = state_slot_ptr(st, slot, &p);
+  if (rc != VV_OK) return rc;
+  if (!host_src || bytes != st->slot_bytes) { set_error("import needs %lld bytes", (long long)st->slot_bytes); return VV_ERR_INVALID_ARG; }
+  VV_CUDA(cudaMemcpy(p, host_src, (size_t)bytes, cudaMemcpyHostToDevice));
+  return VV_OK;
+}
+
+// =====================================================================================================
+// per-kernel entry points (offline form, no state) for the parity tests and bench.py's roofline leg
+// =====================================================================================================
+static int check_block(vv_decoder* d, int stage, int block) {
+  if (!d || !d->finalized) { set_error("decoder not finalized"); return VV_ERR_NOT_FINALIZED; }
+  if (stage < 0 || stage >= (int)d->stages.size() || block < 0 || block >= (int)d->stages[stage].blocks.size()) {
+    set_error("stage %d block %d out of range", stage, block);
+    return VV_ERR_INVALID_ARG;
+  }
+  return VV_OK;
+}
+
+extern "C" int32_t vv_kernel_mixer(vv_decoder* d, int32_t stage, int32_t block, const float* x, float* y, void* a_out,
+                                   int32_t B, int32_t rows, void* cuda_stream) {
+  int rc = check_block(d, stage, block);
+  if (rc != VV_OK) return rc;
+  if (!x || !y || !a_out || B < 1 || rows < 1) { set_error("bad argument"); return VV_ERR_INVALID_ARG; }
+  VV_CUDA(cudaSetDevice(d->cfg.device));
+  const StageW& sw = d->stages[stage];
+  return launch_mixer(d, sw.blocks[block], sw.C, x, y, reinterpret_cast<__nv_bfloat16*>(a_out), B, rows, nullptr,
+                      nullptr, reinterpret_cast<cudaStream_t>(cuda_stream));
+}
+
+extern "C" int32_t vv_kernel_ffn(vv_decoder* d, int32_t stage, int32_t block, const void* a, const float* resid,
+                                 float* out, void* hidden, int32_t B, int32_t rows, void* cuda_stream) {
+  int rc = check_block(d, stage, block);
+  if (rc != VV_OK) return rc;
+  if (!a || !resid || !out || !hidden || B < 1 || rows < 1) { set_error("bad argument"); return VV_ERR_INVALID_ARG; }
+  VV_CUDA(cudaSetDevice(d->cfg.device));
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(cuda_stream);
+  const BlockW& bw = d->stages[stage].blocks[block];
+  const long long R = (long long)B * rows;
+  EpiOut e1;
+  e1.epi = EPI_GELU_BF16; e1.out_bf16 = reinterpret_cast<__nv_bfloat16*>(hidden);
+  rc = launch_gemm(d, reinterpret_cast<const __nv_bfloat16*>(a), R, (int)R, 1, bw.lin1, e1, s);
+  if (rc != VV_OK) return rc;
+  EpiOut e2;
+  e2.epi = EPI_RESID; e2.gamma = bw.ffn_gamma; e2.resid = resid; e2.out_f32 = out;
+  return launch_gemm(d, reinterpret_cast<const __nv_bfloat16*>(hidden), R, (int)R, 1, bw.lin2, e2, s);
+}
+
+extern "C" int32_t vv_kernel_upsample(vv_decoder* d, int32_t stage, void* xb, float* y, int32_t B, int32_t rows,
+                                      void* cuda_stream) {
+  if (!d || !d->finalized) { set_error("decoder not finalized"); return VV_ERR_NOT_FINALIZED; }
+  if (stage < 1 || stage >= (int)d->stages.size()) { set_error("stage %d has no transposed conv", stage); return VV_ERR_INVALID_ARG; }
+  if (!xb || !y || B < 1 || rows < 1) { set_error("bad argument"); return VV_ERR_INVALID_ARG; }
+  VV_CUDA(cudaSetDevice(d->cfg.device));
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(cuda_stream);
+  const StageW& sw = d->stages[stage];
+  HaloArgs hp;
+  hp.xb = reinterpret_cast<__nv_bfloat16*>(xb); hp.nbatch = B; hp.rows = rows; hp.C = sw.up.Ktap;
+  hp.st_ref = make_state_ref(nullptr, nullptr, 0);
+  upsample_halo_kernel<<<(unsigned)std::min((B * hp.C + 255) / 256, 148 * 8), 256, 0, s>>>(hp);
+  d->launches++;
+  VV_CUDA(cudaGetLastError());
+  EpiOut e;
+  e.epi = EPI_BIAS_F32; e.out_f32 = y;
+  return launch_gemm(d, reinterpret_cast<const __nv_bfloat16*>(xb), rows + 1, rows, B, sw.up, e, s);
+}
+
+extern "C" int32_t vv_kernel_head(vv_decoder* d, const float* x, void* out, int32_t out_dtype, int32_t B, int32_t rows,
+                                  void* cuda_stream) {
+  if (!d || !d->finalized) { set_error("decoder not finalized"); return VV_ERR_NOT_FINALIZED; }
+  if (!x || !out || B < 1 || rows < 1) { set_error("bad argument"); return VV_ERR_INVALID_ARG; }
+  VV_CUDA(cudaSetDevice(d->cfg.device));
+  HeadArgs hp;
+  hp.x = x; hp.w = d->head_w; hp.bias = d->head_bias; hp.out = out; hp.out_is_bf16 = (out_dtype == VV_BF16);
+  hp.out_batch_stride = rows; hp.nbatch = B; hp.rows = rows;
+  hp.strip = pick_strip((long long)B * rows, rows);
+  hp.strips_per_batch = (rows + hp.strip - 1) / hp.strip;
+  hp.st = make_state_ref(nullptr, nullptr, 0);
+  const long long groups = (long long)B * hp.strips_per_batch;
+  head_kernel<<<(unsigned)((groups * 8 + 127) / 128), 128, 0, reinterpret_cast<cudaStream_t>(cuda_stream)>>>(hp);
+  d->launches++;
+  VV_CUDA(cudaGetLastError());
+  return VV_OK;
+}

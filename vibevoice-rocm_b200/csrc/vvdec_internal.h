@@ -1,0 +1,72 @@
+// vvdec_internal.h — host-side structures behind the C ABI in include/vvdec.h.
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+#include <map>
+#include <string>
+#include <vector>
+#include "../../include/vvdec.h"
+
+namespace vv {
+
+void set_error(const char* fmt, ...);
+const char* get_error();
+
+#define VV_CUDA(expr)                                                                       \
+  do {                                                                                      \
+    cudaError_t _e = (expr);                                                                \
+    if (_e != cudaSuccess) {                                                                \
+      vv::set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, __LINE__); \
+      return VV_ERR_CUDA;                                                                   \
+    }                                                                                       \
+  } while (0)
+
+struct DenseW {                 // one packed GEMM weight: bf16 [N, K] K-major + its TMA map
+  __nv_bfloat16* w = nullptr;
+  float* bias = nullptr;        // [N]
+  int N = 0, K = 0, Ktap = 0, n_taps = 1;
+  int BN = 0, BK = 0;
+  CUtensorMap tm;
+};
+
+struct BlockW {
+  float *norm_w = nullptr, *dw_w = nullptr, *dw_b = nullptr, *gamma = nullptr, *ffn_norm_w = nullptr,
+        *ffn_gamma = nullptr;
+  DenseW lin1, lin2;
+  long long state_off = 0;      // fp32 [6][C]
+};
+
+struct StageW {
+  int C = 0, rate = 1, ratio = 1;   // ratio: upsampling factor INTO this stage (stage 0: 1)
+  DenseW up;                        // stage 0: stem; else polyphase transposed conv
+  long long up_state_off = 0;       // stage 0: bf16 [6][D]; else bf16 [C_prev]
+  std::vector<BlockW> blocks;
+};
+
+}  // namespace vv
+
+struct vv_decoder {
+  vv_config cfg;
+  int hop = 1, halo = 0;
+  bool finalized = false;
+  std::map<std::string, std::vector<float>> staged;        // name -> fp32 host copy until finalize
+  std::map<std::string, std::vector<int64_t>> staged_shape;
+  std::vector<vv::StageW> stages;
+  float* head_w = nullptr;          // [7][C_last] tap-major
+  float head_bias = 0.f;
+  long long head_state_off = 0;     // fp32 [6][C_last]
+  long long state_slot_bytes = 0;
+  std::vector<void*> allocs;
+  int64_t param_count = 0;
+  int64_t launches = 0;
+};
+
+struct vv_state {
+  const vv_decoder* dec = nullptr;
+  int n_slots = 0;
+  long long slot_bytes = 0, bank_bytes = 0;
+  uint8_t* base = nullptr;          // 2 banks
+  int* parity = nullptr;            // [n_slots]
+};

@@ -1,0 +1,9 @@
+"""vvdec — B200-native (sm_100a) VibeVoice acoustic-tokenizer decoder behind the reference's decode() API.
+
+Importing this package loads libvvdec_b200.so; there is no CPU / PyTorch fallback.
+"""
+from . import _capi
+from .decoder import B200AcousticDecoder, B200StreamingCache, Geometry, patch
+from .shard import plan_shards, Shard
+
+__all__ = ["B200AcousticDecoder", "B200StreamingCache", "Geometry", "patch", "plan_shards", "Shard", "_capi"]

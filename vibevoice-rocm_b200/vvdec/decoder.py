@@ -1,0 +1,333 @@
+"""Host-side mirror of the reference's decode interface over the C ABI (include/vvdec.h).
+
+Mirrors, by name and argument meaning:
+  * ``VibeVoiceAcousticTokenizerModel.decode(latents, cache=None, sample_indices=None,
+    use_cache=False, debug=False)``          — vibevoice/modular/modular_vibevoice_tokenizer.py:1099-1108
+  * ``VibeVoiceTokenizerStreamingCache``      — :193-256 (``set_to_zero``, ``clear``)
+PyTorch is used for device memory, streams and nothing else; all arithmetic runs in the CUDA library.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+from typing import Dict, Iterable, Optional, Sequence, Tuple
+
+import torch
+
+from . import _capi
+
+
+@dataclass(frozen=True)
+class Geometry:
+    """The fields of VibeVoiceAcousticTokenizerConfig that fix shapes on the decode path
+    (configuration_vibevoice.py:16-44; parsed at modular_vibevoice_tokenizer.py:1011-1058)."""
+    vae_dim: int = 64
+    n_filters: int = 32
+    ratios: Tuple[int, ...] = (8, 5, 5, 4, 2, 2)
+    depths: Tuple[int, ...] = (8, 3, 3, 3, 3, 3, 3)      # decoder order (already reversed, :1028)
+    kernel_size: int = 7
+    eps: float = 1e-5
+
+    @property
+    def hop(self) -> int:
+        h = 1
+        for r in self.ratios:
+            h *= r
+        return h
+
+    def stage_channels(self, i: int) -> int:
+        return self.n_filters * (2 ** (len(self.depths) - 1 - i))
+
+    @classmethod
+    def from_config(cls, cfg) -> "Geometry":
+        """Accepts the reference's VibeVoiceAcousticTokenizerConfig; rejects every variant outside the path
+         with ValueError, like the reference's own constructors do (:649, :728)."""
+        def want(name, ok):
+            v = getattr(cfg, name, ok[0])
+            if v not in ok:
+                raise ValueError(f"unsupported tokenizer config: {name}={v!r} (this path implements {ok})")
+        want("causal", (True,))
+        want("mixer_layer", ("depthwise_conv",))
+        want("conv_norm", ("none",))
+        want("pad_mode", ("constant",))
+        want("layernorm", ("RMSNorm",))
+        want("conv_bias", (True,))
+        want("disable_last_norm", (True,))
+        want("channels", (1,))
+        enc = cfg.encoder_depths
+        enc = [int(d) for d in enc.split("-")] if isinstance(enc, str) else list(enc)
+        dd = getattr(cfg, "decoder_depths", None)
+        if dd is not None and isinstance(dd, str):
+            depths = [int(d) for d in dd.split("-")]
+        else:
+            depths = list(reversed(enc))                                        # :1024-1028
+        ratios = getattr(cfg, "decoder_ratios", None) or cfg.encoder_ratios
+        return cls(vae_dim=int(cfg.vae_dim), n_filters=int(cfg.decoder_n_filters), ratios=tuple(int(r) for r in ratios),
+                   depths=tuple(depths), kernel_size=7, eps=float(cfg.layernorm_eps))
+
+
+def _dtype_code(dt: torch.dtype) -> int:
+    if dt == torch.float32:
+        return _capi.VV_F32
+    if dt == torch.bfloat16:
+        return _capi.VV_BF16
+    raise ValueError(f"dtype {dt} not supported on this path (float32 or bfloat16)")
+
+
+class B200StreamingCache:
+    """Device-resident per-stream conv state (replaces VibeVoiceTokenizerStreamingCache, :193-256).
+
+    One slot per ``sample_idx``; every stateful layer's causal context lives in one allocation and is
+    updated in place by the decode kernels.  ``set_to_zero`` / ``clear`` keep the reference's meaning.
+    """
+
+    def __init__(self, decoder: "B200AcousticDecoder", n_slots: int = 256):
+        self._dec = decoder
+        self._lib = _capi.load()
+        h = C.c_void_p()
+        _capi.check(self._lib.vv_state_create(decoder._h, int(n_slots), C.byref(h)), "vv_state_create")
+        self._h = h
+        self.n_slots = int(n_slots)
+        self.seen = set()            # sample indices that own live state (host view, for the strict quirk)
+
+    # -- reference API -----------------------------------------------------------------------------
+    def set_to_zero(self, sample_indices):
+        """:234-241 — zero the listed streams' state, keeping them allocated."""
+        idx = self._dec._indices_tensor(sample_indices)
+        if idx.numel() == 0:
+            return
+        _capi.check(self._lib.vv_state_zero(self._h, C.c_void_p(idx.data_ptr()), int(idx.numel()),
+                                            C.c_void_p(torch.cuda.current_stream(idx.device).cuda_stream)),
+                    "vv_state_zero")
+        self._keep = idx             # keep the index tensor alive until the stream has consumed it
+
+    def clear(self, layer_id=None, sample_indices=None):
+        """:243-256 — forget state.  Per-layer clearing has no meaning for one fused state; a layer_id
+        clears the listed (or all) streams entirely, which is what every reference caller does."""
+        if sample_indices is None:
+            _capi.check(self._lib.vv_state_zero(self._h, None, -1,
+                                                C.c_void_p(torch.cuda.current_stream().cuda_stream)), "vv_state_zero")
+            self.seen.clear()
+        else:
+            self.set_to_zero(sample_indices)
+            for i in self._dec._indices_list(sample_indices):
+                self.seen.discard(i)
+
+    # -- checkpoint --------------------------------------------------------------------------------
+    def export_state(self, sample_idx: int) -> bytes:
+        n = self._lib.vv_state_bytes_per_slot(self._h)
+        buf = (C.c_uint8 * n)()
+        _capi.check(self._lib.vv_state_export(self._h, int(sample_idx), buf, n), "vv_state_export")
+        return bytes(buf)
+
+    def import_state(self, sample_idx: int, blob: bytes):
+        n = self._lib.vv_state_bytes_per_slot(self._h)
+        buf = (C.c_uint8 * n).from_buffer_copy(blob)
+        _capi.check(self._lib.vv_state_import(self._h, int(sample_idx), buf, n), "vv_state_import")
+        self.seen.add(int(sample_idx))
+
+    def __del__(self):
+        try:
+            if getattr(self, "_h", None):
+                self._lib.vv_state_destroy(self._h)
+                self._h = None
+        except Exception:
+            pass
+
+
+class B200AcousticDecoder:
+    """Drop-in for the decode half of VibeVoiceAcousticTokenizerModel on one B200."""
+
+    def __init__(self, geometry: Geometry = Geometry(), device=None, gemm_path: int = 0,
+                 max_workspace_bytes: int = 8 << 30, strict_reference_quirks: bool = False,
+                 default_slots: int = 256):
+        self._lib = _capi.load()
+        if not torch.cuda.is_available():
+            raise RuntimeError("vvdec needs a CUDA device (sm_100a); there is no CPU fallback")
+        self.device = torch.device("cuda", torch.cuda.current_device() if device is None else
+                                   (device if isinstance(device, int) else torch.device(device).index or 0))
+        self.geometry = geometry
+        cfg = _capi.VvConfig()
+        cfg.vae_dim, cfg.n_filters, cfg.n_stages = geometry.vae_dim, geometry.n_filters, len(geometry.depths)
+        if len(geometry.ratios) != len(geometry.depths) - 1 or len(geometry.depths) > _capi.VV_MAX_STAGES:
+            raise ValueError("geometry: len(ratios) must be len(depths) - 1 and at most 7")
+        for i, r in enumerate(geometry.ratios):
+            cfg.ratios[i] = r
+        for i, d in enumerate(geometry.depths):
+            cfg.depths[i] = d
+        cfg.kernel_size, cfg.eps, cfg.device, cfg.gemm_path = geometry.kernel_size, geometry.eps, self.device.index, gemm_path
+        h = C.c_void_p()
+        _capi.check(self._lib.vv_decoder_create(C.byref(cfg), C.byref(h)), "vv_decoder_create")
+        self._h = h
+        self.max_workspace_bytes = int(max_workspace_bytes)
+        self.strict_reference_quirks = bool(strict_reference_quirks)
+        self.default_slots = int(default_slots)
+        self._ws: Optional[torch.Tensor] = None
+        self.vae_dim = geometry.vae_dim
+        self.hop = geometry.hop
+
+    # -- weights -----------------------------------------------------------------------------------
+    def load_state_dict(self, sd: Dict[str, "torch.Tensor"], prefix: str = "") -> "B200AcousticDecoder":
+        """``sd`` uses the reference's names (``decoder.upsample_layers.0.0.conv.conv.weight`` ...,
+        SURVEY.md App. B), optionally under ``prefix`` (e.g. ``model.acoustic_tokenizer.``).  Values may be
+        torch tensors (any device) or numpy arrays."""
+        n = 0
+        for k, v in sd.items():
+            if not k.startswith(prefix + "decoder."):
+                continue
+            t = torch.as_tensor(v)
+            if t.dtype not in (torch.float32, torch.bfloat16):
+                t = t.float()
+            t = t.detach().contiguous()
+            shape = (C.c_int64 * t.dim())(*t.shape)
+            _capi.check(self._lib.vv_decoder_load_tensor(self._h, k[len(prefix):].encode(), C.c_void_p(t.data_ptr()),
+                                                         _dtype_code(t.dtype), shape, t.dim(), 1 if t.is_cuda else 0),
+                        f"vv_decoder_load_tensor({k})")
+            n += 1
+        if n == 0:
+            raise ValueError(f"no '{prefix}decoder.*' tensors in the state dict")
+        _capi.check(self._lib.vv_decoder_finalize(self._h), "vv_decoder_finalize")
+        return self
+
+    @classmethod
+    def from_reference(cls, model, **kw) -> "B200AcousticDecoder":
+        """Build from a reference VibeVoiceAcousticTokenizerModel instance (weights are copied)."""
+        dec = cls(Geometry.from_config(model.config), **kw)
+        return dec.load_state_dict(model.state_dict())
+
+    @property
+    def param_count(self) -> int:
+        return int(self._lib.vv_decoder_param_count(self._h))
+
+    @property
+    def halo_frames(self) -> int:
+        return int(self._lib.vv_decoder_halo_frames(self._h))
+
+    def take_launch_count(self) -> int:
+        return int(self._lib.vv_decoder_take_launch_count(self._h))
+
+    # -- helpers -----------------------------------------------------------------------------------
+    def _indices_list(self, sample_indices) -> Sequence[int]:
+        if isinstance(sample_indices, torch.Tensor):
+            return [int(i) for i in sample_indices.tolist()]
+        return [int(i) for i in sample_indices]
+
+    def _indices_tensor(self, sample_indices) -> torch.Tensor:
+        """int32 device tensor of slot ids; a CUDA tensor is consumed without a host sync."""
+        if isinstance(sample_indices, torch.Tensor):
+            return sample_indices.to(device=self.device, dtype=torch.int32).contiguous()
+        return torch.tensor(list(sample_indices), dtype=torch.int32, device=self.device)
+
+    def workspace_bytes(self, B: int, T: int) -> int:
+        return int(self._lib.vv_decoder_workspace_bytes(self._h, int(B), int(T)))
+
+    def _workspace(self, B: int, T: int) -> torch.Tensor:
+        need = min(self.workspace_bytes(B, T), self.max_workspace_bytes)
+        if self._ws is None or self._ws.numel() < need:
+            self._ws = None
+            self._ws = torch.empty(need + 1024, dtype=torch.uint8, device=self.device)
+        return self._ws
+
+    def new_cache(self, n_slots: Optional[int] = None) -> B200StreamingCache:
+        return B200StreamingCache(self, n_slots or self.default_slots)
+
+    def _state_for(self, cache) -> B200StreamingCache:
+        """Accept our cache, or ANY object the caller uses as the reference cache (e.g. a genuine
+        VibeVoiceTokenizerStreamingCache built at modeling_vibevoice_inference.py:386): the device state hangs
+        off it and its set_to_zero / clear are forwarded, so generate() runs unmodified."""
+        if isinstance(cache, B200StreamingCache):
+            return cache
+        st = getattr(cache, "_b200_state", None)
+        if st is None or st._dec is not self:
+            st = self.new_cache()
+            cache._b200_state = st
+            for name in ("set_to_zero", "clear"):
+                orig = getattr(cache, name, None)
+
+                def fwd(*a, _orig=orig, _name=name, **k):
+                    getattr(st, _name)(*a, **k)
+                    return _orig(*a, **k) if _orig is not None else None
+                setattr(cache, name, fwd)
+        return st
+
+    # -- the reference entry point --------------------------------------------------------------------
+    @torch.no_grad()
+    def decode(self, latents, cache=None, sample_indices=None, use_cache=False, debug=False):
+        """Same contract as VibeVoiceAcousticTokenizerModel.decode (:1099-1108).
+
+        latents: [B, T, vae_dim] or [B, vae_dim, T] (shape[1] == vae_dim means the latter, :1102-1105),
+        float32 or bfloat16, on this decoder's device.  Returns audio [B, 1, T*hop] in the latents' dtype.
+        ``debug`` is accepted and ignored, as in the reference's non-debug build of the path.
+        """
+        if not isinstance(latents, torch.Tensor) or latents.dim() != 3:
+            raise ValueError("latents must be a 3-D tensor")
+        if not latents.is_cuda:
+            raise RuntimeError("latents must live on the CUDA device; vvdec has no CPU path")
+        if latents.dtype not in (torch.float32, torch.bfloat16):
+            latents = latents.float()
+        D = self.vae_dim
+        if latents.shape[1] == D:                       # already [B, D, T]
+            layout, B, T = _capi.VV_LAYOUT_BDT, latents.shape[0], latents.shape[2]
+        elif latents.shape[2] == D:
+            layout, B, T = _capi.VV_LAYOUT_BTD, latents.shape[0], latents.shape[1]
+        else:
+            raise ValueError(f"latents shape {tuple(latents.shape)} has no axis of size vae_dim={D}")
+        if B == 0 or T == 0:
+            return latents.new_zeros((B, 1, T * self.hop))
+        latents = latents.contiguous()
+        state_h, slots = None, None
+        if use_cache and cache is not None:             # :317, :469
+            if sample_indices is None:
+                raise AssertionError("sample_indices must be provided for streaming mode")       # :321
+            st = self._state_for(cache)
+            slots = self._indices_tensor(sample_indices)
+            if slots.numel() != B:
+                raise AssertionError("len(sample_indices) must match batch size")                 # :322-323
+            host_view = not (isinstance(sample_indices, torch.Tensor) and sample_indices.is_cuda)
+            if self.strict_reference_quirks or host_view:
+                idx = self._indices_list(sample_indices)
+                if max(idx) >= st.n_slots or min(idx) < 0:
+                    raise IndexError(f"sample index out of range for a cache of {st.n_slots} slots")
+                if self.strict_reference_quirks and any(i not in st.seen for i in idx):
+                    st.set_to_zero(slots)               # all-or-nothing get(): everyone restarts (:204-207)
+                st.seen.update(idx)
+            state_h = st._h
+        out = torch.empty((B, 1, T * self.hop), dtype=latents.dtype, device=self.device)
+        ws = self._workspace(B, T)
+        ws_ptr = (ws.data_ptr() + 1023) & ~1023
+        ws_bytes = ws.numel() - (ws_ptr - ws.data_ptr())
+        stream = torch.cuda.current_stream(self.device).cuda_stream
+        rc = self._lib.vv_decode(self._h, C.c_void_p(latents.data_ptr()), _dtype_code(latents.dtype), layout, int(B), int(T),
+                                 C.c_void_p(out.data_ptr()), _dtype_code(out.dtype), C.c_void_p(ws_ptr), int(ws_bytes),
+                                 state_h, C.c_void_p(slots.data_ptr()) if slots is not None else None,
+                                 C.c_void_p(stream))
+        _capi.check(rc, "vv_decode")
+        self._keep = (latents, slots)                   # alive until the stream has consumed them
+        return out
+
+    __call__ = decode
+
+    def __del__(self):
+        try:
+            if getattr(self, "_h", None):
+                self._lib.vv_decoder_destroy(self._h)
+                self._h = None
+        except Exception:
+            pass
+
+
+def patch(model, **kw) -> B200AcousticDecoder:
+    """Swap ``decode`` of a reference tokenizer (or of ``model.model.acoustic_tokenizer`` inside the full
+    VibeVoice model) for the B200 path, in place; ``generate()`` (modeling_vibevoice_inference.py:635-641)
+    then runs unmodified.  Returns the decoder object."""
+    tok = model
+    for attr in ("model", "acoustic_tokenizer"):
+        if hasattr(tok, attr) and not hasattr(tok, "decoder"):
+            tok = getattr(tok, attr)
+    if not hasattr(tok, "decoder"):
+        raise ValueError("could not find an acoustic tokenizer with a .decoder on the given model")
+    dev = next(tok.parameters()).device
+    dec = B200AcousticDecoder.from_reference(tok, device=dev if dev.type == "cuda" else None, **kw)
+    tok._b200_decoder = dec
+    tok.decode = dec.decode
+    return dec
