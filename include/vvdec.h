@@ -122,6 +122,25 @@ int32_t vv_decode(vv_decoder* dec, const void* latents, int32_t lat_dtype, int32
 /* Number of kernels vv_decode enqueued since the counter was last read (bench.py's gpu_launches). */
 int64_t vv_decoder_take_launch_count(vv_decoder* dec);
 
+/*
+ * Per-launch timing for bench.py's roofline leg.  While enabled, vv_decode records a CUDA event on the
+ * decode stream after every kernel launch and synchronises the stream before returning; the elapsed
+ * time of each launch is accumulated per (kind, stage).  vv_decoder_read_profile copies up to `cap`
+ * records, clears the accumulator and returns the number of records available.
+ */
+typedef enum vv_kernel_kind {
+  VV_K_PREP = 0, VV_K_STEM = 1, VV_K_MIXER = 2, VV_K_FFN1 = 3, VV_K_FFN2 = 4, VV_K_HALO = 5,
+  VV_K_UPSAMPLE = 6, VV_K_HEAD = 7, VV_K_STATE = 8
+} vv_kernel_kind;
+typedef struct vv_profile_record {
+  int32_t kind;        /* vv_kernel_kind */
+  int32_t stage;
+  int64_t launches;
+  double  ms;          /* summed device time of those launches */
+} vv_profile_record;
+int32_t vv_decoder_set_profiling(vv_decoder* dec, int32_t enabled);
+int32_t vv_decoder_read_profile(vv_decoder* dec, vv_profile_record* out, int32_t cap);
+
 /* ---- streaming state (replaces VibeVoiceTokenizerStreamingCache, :193-256) ------------------ */
 int32_t vv_state_create(const vv_decoder* dec, int32_t n_slots, vv_state** out);   /* zero-filled */
 int32_t vv_state_destroy(vv_state* st);

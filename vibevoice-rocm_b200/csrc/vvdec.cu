@@ -75,6 +75,47 @@ static inline long long align_up(long long v, long long a) { return (v + a - 1) 
 
 using namespace vv;
 
+void vv_decoder::mark(int kind, int stage, cudaStream_t s) {
+  if (!prof_on) return;
+  cudaEvent_t ev;
+  if (!prof_pool.empty()) { ev = prof_pool.back(); prof_pool.pop_back(); }
+  else if (cudaEventCreate(&ev) != cudaSuccess) return;
+  cudaEventRecord(ev, s);
+  prof_marks.push_back({ev, kind, stage});
+}
+
+static void prof_collect(vv_decoder* d, cudaStream_t s) {
+  if (!d->prof_on || d->prof_marks.empty()) return;
+  cudaStreamSynchronize(s);
+  for (size_t i = 1; i < d->prof_marks.size(); ++i) {
+    if (d->prof_marks[i].kind < 0) continue;                 // a start mark
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, d->prof_marks[i - 1].ev, d->prof_marks[i].ev);
+    auto& acc = d->prof_acc[{d->prof_marks[i].kind, d->prof_marks[i].stage}];
+    acc.first += ms;
+    acc.second += 1;
+  }
+  for (auto& m : d->prof_marks) d->prof_pool.push_back(m.ev);
+  d->prof_marks.clear();
+}
+
+extern "C" int32_t vv_decoder_set_profiling(vv_decoder* d, int32_t enabled) {
+  if (!d) { set_error("null decoder"); return VV_ERR_INVALID_ARG; }
+  d->prof_on = enabled != 0;
+  return VV_OK;
+}
+extern "C" int32_t vv_decoder_read_profile(vv_decoder* d, vv_profile_record* out, int32_t cap) {
+  if (!d) return 0;
+  int n = 0;
+  for (auto& kv : d->prof_acc) {
+    if (out && n < cap) { out[n].kind = kv.first.first; out[n].stage = kv.first.second;
+                          out[n].launches = kv.second.second; out[n].ms = kv.second.first; }
+    ++n;
+  }
+  if (out) d->prof_acc.clear();
+  return n;
+}
+
 // =====================================================================================================
 // library
 // =====================================================================================================
@@ -412,8 +453,16 @@ int launch_gemm_inst(const CUtensorMap& tmA, const DenseW& w, const GemmArgs& g,
 }
 
 // D = A (*) W with the fused epilogue.  A: bf16 [nbatch, a_rpb, Ktap] (a_rpb >= rows + n_taps - 1).
+int launch_gemm_impl(vv_decoder* d, const __nv_bfloat16* A, long long a_rpb, int rows, int nbatch, const DenseW& w,
+                     const EpiOut& e, cudaStream_t s);
 int launch_gemm(vv_decoder* d, const __nv_bfloat16* A, long long a_rpb, int rows, int nbatch, const DenseW& w,
-                const EpiOut& e, cudaStream_t s) {
+                const EpiOut& e, cudaStream_t s, int kind = -2, int stage = 0) {
+  const int rc = launch_gemm_impl(d, A, a_rpb, rows, nbatch, w, e, s);
+  if (rc == VV_OK && kind != -2) d->mark(kind, stage, s);
+  return rc;
+}
+int launch_gemm_impl(vv_decoder* d, const __nv_bfloat16* A, long long a_rpb, int rows, int nbatch, const DenseW& w,
+                     const EpiOut& e, cudaStream_t s) {
   GemmArgs g;
   memset(&g, 0, sizeof(g));
   g.rows = rows; g.nbatch = nbatch; g.n_taps = w.n_taps; g.kb_per_tap = w.Ktap / w.BK; g.N = w.N;
@@ -539,6 +588,7 @@ int run_pass(vv_decoder* d, const LatView& lat, int nb, int T, void* audio, int 
   ar[0] = ws + align_up((long long)nb * (T + 6) * D * 2, 1024);
   ar[1] = ar[0] + arena;
 
+  d->mark(-1, 0, s);
   {  // latents -> bf16 [nb, T+6, D] with the causal context rows
     PrepArgs p;
     p.lat = lat.p; p.lat_is_bf16 = lat.is_bf16; p.sb = lat.sb; p.st = lat.st; p.sd = lat.sd;
@@ -548,6 +598,7 @@ int run_pass(vv_decoder* d, const LatView& lat, int nb, int T, void* audio, int 
     prep_latents_kernel<<<(unsigned)std::min<long long>((total + 255) / 256, 148 * 16), 256, 0, s>>>(p);
     d->launches++;
     VV_CUDA(cudaGetLastError());
+    d->mark(VV_K_PREP, 0, s);
   }
   int rc;
   for (int i = 0; i < S; ++i) {
@@ -564,7 +615,7 @@ int run_pass(vv_decoder* d, const LatView& lat, int nb, int T, void* audio, int 
     if (i == 0) {
       EpiOut e;
       e.epi = EPI_BIAS_F32; e.out_f32 = X;
-      rc = launch_gemm(d, LB, T + 6, T, nb, sw.up, e, s);
+      rc = launch_gemm(d, LB, T + 6, T, nb, sw.up, e, s, VV_K_STEM, 0);
       if (rc != VV_OK) return rc;
     } else {
       // polyphase transposed conv from the previous stage's haloed bf16 copy
@@ -578,9 +629,10 @@ int run_pass(vv_decoder* d, const LatView& lat, int nb, int T, void* audio, int 
       upsample_halo_kernel<<<(unsigned)std::min((nb * pw.C + 255) / 256, 148 * 8), 256, 0, s>>>(hp);
       d->launches++;
       VV_CUDA(cudaGetLastError());
+      d->mark(VV_K_HALO, i, s);
       EpiOut e;
       e.epi = EPI_BIAS_F32; e.out_f32 = X;
-      rc = launch_gemm(d, PXB, prow + 1, prow, nb, sw.up, e, s);
+      rc = launch_gemm(d, PXB, prow + 1, prow, nb, sw.up, e, s, VV_K_UPSAMPLE, i);
       if (rc != VV_OK) return rc;
     }
     const int nblk = (int)sw.blocks.size();
@@ -588,18 +640,19 @@ int run_pass(vv_decoder* d, const LatView& lat, int nb, int T, void* audio, int 
       const BlockW& bw = sw.blocks[j];
       rc = launch_mixer(d, bw, C, X, Y, A, nb, rows_pb, st, slots, s);
       if (rc != VV_OK) return rc;
+      d->mark(VV_K_MIXER, i, s);
       EpiOut e1;
       e1.epi = EPI_GELU_BF16; e1.out_bf16 = H;
-      rc = launch_gemm(d, A, (long long)nb * rows_pb, nb * rows_pb, 1, bw.lin1, e1, s);
+      rc = launch_gemm(d, A, (long long)nb * rows_pb, nb * rows_pb, 1, bw.lin1, e1, s, VV_K_FFN1, i);
       if (rc != VV_OK) return rc;
       EpiOut e2;
       e2.epi = EPI_RESID; e2.gamma = bw.ffn_gamma; e2.resid = Y; e2.out_f32 = X;
       const bool feeds_up = (j == nblk - 1) && (i + 1 < S);
       if (feeds_up) {
         e2.out_bf16 = XB; e2.bf16_halo = 1;
-        rc = launch_gemm(d, H, rows_pb, rows_pb, nb, bw.lin2, e2, s);
+        rc = launch_gemm(d, H, rows_pb, rows_pb, nb, bw.lin2, e2, s, VV_K_FFN2, i);
       } else {
-        rc = launch_gemm(d, H, (long long)nb * rows_pb, nb * rows_pb, 1, bw.lin2, e2, s);
+        rc = launch_gemm(d, H, (long long)nb * rows_pb, nb * rows_pb, 1, bw.lin2, e2, s, VV_K_FFN2, i);
       }
       if (rc != VV_OK) return rc;
     }
@@ -615,12 +668,14 @@ int run_pass(vv_decoder* d, const LatView& lat, int nb, int T, void* audio, int 
       head_kernel<<<(unsigned)((groups * 8 + 127) / 128), 128, 0, s>>>(hp);
       d->launches++;
       VV_CUDA(cudaGetLastError());
+      d->mark(VV_K_HEAD, i, s);
     }
   }
   if (st != nullptr) {
     state_flip_kernel<<<(nb + 127) / 128, 128, 0, s>>>(slots, nb, st->parity);
     d->launches++;
     VV_CUDA(cudaGetLastError());
+    d->mark(VV_K_STATE, 0, s);
   }
   return VV_OK;
 }
@@ -635,7 +690,7 @@ extern "C" int64_t vv_decoder_workspace_bytes(const vv_decoder* d, int32_t B, in
   return pass_bytes(d, B, T);
 }
 
-extern "C" int32_t vv_decode(vv_decoder* d, const void* latents, int32_t lat_dtype, int32_t layout, int32_t B,
+static int32_t decode_impl(vv_decoder* d, const void* latents, int32_t lat_dtype, int32_t layout, int32_t B,
                              int32_t T, void* audio, int32_t out_dtype, void* workspace, int64_t workspace_bytes,
                              vv_state* state, const int32_t* slot_ids, void* cuda_stream) {
   if (!d || !latents || !audio || !workspace) { set_error("null argument"); return VV_ERR_INVALID_ARG; }
@@ -717,6 +772,15 @@ extern "C" int32_t vv_decode(vv_decoder* d, const void* latents, int32_t lat_dty
     }
   }
   return VV_OK;
+}
+
+extern "C" int32_t vv_decode(vv_decoder* d, const void* latents, int32_t lat_dtype, int32_t layout, int32_t B,
+                             int32_t T, void* audio, int32_t out_dtype, void* workspace, int64_t workspace_bytes,
+                             vv_state* state, const int32_t* slot_ids, void* cuda_stream) {
+  const int32_t rc = decode_impl(d, latents, lat_dtype, layout, B, T, audio, out_dtype, workspace, workspace_bytes,
+                                 state, slot_ids, cuda_stream);
+  if (d != nullptr) prof_collect(d, reinterpret_cast<cudaStream_t>(cuda_stream));
+  return rc;
 }
 
 // =====================================================================================================

@@ -61,6 +61,13 @@ struct vv_decoder {
   std::vector<void*> allocs;
   int64_t param_count = 0;
   int64_t launches = 0;
+  // optional per-launch timing (vv_decoder_set_profiling): CUDA events recorded on the decode stream
+  bool prof_on = false;
+  struct ProfMark { cudaEvent_t ev; int kind; int stage; };
+  std::vector<ProfMark> prof_marks;             // marks of the call in flight
+  std::vector<cudaEvent_t> prof_pool;           // recycled events
+  std::map<std::pair<int, int>, std::pair<double, int64_t>> prof_acc;   // (kind, stage) -> (ms, launches)
+  void mark(int kind, int stage, cudaStream_t s);
 };
 
 struct vv_state {

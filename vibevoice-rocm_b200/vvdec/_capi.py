@@ -33,6 +33,12 @@ class VvConfig(C.Structure):
     ]
 
 
+class VvProfileRecord(C.Structure):
+    _fields_ = [("kind", C.c_int32), ("stage", C.c_int32), ("launches", C.c_int64), ("ms", C.c_double)]
+
+
+KERNEL_KINDS = ("prep", "stem", "mixer", "ffn1", "ffn2", "halo", "upsample", "head", "state")
+
 # name -> (restype, argtypes): every symbol include/vvdec.h declares
 _P, _I32, _I64 = C.c_void_p, C.c_int32, C.c_int64
 SIGNATURES = {
@@ -49,6 +55,8 @@ SIGNATURES = {
     "vv_decoder_workspace_bytes": (_I64, [_P, _I32, _I32]),
     "vv_decode": (_I32, [_P, _P, _I32, _I32, _I32, _I32, _P, _I32, _P, _I64, _P, _P, _P]),
     "vv_decoder_take_launch_count": (_I64, [_P]),
+    "vv_decoder_set_profiling": (_I32, [_P, _I32]),
+    "vv_decoder_read_profile": (_I32, [_P, _P, _I32]),
     "vv_state_create": (_I32, [_P, _I32, C.POINTER(_P)]),
     "vv_state_destroy": (_I32, [_P]),
     "vv_state_n_slots": (_I32, [_P]),

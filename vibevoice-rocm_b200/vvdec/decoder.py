@@ -203,6 +203,18 @@ class B200AcousticDecoder:
     def halo_frames(self) -> int:
         return int(self._lib.vv_decoder_halo_frames(self._h))
 
+    def set_profiling(self, enabled: bool) -> None:
+        """Per-launch CUDA-event timing inside vv_decode (synchronises each call while enabled)."""
+        _capi.check(self._lib.vv_decoder_set_profiling(self._h, 1 if enabled else 0), "vv_decoder_set_profiling")
+
+    def read_profile(self):
+        """-> list of dicts {kind, stage, launches, ms}; clears the accumulator."""
+        n = self._lib.vv_decoder_read_profile(self._h, None, 0)
+        buf = (_capi.VvProfileRecord * max(n, 1))()
+        n = min(n, self._lib.vv_decoder_read_profile(self._h, buf, n))
+        return [dict(kind=_capi.KERNEL_KINDS[buf[i].kind], stage=int(buf[i].stage), launches=int(buf[i].launches),
+                     ms=float(buf[i].ms)) for i in range(n)]
+
     def take_launch_count(self) -> int:
         return int(self._lib.vv_decoder_take_launch_count(self._h))
 
