@@ -1,0 +1,308 @@
+#!/usr/bin/env python
+"""bench.py — decoded audio-seconds per second of the acoustic-tokenizer decode path on N B200s.
+
+    python bench.py --gpus N --steps K --warmup W            (N > 1: launched under torch.distributed.run)
+    python bench.py --impl reference ...                      CPU arm: the numpy port of the reference path
+
+A step = one pass of the hot path over one batch of synthetic latents: BASELINE.json configs[1],
+batch 64 x 60 s (450 latent frames) per GPU, bf16 latents in / bf16 waveform out.  Utterances are sharded
+across ranks with no collective on the data path (weak scaling: every rank decodes its own 64).
+One JSON line on rank 0; see DESIGN.md "Measurement" for every key.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for p in (ROOT, os.path.join(ROOT, "vibevoice-rocm_b200")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+FRAME_RATE = 7.5
+METRIC = "decoded audio-sec/sec"
+UNIT = "audio-s/s"
+K2_B, K2_T = 64, 450
+CPU_SAMPLE_B, CPU_SAMPLE_T = 1, 75          # configs[0]: the reference's own CPU-runnable case (10 s)
+
+
+def peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.isfile(path):
+        with open(path) as f:
+            p = json.load(f)
+        return dict(hbm_gbs=float(p["hbm_gbs"]), tf_burst=float(p["bf16_tflops"]),
+                    tf_sustained=float(p.get("bf16_tflops_sustained", p["bf16_tflops"])), source="measured")
+    return dict(hbm_gbs=6650.0, tf_burst=1590.0, tf_sustained=1400.0, source="fallback")
+
+
+# --------------------------------------------------------------------------------------------------
+# CPU arm: the oracle port, timed on the host cores (checker code used as the reported CPU baseline)
+# --------------------------------------------------------------------------------------------------
+def cpu_port_audio_s_per_s(sd, steps: int, warmup: int):
+    import numpy as np
+    from oracle.geometry import FULL
+    from oracle.vv_oracle import OracleDecoder
+    from oracle.weights import make_latents
+    dec = OracleDecoder({k: v.numpy() for k, v in sd.items()}, FULL)
+    lat = make_latents(CPU_SAMPLE_B, CPU_SAMPLE_T, FULL.vae_dim, 1)
+    for _ in range(warmup):
+        dec.decode(lat)
+    ts = []
+    for _ in range(steps):
+        t0 = time.perf_counter()
+        dec.decode(lat)
+        ts.append(time.perf_counter() - t0)
+    sec = sum(ts) / len(ts)
+    return CPU_SAMPLE_B * CPU_SAMPLE_T / FRAME_RATE / sec, sec
+
+
+def run_reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import torch
+    from vvdec.synthetic import random_state_dict
+    torch.set_num_threads(os.cpu_count() or 1)
+    sd = random_state_dict()
+    v, sec = cpu_port_audio_s_per_s(sd, max(1, args.steps), max(0, args.warmup))
+    sample = f"batch {CPU_SAMPLE_B} x {CPU_SAMPLE_T} frames (10 s) per step, numpy fp32 port of the reference path"
+    line = {
+        "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"acoustic decoder, batch {K2_B} x 60 s ({K2_T} latent frames) per GPU; CPU arm "
+                               f"times a bounded sample: {sample}"},
+        "cpu_baseline": {"value": v, "unit": UNIT, "cores": os.cpu_count(), "kind": "port", "sample": sample},
+        "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# --------------------------------------------------------------------------------------------------
+# clocks
+# --------------------------------------------------------------------------------------------------
+class ClockSampler(threading.Thread):
+    REASONS = {0x1: "gpu_idle", 0x2: "applications_clocks_setting", 0x4: "sw_power_cap", 0x8: "hw_slowdown",
+               0x10: "sync_boost", 0x20: "sw_thermal_slowdown", 0x40: "hw_thermal_slowdown",
+               0x80: "hw_power_brake_slowdown", 0x100: "display_clock_setting"}
+
+    def __init__(self, index: int):
+        super().__init__(daemon=True)
+        self.index, self.samples, self.reasons, self.max_mhz, self._halt = index, [], set(), None, threading.Event()
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def run(self):
+        if self.nv is None:
+            return
+        while not self._halt.is_set():
+            try:
+                self.samples.append(self.nv.nvmlDeviceGetClockInfo(self.h, self.nv.NVML_CLOCK_SM))
+                r = self.nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                for bit, name in self.REASONS.items():
+                    if r & bit and name != "gpu_idle":
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            self._halt.wait(0.05)
+
+    def finish(self):
+        self._halt.set()
+        self.join(timeout=2)
+        s = sorted(self.samples)
+        return {"sm_mhz": (s[len(s) // 2] if s else None), "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(s)}
+
+
+# --------------------------------------------------------------------------------------------------
+# roofline bookkeeping: algorithmic work per latent frame of each kernel (DESIGN.md "Kernels")
+# --------------------------------------------------------------------------------------------------
+def kernel_work(geom, kind: str, stage: int):
+    """-> (bound, algorithmic bytes per frame, algorithmic flop per frame, bytes this design moves per frame)."""
+    C = geom.stage_channels(stage)
+    M = 1
+    for r in geom.ratios[:stage]:
+        M *= r
+    cm = C * M
+    if kind == "mixer":        # 4*C*M bytes (bf16 in + out), ~20*C*M flop; we move fp32 x, fp32 y, bf16 a
+        return "hbm", 4 * cm, 20 * cm, 10 * cm
+    if kind in ("ffn1", "ffn2"):   # FFN half = 4*C*M bytes and 16*C^2*M flop, split evenly over its two launches
+        bound = "tensor" if C >= 128 else "hbm"
+        moved = (2 * cm + 8 * cm) if kind == "ffn1" else (8 * cm + 4 * cm + 4 * cm)
+        return bound, 2 * cm, 8 * C * cm, moved
+    if kind == "upsample":     # 2*(Cin*Min + Cout*Mout) bytes, 4*Cin*Cout*r*Min flop
+        cin, r = geom.stage_channels(stage - 1), geom.ratios[stage - 1]
+        min_ = M // r
+        bound = "tensor" if cin >= 256 else "hbm"
+        return bound, 2 * (cin * min_ + cm), 4 * cin * C * r * min_, 2 * cin * min_ + 4 * cm
+    if kind == "stem":
+        return "hbm", 2 * geom.vae_dim + 2 * cm, 2 * 7 * geom.vae_dim * C, 2 * geom.vae_dim + 4 * cm
+    if kind == "head":
+        return "hbm", 2 * cm + 4 * M, 2 * 7 * cm, 4 * cm + 2 * M
+    return "hbm", 0, 0, 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--batch", type=int, default=K2_B)
+    ap.add_argument("--frames", type=int, default=K2_T)
+    ap.add_argument("--workspace-gb", type=float, default=24.0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--kernels-out", default="", help="write the per-kernel timing table (JSON) here")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+    if args.impl == "reference":
+        return run_reference_arm(args)
+
+    import torch
+    import torch.distributed as dist
+    import vvdec
+    from vvdec.synthetic import random_state_dict
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    B, T = args.batch, args.frames
+    geom = vvdec.Geometry()
+    sd = random_state_dict(geom)
+    dec = vvdec.B200AcousticDecoder(geom, device=local, max_workspace_bytes=int(args.workspace_gb * (1 << 30)))
+    dec.load_state_dict(sd)
+
+    gen = torch.Generator().manual_seed(2 + rank)
+    lat_host = torch.randn(B, T, geom.vae_dim, generator=gen).to(torch.bfloat16).pin_memory()
+    lat = lat_host.to(dev)
+    out_host = torch.empty((B, 1, T * geom.hop), dtype=torch.bfloat16).pin_memory()
+    audio_s = B * T / FRAME_RATE
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(ms: float) -> float:
+        if world == 1:
+            return ms
+        t = torch.tensor([ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    # ---- device-resident throughput --------------------------------------------------------------
+    for _ in range(args.warmup):
+        y = dec.decode(lat)
+    barrier()
+    dec.take_launch_count()
+    sampler = ClockSampler(local)
+    sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        y = dec.decode(lat)               # 738 MB of fresh activations per pass >> 126 MB L2: no flush needed
+    e1.record()
+    barrier()
+    clocks = sampler.finish()
+    launches = dec.take_launch_count()
+    ms_step = max_over_ranks(e0.elapsed_time(e1) / args.steps)
+    value = world * audio_s / (ms_step / 1e3)
+
+    # ---- end to end through the public decode() with host buffers --------------------------------
+    def e2e_step():
+        x = lat_host.to(dev, non_blocking=True)
+        out_host.copy_(dec.decode(x), non_blocking=True)
+    for _ in range(2):
+        e2e_step()
+    barrier()
+    e0.record()
+    for _ in range(args.steps):
+        e2e_step()
+    e1.record()
+    barrier()
+    ms_e2e = max_over_ranks(e0.elapsed_time(e1) / args.steps)
+    e2e = {"value": world * audio_s / (ms_e2e / 1e3), "unit": UNIT, "ms_per_step": ms_e2e,
+           "h2d_bytes_per_step": lat_host.numel() * 2, "d2h_bytes_per_step": out_host.numel() * 2}
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    # ---- per-kernel timing, live, CUDA events on the decode stream (one extra step) --------------
+    pk = peaks()
+    dec.set_profiling(True)
+    dec.decode(lat)
+    prof = dec.read_profile()
+    dec.set_profiling(False)
+    total_ms = sum(r["ms"] for r in prof) or 1.0
+    table = []
+    frames = B * T
+    for r in prof:
+        bound, abytes, aflop, moved = kernel_work(geom, r["kind"], r["stage"])
+        n = max(1, r["launches"])
+        nblk = geom.depths[r["stage"]] if r["kind"] in ("mixer", "ffn1", "ffn2") else 1
+        passes = n // nblk                                   # decode passes the workspace split the batch into
+        units = frames / passes                              # latent frames one launch processes
+        ms_launch = r["ms"] / n
+        row = dict(kind=r["kind"], stage=r["stage"], launches=n, ms_total=r["ms"], share=r["ms"] / total_ms,
+                   ms_per_launch=ms_launch, frames_per_launch=units, bound=bound,
+                   gbs_algorithmic=abytes * units / (ms_launch * 1e-3) / 1e9 if ms_launch > 0 else 0.0,
+                   gbs_moved=moved * units / (ms_launch * 1e-3) / 1e9 if ms_launch > 0 else 0.0,
+                   tflops=aflop * units / (ms_launch * 1e-3) / 1e12 if ms_launch > 0 else 0.0)
+        table.append(row)
+    table.sort(key=lambda r: -r["ms_total"])
+    top = table[0]
+    if top["bound"] == "tensor":
+        roof = {"bound": "tensor", "achieved": top["tflops"], "peak": pk["tf_sustained"], "unit": "TFLOP/s",
+                "frac": top["tflops"] / pk["tf_sustained"]}
+    else:
+        roof = {"bound": "hbm", "achieved": top["gbs_algorithmic"], "peak": pk["hbm_gbs"], "unit": "GB/s",
+                "frac": top["gbs_algorithmic"] / pk["hbm_gbs"], "moved_gbs": top["gbs_moved"]}
+    roof.update({"kernel": f"{top['kind']}@stage{top['stage']}", "share_of_step": top["share"], "traffic": None,
+                 "peak_source": pk["source"], "ms_per_launch": top["ms_per_launch"]})
+    if args.kernels_out:
+        with open(args.kernels_out, "w") as f:
+            json.dump({"config": {"B": B, "T": T, "ms_per_step": ms_step, "value": value}, "kernels": table}, f, indent=1)
+
+    # ---- CPU baseline (reported, not the target): bounded sample on the host cores -----------------
+    cpu = None
+    if not args.no_cpu_baseline:
+        torch.set_num_threads(os.cpu_count() or 1)
+        v, sec = cpu_port_audio_s_per_s(sd, 2, 1)
+        cpu = {"value": v, "unit": UNIT, "cores": os.cpu_count(), "kind": "port",
+               "sample": f"batch {CPU_SAMPLE_B} x {CPU_SAMPLE_T} frames (10 s), numpy fp32 port, {sec:.2f} s per decode"}
+
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16",
+        "data": "synthetic",
+        "config": {"workload": f"acoustic decoder bf16, batch {B} x {T / FRAME_RATE:.0f} s ({T} latent frames) synthetic "
+                               f"latents per GPU, random-init (stress) weights",
+                   "l2": "inputs >> L2 (each pass streams >700 MB of activations per utterance group)",
+                   "sharding": "utterances per rank, no data-path collective"},
+        "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roof, "cpu_baseline": cpu,
+    }
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -171,6 +171,9 @@ int32_t vv_kernel_upsample(vv_decoder* dec, int32_t stage, void* xb, float* y, i
 int32_t vv_kernel_head(vv_decoder* dec, const float* x, void* out, int32_t out_dtype, int32_t B,
                        int32_t rows, void* cuda_stream);
 
+/* The GELU of the FFN epilogue (:589, :594), alone: y[i] = gelu(x[i]); device pointers.  Accuracy test hook. */
+int32_t vv_test_gelu(const float* x, float* y, int32_t n, void* cuda_stream);
+
 #ifdef __cplusplus
 }
 #endif

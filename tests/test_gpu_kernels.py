@@ -108,3 +108,19 @@ def test_head_fir(full_decoder, B, rows, dt):
     torch.cuda.synchronize()
     m = O.parity_metrics(out.float().cpu().numpy(), ref[:, 0])
     assert m["rel_max"] < (1e-5 if dt == "f32" else 8e-3), m
+
+
+def test_gelu_epilogue_accuracy(full_decoder):
+    """The epilogue GELU (tanh.approx form of the exact erf GELU) against float64 erf: the error must stay
+    well below the bf16 rounding (2^-9 relative) the hidden activation gets next."""
+    from scipy.special import erf
+    dec, _ = full_decoder
+    x = np.concatenate([np.linspace(-12, 12, 200001), _rng(1).standard_normal(100000) * 1.5]).astype(np.float32)
+    xt = torch.from_numpy(x).cuda()
+    y = torch.empty_like(xt)
+    rc = dec._lib.vv_test_gelu(_ptr(xt), _ptr(y), x.size, _stream())
+    _check(dec, rc, "vv_test_gelu")
+    ref = 0.5 * x.astype(np.float64) * (1 + erf(x.astype(np.float64) / np.sqrt(2)))
+    err = np.abs(y.cpu().numpy().astype(np.float64) - ref)
+    print("gelu max abs err", err.max(), "max err/|x|", (err / np.maximum(np.abs(x), 1e-3)).max())
+    assert (err <= 3e-4 * np.maximum(np.abs(x), 1.0)).all()

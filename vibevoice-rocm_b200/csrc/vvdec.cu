@@ -932,3 +932,15 @@ extern "C" int32_t vv_kernel_head(vv_decoder* d, const float* x, void* out, int3
   VV_CUDA(cudaGetLastError());
   return VV_OK;
 }
+
+// GELU as the FFN epilogue evaluates it, exposed for the accuracy test (device pointers, n floats).
+namespace { __global__ void gelu_test_kernel(const float* x, float* y, int n) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) y[i] = vv::gelu_erf(x[i]);
+} }
+extern "C" int32_t vv_test_gelu(const float* x, float* y, int32_t n, void* cuda_stream) {
+  if (!x || !y || n < 1) { set_error("bad argument"); return VV_ERR_INVALID_ARG; }
+  gelu_test_kernel<<<(n + 255) / 256, 256, 0, reinterpret_cast<cudaStream_t>(cuda_stream)>>>(x, y, n);
+  VV_CUDA(cudaGetLastError());
+  return VV_OK;
+}

@@ -67,6 +67,7 @@ SIGNATURES = {
     "vv_kernel_mixer": (_I32, [_P, _I32, _I32, _P, _P, _P, _I32, _I32, _P]),
     "vv_kernel_ffn": (_I32, [_P, _I32, _I32, _P, _P, _P, _P, _I32, _I32, _P]),
     "vv_kernel_upsample": (_I32, [_P, _I32, _P, _P, _I32, _I32, _P]),
+    "vv_test_gelu": (_I32, [_P, _P, _I32, _P]),
     "vv_kernel_head": (_I32, [_P, _P, _P, _I32, _I32, _I32, _P]),
 }
 
