@@ -66,8 +66,9 @@ typedef struct vv_config {
   int32_t kernel_size;                /* 7 (depthwise mixer, stem, head)                        */
   float   eps;                        /* layernorm_eps 1e-5                                     */
   int32_t device;                     /* CUDA device ordinal                                    */
-  int32_t gemm_path;                  /* 0 = auto (tcgen05 where the shape allows), 1 = force the
-                                         CUDA-core GEMM everywhere (validation / debugging)     */
+  int32_t gemm_path;                  /* 0 = product path (fused tcgen05 FFN at C<=64, tcgen05 GEMMs
+                                         elsewhere); 1 = CUDA-core validation GEMM everywhere;
+                                         2 = unfused tcgen05 GEMMs everywhere (A/B against 0)   */
 } vv_config;
 
 typedef struct vv_decoder vv_decoder; /* opaque: packed weights + launch plan                    */
@@ -130,7 +131,7 @@ int64_t vv_decoder_take_launch_count(vv_decoder* dec);
  */
 typedef enum vv_kernel_kind {
   VV_K_PREP = 0, VV_K_STEM = 1, VV_K_MIXER = 2, VV_K_FFN1 = 3, VV_K_FFN2 = 4, VV_K_HALO = 5,
-  VV_K_UPSAMPLE = 6, VV_K_HEAD = 7, VV_K_STATE = 8
+  VV_K_UPSAMPLE = 6, VV_K_HEAD = 7, VV_K_STATE = 8, VV_K_FFN_FUSED = 9
 } vv_kernel_kind;
 typedef struct vv_profile_record {
   int32_t kind;        /* vv_kernel_kind */

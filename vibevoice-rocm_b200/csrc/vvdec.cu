@@ -9,6 +9,7 @@
 #include <cmath>
 #include "vvdec_internal.h"
 #include "rowops.cuh"
+#include "ffn_fused.cuh"
 
 namespace vv {
 
@@ -37,9 +38,9 @@ static EncodeTiledFn get_encode_fn() {
   return fn;
 }
 
-// bf16 tensor [d2][d1][d0] (d0 contiguous), box (b0, b1, b2); swizzle span = b0 * 2 bytes (128 or 64).
+// bf16 (or fp32) tensor [d2][d1][d0] (d0 contiguous), box (b0, b1, b2); swizzle span = b0 * elem bytes (128 or 64).
 static int encode_map(CUtensorMap* tm, const void* ptr, int rank, const uint64_t* dims, const uint64_t* strides_b,
-                      const uint32_t* box) {
+                      const uint32_t* box, bool is_f32 = false) {
   EncodeTiledFn fn = get_encode_fn();
   if (fn == nullptr) {
     set_error("cuTensorMapEncodeTiled entry point unavailable");
@@ -49,8 +50,9 @@ static int encode_map(CUtensorMap* tm, const void* ptr, int rank, const uint64_t
   cuuint32_t bx[3], es[3] = {1, 1, 1};
   for (int i = 0; i < rank; ++i) { gd[i] = dims[i]; bx[i] = box[i]; }
   for (int i = 0; i + 1 < rank; ++i) gs[i] = strides_b[i];
-  const CUtensorMapSwizzle sw = (box[0] * 2 == 128) ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B;
-  CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(ptr), gd, gs, bx, es,
+  const uint32_t esz = is_f32 ? 4 : 2;
+  const CUtensorMapSwizzle sw = (box[0] * esz == 128) ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B;
+  CUresult r = fn(tm, is_f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(ptr), gd, gs, bx, es,
                   CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
@@ -511,6 +513,51 @@ int launch_gemm_impl(vv_decoder* d, const __nv_bfloat16* A, long long a_rpb, int
   return VV_OK;
 }
 
+// Whole FFN half in one kernel (C = 32, 64): hidden stays on chip.  a: bf16 [R, C]; resid/out fp32 [R, C].
+template <int C>
+int launch_ffn_fused_inst(vv_decoder* d, const CUtensorMap& tmA, const CUtensorMap& tmR, const CUtensorMap& tmO,
+                          const BlockW& bw, const FfnFusedArgs& fa, cudaStream_t s) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    VV_CUDA(cudaFuncSetAttribute(ffn_fused_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)FfnFusedSmem<C>::TOTAL));
+    attr_set = true;
+  }
+  static int num_sms = 0;
+  if (num_sms == 0) VV_CUDA(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, d->cfg.device));
+  const long long ntiles = (fa.R + 127) / 128;
+  const unsigned grid = (unsigned)std::min<long long>(ntiles, num_sms);
+  ffn_fused_kernel<C><<<grid, FF_THREADS, FfnFusedSmem<C>::TOTAL, s>>>(tmA, tmR, tmO, bw.lin1.tm, bw.lin2.tm, fa);
+  VV_CUDA(cudaGetLastError());
+  return VV_OK;
+}
+
+bool ffn_fused_supported(const vv_decoder* d, int C) { return d->cfg.gemm_path == 0 && (C == 32 || C == 64); }
+
+int launch_ffn_fused(vv_decoder* d, int C, const BlockW& bw, const __nv_bfloat16* a, const float* resid, float* out,
+                     __nv_bfloat16* out_bf16, long long R, int rows_pb, cudaStream_t s) {
+  FfnFusedArgs fa;
+  fa.R = R; fa.rows_pb = rows_pb; fa.b1 = bw.lin1.bias; fa.b2 = bw.lin2.bias; fa.gamma = bw.ffn_gamma;
+  fa.resid = resid; fa.out = out; fa.out_bf16 = out_bf16;
+  CUtensorMap tmA;
+  const uint64_t dims[2] = {(uint64_t)C, (uint64_t)R};
+  const uint64_t strides[1] = {(uint64_t)C * 2};
+  const uint32_t box[2] = {(uint32_t)C, 128u};
+  int rc = encode_map(&tmA, a, 2, dims, strides, box);
+  if (rc != VV_OK) return rc;
+  CUtensorMap tmR;                                   // residual, fp32 [R, C], boxes of [128 rows, 32 floats]
+  const uint64_t rstrides[1] = {(uint64_t)C * 4};
+  const uint32_t rbox[2] = {32u, 128u};
+  rc = encode_map(&tmR, resid, 2, dims, rstrides, rbox, true);
+  if (rc != VV_OK) return rc;
+  CUtensorMap tmO;                                   // output, same geometry as the residual
+  rc = encode_map(&tmO, out, 2, dims, rstrides, rbox, true);
+  if (rc != VV_OK) return rc;
+  d->launches++;
+  if (C == 32) return launch_ffn_fused_inst<32>(d, tmA, tmR, tmO, bw, fa, s);
+  return launch_ffn_fused_inst<64>(d, tmA, tmR, tmO, bw, fa, s);
+}
+
 int pick_strip(long long total_rows, int rows) {
   // longer strips amortise the 6 warm-up rows; shorter ones keep the machine full on small problems
   int strip = 113;
@@ -641,13 +688,19 @@ int run_pass(vv_decoder* d, const LatView& lat, int nb, int T, void* audio, int 
       rc = launch_mixer(d, bw, C, X, Y, A, nb, rows_pb, st, slots, s);
       if (rc != VV_OK) return rc;
       d->mark(VV_K_MIXER, i, s);
+      const bool feeds_up = (j == nblk - 1) && (i + 1 < S);
+      if (ffn_fused_supported(d, C)) {
+        rc = launch_ffn_fused(d, C, bw, A, Y, X, feeds_up ? XB : nullptr, (long long)nb * rows_pb, rows_pb, s);
+        if (rc != VV_OK) return rc;
+        d->mark(VV_K_FFN_FUSED, i, s);
+        continue;
+      }
       EpiOut e1;
       e1.epi = EPI_GELU_BF16; e1.out_bf16 = H;
       rc = launch_gemm(d, A, (long long)nb * rows_pb, nb * rows_pb, 1, bw.lin1, e1, s, VV_K_FFN1, i);
       if (rc != VV_OK) return rc;
       EpiOut e2;
       e2.epi = EPI_RESID; e2.gamma = bw.ffn_gamma; e2.resid = Y; e2.out_f32 = X;
-      const bool feeds_up = (j == nblk - 1) && (i + 1 < S);
       if (feeds_up) {
         e2.out_bf16 = XB; e2.bf16_halo = 1;
         rc = launch_gemm(d, H, rows_pb, rows_pb, nb, bw.lin2, e2, s, VV_K_FFN2, i);
@@ -887,6 +940,9 @@ extern "C" int32_t vv_kernel_ffn(vv_decoder* d, int32_t stage, int32_t block, co
   cudaStream_t s = reinterpret_cast<cudaStream_t>(cuda_stream);
   const BlockW& bw = d->stages[stage].blocks[block];
   const long long R = (long long)B * rows;
+  if (ffn_fused_supported(d, d->stages[stage].C))
+    return launch_ffn_fused(d, d->stages[stage].C, bw, reinterpret_cast<const __nv_bfloat16*>(a), resid, out, nullptr, R,
+                            rows, s);
   EpiOut e1;
   e1.epi = EPI_GELU_BF16; e1.out_bf16 = reinterpret_cast<__nv_bfloat16*>(hidden);
   rc = launch_gemm(d, reinterpret_cast<const __nv_bfloat16*>(a), R, (int)R, 1, bw.lin1, e1, s);

@@ -37,7 +37,7 @@ class VvProfileRecord(C.Structure):
     _fields_ = [("kind", C.c_int32), ("stage", C.c_int32), ("launches", C.c_int64), ("ms", C.c_double)]
 
 
-KERNEL_KINDS = ("prep", "stem", "mixer", "ffn1", "ffn2", "halo", "upsample", "head", "state")
+KERNEL_KINDS = ("prep", "stem", "mixer", "ffn1", "ffn2", "halo", "upsample", "head", "state", "ffn_fused")
 
 # name -> (restype, argtypes): every symbol include/vvdec.h declares
 _P, _I32, _I64 = C.c_void_p, C.c_int32, C.c_int64
