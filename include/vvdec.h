@@ -68,7 +68,8 @@ typedef struct vv_config {
   int32_t device;                     /* CUDA device ordinal                                    */
   int32_t gemm_path;                  /* 0 = product path (fused tcgen05 FFN at C<=64, tcgen05 GEMMs
                                          elsewhere); 1 = CUDA-core validation GEMM everywhere;
-                                         2 = unfused tcgen05 GEMMs everywhere (A/B against 0)   */
+                                         2 = unfused tcgen05 GEMMs everywhere (A/B against 0);
+                                         3 = as 2 but only the non-persistent GEMM kernel       */
 } vv_config;
 
 typedef struct vv_decoder vv_decoder; /* opaque: packed weights + launch plan                    */

@@ -32,7 +32,7 @@ def _decoder_for(meta, weight_cache, **kw):
     return dec, geom
 
 
-@pytest.mark.parametrize("gemm_path", [1, 2, 0])
+@pytest.mark.parametrize("gemm_path", [1, 3, 2, 0])
 def test_offline_stress_T6_matches_reference(weight_cache, gemm_path):
     """gemm_path=1 (CUDA-core validation GEMM) isolates every non-tensor-core kernel, 2 = unfused tcgen05 GEMMs,
     0 = the product path (fused FFN kernel at C <= 64)."""

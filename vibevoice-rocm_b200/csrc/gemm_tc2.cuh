@@ -1,0 +1,276 @@
+// gemm_tc2.cuh — persistent version of the tap GEMM (gemm_tc.cuh) for the 128 x 128 x 64 tile, i.e. every
+// hot dense layer with C >= 128: FFN linear1/linear2, the polyphase transposed convs, the stem.
+//
+// What changed against gemm_tc_kernel, and why (ncu on the first round-1 build, profiles/):
+//   * row-per-thread global loads/stores in the epilogue cost one L1TEX tag cycle per ROW per instruction;
+//     L1TEX was the busiest unit.  Now the epilogue works on a shared-memory staging tile in the
+//     128B-swizzled layout TMA uses: the residual tile is TMA-LOADED into it, the epilogue updates it in
+//     place (thread = row, conflict-free in 4 wavefronts), and a dedicated warp TMA-STORES it.
+//   * one CTA per SM loops over tiles (N fastest, so CTAs running together share the A tile in L2);
+//     two TMEM accumulators and two staging slots let tile i's epilogue overlap tile i+1's TMA + MMA.
+//   * 8 epilogue warps (two per TMEM lane quarter, splitting the columns) instead of 4.
+// Roles: warp 0 TMA loads (A/B ring + residual tile), warp 1 MMA issue + TMEM owner, warps 2..9 epilogue,
+// warp 10 TMA stores.
+#pragma once
+#include <cuda.h>
+#include "ptx.cuh"
+#include "epilogue.cuh"
+#include "gemm_tc.cuh"
+
+namespace vv {
+
+constexpr int G2_THREADS = 352;
+constexpr int G2_EPI_WARPS = 8;
+constexpr int G2_BN = 128, G2_BK = 64;
+constexpr int G2_A_BYTES = GEMM_BM * G2_BK * 2;   // 16 KB
+constexpr int G2_B_BYTES = G2_BN * G2_BK * 2;     // 16 KB
+constexpr int G2_BOX_BYTES = 128 * 128;           // one staged box: 128 rows x 128 bytes
+
+template <int EPI>
+struct Gemm2Cfg {
+  static constexpr bool OUT_BF16 = (EPI == EPI_GELU_BF16);
+  static constexpr int COLS_PER_BOX = OUT_BF16 ? 64 : 32;
+  static constexpr int BOXES = G2_BN / COLS_PER_BOX;                 // 2 or 4
+  static constexpr int STG_BYTES = BOXES * G2_BOX_BYTES;             // 32 KB or 64 KB
+  static constexpr int NSTG = 2;
+  static constexpr int STAGES = OUT_BF16 ? 5 : 3;                    // A/B ring depth
+  static constexpr int OFF_RING = 0;
+  static constexpr int OFF_STG = STAGES * (G2_A_BYTES + G2_B_BYTES);
+  static constexpr int OFF_BAR = OFF_STG + NSTG * STG_BYTES;
+  static constexpr int TOTAL = OFF_BAR + 512 + 1024;
+  static_assert(TOTAL <= 232448, "shared memory budget");
+};
+
+struct Gemm2Args {
+  GemmArgs g;          // shapes, bias / gamma, optional haloed bf16 copy (out_bf16, ob_rpb, ob_off) for EPI_RESID
+};
+
+template <int EPI>
+__global__ void __launch_bounds__(G2_THREADS, 1)
+gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                const __grid_constant__ CUtensorMap tmR, const __grid_constant__ CUtensorMap tmO,
+                const GemmArgs g) {
+  using Cfg = Gemm2Cfg<EPI>;
+  constexpr int S = Cfg::STAGES;
+  constexpr int NSTG = Cfg::NSTG;
+  constexpr int BN = G2_BN, BK = G2_BK;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  uint8_t* sA = smem + Cfg::OFF_RING;
+  uint8_t* sB = sA + S * G2_A_BYTES;
+  uint8_t* sStg = smem + Cfg::OFF_STG;
+  uint64_t* bars = (uint64_t*)(smem + Cfg::OFF_BAR);
+  uint64_t* full = bars;                   // [S]
+  uint64_t* empty = full + S;              // [S]
+  uint64_t* acc_full = empty + S;          // [2]
+  uint64_t* acc_empty = acc_full + 2;      // [2]
+  uint64_t* stg_full = acc_empty + 2;      // [NSTG] residual tile landed (EPI_RESID)
+  uint64_t* stg_ready = stg_full + NSTG;   // [NSTG] epilogue finished writing the staged output
+  uint64_t* stg_empty = stg_ready + NSTG;  // [NSTG] TMA store has read the slot
+  uint32_t* tmem_slot = (uint32_t*)(stg_empty + NSTG);
+  static_assert((2 * S + 4 + 3 * NSTG + 1) * 8 <= 512, "barrier block");
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int bt = 1 << g.bt_log2;
+  const int bb = GEMM_BM >> g.bt_log2;
+  const int tiles_t = (g.rows + bt - 1) >> g.bt_log2;
+  const int tiles_b = (g.nbatch + bb - 1) / bb;
+  const int tiles_n = g.N / BN;
+  const long long ntiles = (long long)tiles_t * tiles_b * tiles_n;
+  const long long my_tiles = (ntiles > blockIdx.x) ? (ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+  const int nk = g.n_taps * g.kb_per_tap;
+
+  if (threadIdx.x == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+    tma_prefetch_desc(&tmO);
+    if (EPI == EPI_RESID) tma_prefetch_desc(&tmR);
+    for (int s = 0; s < S; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], G2_EPI_WARPS); }
+    for (int i = 0; i < NSTG; ++i) {
+      mbar_init(&stg_full[i], 1);
+      mbar_init(&stg_ready[i], G2_EPI_WARPS);
+      mbar_init(&stg_empty[i], 1);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 1) {
+    tmem_alloc(tmem_slot, 2 * BN);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  // tile index -> (n, t, b) coordinates
+  auto tile_coords = [&](long long it, int& tile_n, int& tile_t, int& tile_b) {
+    const long long tile = blockIdx.x + it * gridDim.x;
+    tile_n = (int)(tile % tiles_n);
+    const long long tm = tile / tiles_n;
+    tile_t = (int)(tm % tiles_t);
+    tile_b = (int)(tm / tiles_t);
+  };
+
+  if (warp == 0) {
+    // ===== TMA loads ===============================================================================
+    if (elect_one()) {
+      long long kbg = 0;                                  // global k-block counter (ring position)
+      for (long long it = 0; it < my_tiles; ++it) {
+        int tile_n, tile_t, tile_b;
+        tile_coords(it, tile_n, tile_t, tile_b);
+        if (EPI == EPI_RESID) {                           // residual tile -> staging slot
+          const int ss = (int)(it % NSTG);
+          mbar_wait(&stg_empty[ss], (uint32_t)(((it / NSTG) & 1) ^ 1));
+          mbar_expect_tx(&stg_full[ss], Cfg::STG_BYTES);
+#pragma unroll
+          for (int c = 0; c < Cfg::BOXES; ++c)
+            tma_load_3d(sStg + ss * Cfg::STG_BYTES + c * G2_BOX_BYTES, &tmR, &stg_full[ss],
+                        tile_n * BN + c * Cfg::COLS_PER_BOX, tile_t * bt, tile_b * bb);
+        }
+        for (int kb = 0; kb < nk; ++kb, ++kbg) {
+          const int s = (int)(kbg % S);
+          mbar_wait(&empty[s], (uint32_t)(((kbg / S) & 1) ^ 1));
+          const int tap = kb / g.kb_per_tap;
+          const int kin = (kb - tap * g.kb_per_tap) * BK;
+          mbar_expect_tx(&full[s], G2_A_BYTES + G2_B_BYTES);
+          tma_load_3d(sA + s * G2_A_BYTES, &tmA, &full[s], kin, tile_t * bt + tap, tile_b * bb);
+          tma_load_2d(sB + s * G2_B_BYTES, &tmB, &full[s], kb * BK, tile_n * BN);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer ================================================================================
+    if (elect_one()) {
+      constexpr uint32_t idesc = umma_idesc_bf16(GEMM_BM, BN);
+      long long kbg = 0;
+      for (long long it = 0; it < my_tiles; ++it) {
+        const int ab = (int)(it & 1);
+        mbar_wait(&acc_empty[ab], (uint32_t)(((it >> 1) & 1) ^ 1));
+        tc_fence_after();
+        for (int kb = 0; kb < nk; ++kb, ++kbg) {
+          const int s = (int)(kbg % S);
+          mbar_wait(&full[s], (uint32_t)((kbg / S) & 1));
+          tc_fence_after();
+          const uint64_t da = umma_smem_desc<128>(smem_u32(sA + s * G2_A_BYTES));
+          const uint64_t db = umma_smem_desc<128>(smem_u32(sB + s * G2_B_BYTES));
+#pragma unroll
+          for (int kk = 0; kk < BK / 16; ++kk)
+            umma_bf16(tmem_base + (uint32_t)(ab * BN), da + (uint64_t)(kk * 2), db + (uint64_t)(kk * 2), idesc,
+                      (kb | kk) != 0);
+          umma_commit(&empty[s]);
+        }
+        umma_commit(&acc_full[ab]);
+      }
+    }
+  } else if (warp < 2 + G2_EPI_WARPS) {
+    // ===== epilogue: TMEM -> (bias | GELU | layer-scale + residual) -> staged tile in shared memory ==========
+    const int q = warp & 3;
+    const int colhalf = (warp - 2) >> 2;                  // columns [colhalf*64, +64) of the tile
+    const int r = q * 32 + lane;
+    for (long long it = 0; it < my_tiles; ++it) {
+      int tile_n, tile_t, tile_b;
+      tile_coords(it, tile_n, tile_t, tile_b);
+      const int ab = (int)(it & 1), ss = (int)(it % NSTG);
+      const int n0 = tile_n * BN + colhalf * 64;
+      mbar_wait(&acc_full[ab], (uint32_t)((it >> 1) & 1));
+      if (EPI == EPI_RESID) mbar_wait(&stg_full[ss], (uint32_t)((it / NSTG) & 1));
+      else mbar_wait(&stg_empty[ss], (uint32_t)(((it / NSTG) & 1) ^ 1));
+      tc_fence_after();
+      uint8_t* stg = sStg + ss * Cfg::STG_BYTES + r * 128;
+#pragma unroll
+      for (int c = 0; c < 2; ++c) {                       // two 32-column groups
+        uint32_t v[32];
+        tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(ab * BN + colhalf * 64 + c * 32), v);
+        tmem_ld_wait();
+        const int n = n0 + c * 32;                        // global column of v[0]
+        const int nl = colhalf * 64 + c * 32;             // column inside the tile
+        if (EPI == EPI_GELU_BF16) {
+          uint8_t* box = stg + (nl >> 6) * G2_BOX_BYTES;  // 64 bf16 columns per box
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const float4 b0 = __ldg(reinterpret_cast<const float4*>(g.bias + n + i * 8));
+            const float4 b1 = __ldg(reinterpret_cast<const float4*>(g.bias + n + i * 8 + 4));
+            uint4 pk;
+            pk.x = gelu2_bias_pack(__uint_as_float(v[i * 8 + 0]), __uint_as_float(v[i * 8 + 1]), b0.x, b0.y);
+            pk.y = gelu2_bias_pack(__uint_as_float(v[i * 8 + 2]), __uint_as_float(v[i * 8 + 3]), b0.z, b0.w);
+            pk.z = gelu2_bias_pack(__uint_as_float(v[i * 8 + 4]), __uint_as_float(v[i * 8 + 5]), b1.x, b1.y);
+            pk.w = gelu2_bias_pack(__uint_as_float(v[i * 8 + 6]), __uint_as_float(v[i * 8 + 7]), b1.z, b1.w);
+            const int chunk = (((nl & 63) >> 3) + i) ^ (r & 7);
+            *reinterpret_cast<uint4*>(box + chunk * 16) = pk;
+          }
+        } else {
+          uint8_t* box = stg + (nl >> 5) * G2_BOX_BYTES;  // 32 fp32 columns per box
+          float x[32];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const float4 bv = __ldg(reinterpret_cast<const float4*>(g.bias + n + i * 4));
+            float4* cell = reinterpret_cast<float4*>(box + ((i ^ (r & 7)) * 16));
+            float4 o;
+            o.x = __uint_as_float(v[i * 4 + 0]) + bv.x;
+            o.y = __uint_as_float(v[i * 4 + 1]) + bv.y;
+            o.z = __uint_as_float(v[i * 4 + 2]) + bv.z;
+            o.w = __uint_as_float(v[i * 4 + 3]) + bv.w;
+            if (EPI == EPI_RESID) {
+              const float4 gv = __ldg(reinterpret_cast<const float4*>(g.gamma + n + i * 4));
+              const float4 rv = *cell;
+              o.x = fmaf(gv.x, o.x, rv.x);
+              o.y = fmaf(gv.y, o.y, rv.y);
+              o.z = fmaf(gv.z, o.z, rv.z);
+              o.w = fmaf(gv.w, o.w, rv.w);
+            }
+            *cell = o;
+            x[i * 4 + 0] = o.x; x[i * 4 + 1] = o.y; x[i * 4 + 2] = o.z; x[i * 4 + 3] = o.w;
+          }
+          if (EPI == EPI_RESID && g.out_bf16 != nullptr) {  // haloed bf16 copy for the upsampler (last block only)
+            const int b = tile_b * bb + (r >> g.bt_log2);
+            const int t = tile_t * bt + (r & (bt - 1));
+            if (b < g.nbatch && t < g.rows) {
+              __nv_bfloat16* op = g.out_bf16 + ((long long)b * g.ob_rpb + g.ob_off + t) * g.N + n;
+#pragma unroll
+              for (int i = 0; i < 4; ++i) {
+                uint4 pk;
+                pk.x = pack_bf16x2(x[i * 8 + 0], x[i * 8 + 1]);
+                pk.y = pack_bf16x2(x[i * 8 + 2], x[i * 8 + 3]);
+                pk.z = pack_bf16x2(x[i * 8 + 4], x[i * 8 + 5]);
+                pk.w = pack_bf16x2(x[i * 8 + 6], x[i * 8 + 7]);
+                *reinterpret_cast<uint4*>(op + i * 8) = pk;
+              }
+            }
+          }
+        }
+      }
+      tc_fence_before();
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) {
+        mbar_arrive(&acc_empty[ab]);
+        mbar_arrive(&stg_ready[ss]);
+      }
+    }
+  } else {
+    // ===== TMA stores ================================================================================
+    if (elect_one()) {
+      for (long long it = 0; it < my_tiles; ++it) {
+        int tile_n, tile_t, tile_b;
+        tile_coords(it, tile_n, tile_t, tile_b);
+        const int ss = (int)(it % NSTG);
+        mbar_wait(&stg_ready[ss], (uint32_t)((it / NSTG) & 1));
+#pragma unroll
+        for (int c = 0; c < Cfg::BOXES; ++c)
+          tma_store_3d(&tmO, sStg + ss * Cfg::STG_BYTES + c * G2_BOX_BYTES, tile_n * BN + c * Cfg::COLS_PER_BOX,
+                       tile_t * bt, tile_b * bb);
+        tma_store_commit();
+        tma_store_wait_read<0>();
+        mbar_arrive(&stg_empty[ss]);
+      }
+      tma_store_wait_all<0>();
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, 2 * BN);
+}
+
+}  // namespace vv

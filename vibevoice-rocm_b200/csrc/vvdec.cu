@@ -10,6 +10,7 @@
 #include "vvdec_internal.h"
 #include "rowops.cuh"
 #include "ffn_fused.cuh"
+#include "gemm_tc2.cuh"
 
 namespace vv {
 
@@ -498,6 +499,45 @@ int launch_gemm_impl(vv_decoder* d, const __nv_bfloat16* A, long long a_rpb, int
   const uint32_t box[3] = {(uint32_t)w.BK, 1u << best_log2, 128u >> best_log2};
   int rc = encode_map(&tmA, A, 3, dims, strides, box);
   if (rc != VV_OK) return rc;
+  if (w.BN == G2_BN && w.BK == G2_BK && d->cfg.gemm_path != 3) {
+    // persistent kernel with TMA-staged epilogue (gemm_tc2.cuh)
+    CUtensorMap tmR, tmO;
+    const uint32_t bt = 1u << best_log2, bb = 128u >> best_log2;
+    const uint64_t odims[3] = {(uint64_t)w.N, (uint64_t)rows, (uint64_t)nbatch};
+    if (e.epi == EPI_GELU_BF16) {
+      const uint64_t ostr[2] = {(uint64_t)w.N * 2, (uint64_t)rows * w.N * 2};
+      const uint32_t obox[3] = {64u, bt, bb};
+      rc = encode_map(&tmO, e.out_bf16, 3, odims, ostr, obox, false);
+      tmR = tmO;
+    } else {
+      const uint64_t ostr[2] = {(uint64_t)w.N * 4, (uint64_t)rows * w.N * 4};
+      const uint32_t obox[3] = {32u, bt, bb};
+      rc = encode_map(&tmO, e.out_f32, 3, odims, ostr, obox, true);
+      if (rc == VV_OK && e.epi == EPI_RESID) rc = encode_map(&tmR, e.resid, 3, odims, ostr, obox, true);
+      else tmR = tmO;
+    }
+    if (rc != VV_OK) return rc;
+    static int num_sms = 0;
+    if (num_sms == 0) VV_CUDA(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, d->cfg.device));
+    const long long ntiles = best_tiles * (w.N / w.BN);
+    const unsigned grid2 = (unsigned)std::min<long long>(ntiles, num_sms);
+    static bool attr_set[3] = {false, false, false};
+#define VV_G2_LAUNCH(E)                                                                                     \
+    do {                                                                                                      \
+      if (!attr_set[E]) {                                                                                     \
+        VV_CUDA(cudaFuncSetAttribute(gemm_tc2_kernel<E>, cudaFuncAttributeMaxDynamicSharedMemorySize,         \
+                                     (int)Gemm2Cfg<E>::TOTAL));                                               \
+        attr_set[E] = true;                                                                                   \
+      }                                                                                                       \
+      gemm_tc2_kernel<E><<<grid2, G2_THREADS, Gemm2Cfg<E>::TOTAL, s>>>(tmA, w.tm, tmR, tmO, g);               \
+    } while (0)
+    if (e.epi == EPI_BIAS_F32) VV_G2_LAUNCH(EPI_BIAS_F32);
+    else if (e.epi == EPI_GELU_BF16) VV_G2_LAUNCH(EPI_GELU_BF16);
+    else VV_G2_LAUNCH(EPI_RESID);
+#undef VV_G2_LAUNCH
+    VV_CUDA(cudaGetLastError());
+    return VV_OK;
+  }
   const long long n_cta = best_tiles * (w.N / w.BN);
   if (n_cta > 0x7fffffffLL) { set_error("internal: %lld tiles exceed the launch limit", n_cta); return VV_ERR_WORKSPACE; }
   dim3 grid((unsigned)n_cta);
