@@ -26,14 +26,16 @@ constexpr int G2_A_BYTES = GEMM_BM * G2_BK * 2;   // 16 KB
 constexpr int G2_B_BYTES = G2_BN * G2_BK * 2;     // 16 KB
 constexpr int G2_BOX_BYTES = 128 * 128;           // one staged box: 128 rows x 128 bytes
 
-template <int EPI>
+// DEEP = long K loop (>= 32 k-blocks): the mainloop dominates, so shared memory goes to a deeper A/B ring
+// and the epilogue staging is single-buffered; otherwise the epilogue dominates and staging is double-buffered.
+template <int EPI, bool DEEP>
 struct Gemm2Cfg {
   static constexpr bool OUT_BF16 = (EPI == EPI_GELU_BF16);
   static constexpr int COLS_PER_BOX = OUT_BF16 ? 64 : 32;
   static constexpr int BOXES = G2_BN / COLS_PER_BOX;                 // 2 or 4
   static constexpr int STG_BYTES = BOXES * G2_BOX_BYTES;             // 32 KB or 64 KB
-  static constexpr int NSTG = 2;
-  static constexpr int STAGES = OUT_BF16 ? 5 : 3;                    // A/B ring depth
+  static constexpr int NSTG = DEEP ? 1 : 2;
+  static constexpr int STAGES = DEEP ? (OUT_BF16 ? 6 : 5) : (OUT_BF16 ? 5 : 3);   // A/B ring depth
   static constexpr int OFF_RING = 0;
   static constexpr int OFF_STG = STAGES * (G2_A_BYTES + G2_B_BYTES);
   static constexpr int OFF_BAR = OFF_STG + NSTG * STG_BYTES;
@@ -45,12 +47,12 @@ struct Gemm2Args {
   GemmArgs g;          // shapes, bias / gamma, optional haloed bf16 copy (out_bf16, ob_rpb, ob_off) for EPI_RESID
 };
 
-template <int EPI>
+template <int EPI, bool DEEP>
 __global__ void __launch_bounds__(G2_THREADS, 1)
 gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                 const __grid_constant__ CUtensorMap tmR, const __grid_constant__ CUtensorMap tmO,
                 const GemmArgs g) {
-  using Cfg = Gemm2Cfg<EPI>;
+  using Cfg = Gemm2Cfg<EPI, DEEP>;
   constexpr int S = Cfg::STAGES;
   constexpr int NSTG = Cfg::NSTG;
   constexpr int BN = G2_BN, BK = G2_BK;

@@ -521,19 +521,20 @@ int launch_gemm_impl(vv_decoder* d, const __nv_bfloat16* A, long long a_rpb, int
     if (num_sms == 0) VV_CUDA(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, d->cfg.device));
     const long long ntiles = best_tiles * (w.N / w.BN);
     const unsigned grid2 = (unsigned)std::min<long long>(ntiles, num_sms);
-    static bool attr_set[3] = {false, false, false};
-#define VV_G2_LAUNCH(E)                                                                                     \
+    static bool attr_set[3][2] = {{false, false}, {false, false}, {false, false}};
+    const bool deep = nk >= 32;   // K >= 2048: mainloop-dominated
+#define VV_G2_LAUNCH(E, D)                                                                                  \
     do {                                                                                                      \
-      if (!attr_set[E]) {                                                                                     \
-        VV_CUDA(cudaFuncSetAttribute(gemm_tc2_kernel<E>, cudaFuncAttributeMaxDynamicSharedMemorySize,         \
-                                     (int)Gemm2Cfg<E>::TOTAL));                                               \
-        attr_set[E] = true;                                                                                   \
+      if (!attr_set[E][D]) {                                                                                  \
+        VV_CUDA(cudaFuncSetAttribute(gemm_tc2_kernel<E, D>, cudaFuncAttributeMaxDynamicSharedMemorySize,      \
+                                     (int)Gemm2Cfg<E, D>::TOTAL));                                            \
+        attr_set[E][D] = true;                                                                                \
       }                                                                                                       \
-      gemm_tc2_kernel<E><<<grid2, G2_THREADS, Gemm2Cfg<E>::TOTAL, s>>>(tmA, w.tm, tmR, tmO, g);               \
+      gemm_tc2_kernel<E, D><<<grid2, G2_THREADS, Gemm2Cfg<E, D>::TOTAL, s>>>(tmA, w.tm, tmR, tmO, g);         \
     } while (0)
-    if (e.epi == EPI_BIAS_F32) VV_G2_LAUNCH(EPI_BIAS_F32);
-    else if (e.epi == EPI_GELU_BF16) VV_G2_LAUNCH(EPI_GELU_BF16);
-    else VV_G2_LAUNCH(EPI_RESID);
+    if (e.epi == EPI_BIAS_F32) { if (deep) VV_G2_LAUNCH(EPI_BIAS_F32, true); else VV_G2_LAUNCH(EPI_BIAS_F32, false); }
+    else if (e.epi == EPI_GELU_BF16) { if (deep) VV_G2_LAUNCH(EPI_GELU_BF16, true); else VV_G2_LAUNCH(EPI_GELU_BF16, false); }
+    else { if (deep) VV_G2_LAUNCH(EPI_RESID, true); else VV_G2_LAUNCH(EPI_RESID, false); }
 #undef VV_G2_LAUNCH
     VV_CUDA(cudaGetLastError());
     return VV_OK;
