@@ -19,8 +19,12 @@
 
 namespace vv {
 
-constexpr int G2_THREADS = 352;
-constexpr int G2_EPI_WARPS = 8;
+// epilogue warps: 8 (two per TMEM lane quarter, 64 columns each) — or 16 (32 columns each) for the GELU epilogue,
+// which is issue-bound and needs more warps in flight to fill the issue slots (measured on the fused FFN: IPC 1.9 -> 2.2+)
+template <int EPI> struct G2Warps {
+  static constexpr int EPI_WARPS = (EPI == EPI_GELU_BF16) ? 16 : 8;
+  static constexpr int THREADS = (2 + EPI_WARPS + 1) * 32;
+};
 constexpr int G2_BN = 128, G2_BK = 64;
 constexpr int G2_A_BYTES = GEMM_BM * G2_BK * 2;   // 16 KB
 constexpr int G2_B_BYTES = G2_BN * G2_BK * 2;     // 16 KB
@@ -48,7 +52,7 @@ struct Gemm2Args {
 };
 
 template <int EPI, bool DEEP>
-__global__ void __launch_bounds__(G2_THREADS, 1)
+__global__ void __launch_bounds__(G2Warps<EPI>::THREADS, 1)
 gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                 const __grid_constant__ CUtensorMap tmR, const __grid_constant__ CUtensorMap tmO,
                 const GemmArgs g) {
@@ -56,6 +60,8 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   constexpr int S = Cfg::STAGES;
   constexpr int NSTG = Cfg::NSTG;
   constexpr int BN = G2_BN, BK = G2_BK;
+  constexpr int EW = G2Warps<EPI>::EPI_WARPS;
+  constexpr int CPW = BN / (EW / 4);        // columns per epilogue warp: 64 or 32
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   uint8_t* sA = smem + Cfg::OFF_RING;
@@ -89,10 +95,10 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     tma_prefetch_desc(&tmO);
     if (EPI == EPI_RESID) tma_prefetch_desc(&tmR);
     for (int s = 0; s < S; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], G2_EPI_WARPS); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], EW); }
     for (int i = 0; i < NSTG; ++i) {
       mbar_init(&stg_full[i], 1);
-      mbar_init(&stg_ready[i], G2_EPI_WARPS);
+      mbar_init(&stg_ready[i], EW);
       mbar_init(&stg_empty[i], 1);
     }
     fence_mbar_init();
@@ -166,28 +172,28 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         umma_commit(&acc_full[ab]);
       }
     }
-  } else if (warp < 2 + G2_EPI_WARPS) {
+  } else if (warp < 2 + EW) {
     // ===== epilogue: TMEM -> (bias | GELU | layer-scale + residual) -> staged tile in shared memory ==========
     const int q = warp & 3;
-    const int colhalf = (warp - 2) >> 2;                  // columns [colhalf*64, +64) of the tile
+    const int colgrp = (warp - 2) >> 2;                   // columns [colgrp*CPW, +CPW) of the tile
     const int r = q * 32 + lane;
     for (long long it = 0; it < my_tiles; ++it) {
       int tile_n, tile_t, tile_b;
       tile_coords(it, tile_n, tile_t, tile_b);
       const int ab = (int)(it & 1), ss = (int)(it % NSTG);
-      const int n0 = tile_n * BN + colhalf * 64;
+      const int n0 = tile_n * BN + colgrp * CPW;
       mbar_wait(&acc_full[ab], (uint32_t)((it >> 1) & 1));
       if (EPI == EPI_RESID) mbar_wait(&stg_full[ss], (uint32_t)((it / NSTG) & 1));
       else mbar_wait(&stg_empty[ss], (uint32_t)(((it / NSTG) & 1) ^ 1));
       tc_fence_after();
       uint8_t* stg = sStg + ss * Cfg::STG_BYTES + r * 128;
 #pragma unroll
-      for (int c = 0; c < 2; ++c) {                       // two 32-column groups
+      for (int c = 0; c < CPW / 32; ++c) {                // 32-column groups
         uint32_t v[32];
-        tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(ab * BN + colhalf * 64 + c * 32), v);
+        tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(ab * BN + colgrp * CPW + c * 32), v);
         tmem_ld_wait();
         const int n = n0 + c * 32;                        // global column of v[0]
-        const int nl = colhalf * 64 + c * 32;             // column inside the tile
+        const int nl = colgrp * CPW + c * 32;             // column inside the tile
         if (EPI == EPI_GELU_BF16) {
           uint8_t* box = stg + (nl >> 6) * G2_BOX_BYTES;  // 64 bf16 columns per box
 #pragma unroll

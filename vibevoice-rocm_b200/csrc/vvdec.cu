@@ -530,7 +530,7 @@ int launch_gemm_impl(vv_decoder* d, const __nv_bfloat16* A, long long a_rpb, int
                                      (int)Gemm2Cfg<E, D>::TOTAL));                                            \
         attr_set[E][D] = true;                                                                                \
       }                                                                                                       \
-      gemm_tc2_kernel<E, D><<<grid2, G2_THREADS, Gemm2Cfg<E, D>::TOTAL, s>>>(tmA, w.tm, tmR, tmO, g);         \
+      gemm_tc2_kernel<E, D><<<grid2, G2Warps<E>::THREADS, Gemm2Cfg<E, D>::TOTAL, s>>>(tmA, w.tm, tmR, tmO, g);         \
     } while (0)
     if (e.epi == EPI_BIAS_F32) { if (deep) VV_G2_LAUNCH(EPI_BIAS_F32, true); else VV_G2_LAUNCH(EPI_BIAS_F32, false); }
     else if (e.epi == EPI_GELU_BF16) { if (deep) VV_G2_LAUNCH(EPI_GELU_BF16, true); else VV_G2_LAUNCH(EPI_GELU_BF16, false); }
