@@ -85,8 +85,11 @@ __device__ __forceinline__ void reduce7(float (&s)[7], float* xchg, int buf) {
   }
 }
 
+#ifndef VV_MIXER_MINBLOCKS
+#define VV_MIXER_MINBLOCKS 4
+#endif
 template <int LPR>
-__global__ void __launch_bounds__((LPR <= 32) ? 128 : LPR)
+__global__ void __launch_bounds__((LPR <= 32) ? 128 : LPR, (LPR <= 32) ? VV_MIXER_MINBLOCKS : 1)
 mixer_kernel(const MixerArgs p) {
   __shared__ float xchg[(LPR <= 32) ? 1 : 4 * (LPR / 32) * 8];
   int group, lane_in_group;

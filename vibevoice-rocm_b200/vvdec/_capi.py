@@ -10,7 +10,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libvvdec_b200.so")
+LIB_PATH = os.environ.get("VVDEC_LIB", os.path.join(_HERE, "libvvdec_b200.so"))   # override: A/B builds only
 
 VV_MAX_STAGES = 8
 VV_F32, VV_BF16 = 0, 1
