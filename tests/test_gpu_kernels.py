@@ -55,7 +55,7 @@ def test_mixer_half(full_decoder, stage, B, rows):
 
 
 @pytest.mark.parametrize("stage,B,rows", [(6, 2, 300), (5, 1, 129), (4, 2, 200), (3, 1, 130), (2, 1, 70), (1, 1, 20),
-                                          (0, 1, 7), (6, 1, 1)])
+                                          (0, 1, 7), (6, 1, 1), (4, 1, 1), (4, 3, 19001), (5, 2, 40001), (6, 1, 90001)])
 def test_ffn_half(full_decoder, stage, B, rows):
     dec, w = full_decoder
     Cc = FULL.stage_channels(stage)
@@ -123,4 +123,5 @@ def test_gelu_epilogue_accuracy(full_decoder):
     ref = 0.5 * x.astype(np.float64) * (1 + erf(x.astype(np.float64) / np.sqrt(2)))
     err = np.abs(y.cpu().numpy().astype(np.float64) - ref)
     print("gelu max abs err", err.max(), "max err/|x|", (err / np.maximum(np.abs(x), 1e-3)).max())
-    assert (err <= 3e-4 * np.maximum(np.abs(x), 1.0)).all()
+    # fitted tanh argument (2.7e-4 abs) + tanh.approx (2^-11 relative on tanh => 2.4e-4 |x|)
+    assert (err <= 6e-4 * np.maximum(np.abs(x), 1.0)).all()

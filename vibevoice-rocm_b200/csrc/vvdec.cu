@@ -10,6 +10,7 @@
 #include "vvdec_internal.h"
 #include "rowops.cuh"
 #include "ffn_fused.cuh"
+#include "ffn_stream.cuh"
 #include "gemm_tc2.cuh"
 
 namespace vv {
@@ -386,8 +387,19 @@ extern "C" int32_t vv_decoder_finalize(vv_decoder* d) {
       bw.ffn_norm_w = pk.upload(*fnw);
       bw.dw_w = pk.upload(dwt);
       bw.dw_b = pk.upload(*db);
-      pk.dense(bw.lin1, to_bf16(*w1), *b1, 4 * C, C, 1);
+      {  // linear1 is packed PRE-SCALED by 0.5 (exact): every GELU epilogue works on z = x/2 (epilogue.cuh)
+        std::vector<float> w1h(*w1), b1h(*b1);
+        for (float& v : w1h) v *= 0.5f;
+        for (float& v : b1h) v *= 0.5f;
+        pk.dense(bw.lin1, to_bf16(w1h), b1h, 4 * C, C, 1);
+      }
       pk.dense(bw.lin2, to_bf16(*w2), *b2, C, 4 * C, 1);
+      if (pk.status == VV_OK && C == 128) {   // ffn_stream_kernel reads linear1 in chunks of 64 hidden units
+        const uint64_t dims[2] = {(uint64_t)C, (uint64_t)(4 * C)};
+        const uint64_t strides[1] = {(uint64_t)C * 2};
+        const uint32_t box[2] = {64u, 64u};
+        pk.status = encode_map(&bw.tm_w1s, bw.lin1.w, 2, dims, strides, box);
+      }
       bw.state_off = soff;
       soff += 6LL * C * 4;
       st.blocks.push_back(bw);
@@ -573,7 +585,9 @@ int launch_ffn_fused_inst(vv_decoder* d, const CUtensorMap& tmA, const CUtensorM
   return VV_OK;
 }
 
-bool ffn_fused_supported(const vv_decoder* d, int C) { return d->cfg.gemm_path == 0 && (C == 32 || C == 64); }
+bool ffn_fused_supported(const vv_decoder* d, int C) {
+  return d->cfg.gemm_path == 0 && (C == 32 || C == 64 || C == 128);
+}
 
 int launch_ffn_fused(vv_decoder* d, int C, const BlockW& bw, const __nv_bfloat16* a, const float* resid, float* out,
                      __nv_bfloat16* out_bf16, long long R, int rows_pb, cudaStream_t s) {
@@ -583,7 +597,7 @@ int launch_ffn_fused(vv_decoder* d, int C, const BlockW& bw, const __nv_bfloat16
   CUtensorMap tmA;
   const uint64_t dims[2] = {(uint64_t)C, (uint64_t)R};
   const uint64_t strides[1] = {(uint64_t)C * 2};
-  const uint32_t box[2] = {(uint32_t)C, 128u};
+  const uint32_t box[2] = {(uint32_t)std::min(C, 64), 128u};   // C = 128: [128 rows x 64] K blocks (ffn_stream.cuh)
   int rc = encode_map(&tmA, a, 2, dims, strides, box);
   if (rc != VV_OK) return rc;
   CUtensorMap tmR;                                   // residual, fp32 [R, C], boxes of [128 rows, 32 floats]
@@ -596,7 +610,21 @@ int launch_ffn_fused(vv_decoder* d, int C, const BlockW& bw, const __nv_bfloat16
   if (rc != VV_OK) return rc;
   d->launches++;
   if (C == 32) return launch_ffn_fused_inst<32>(d, tmA, tmR, tmO, bw, fa, s);
-  return launch_ffn_fused_inst<64>(d, tmA, tmR, tmO, bw, fa, s);
+  if (C == 64) return launch_ffn_fused_inst<64>(d, tmA, tmR, tmO, bw, fa, s);
+  // C = 128: hidden on chip, weights streamed (ffn_stream.cuh); a is read in [128 rows x 64] K blocks
+  static bool attr_set = false;
+  if (!attr_set) {
+    VV_CUDA(cudaFuncSetAttribute(ffn_stream_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)FfnStreamCfg<128>::TOTAL));
+    attr_set = true;
+  }
+  static int num_sms = 0;
+  if (num_sms == 0) VV_CUDA(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, d->cfg.device));
+  const long long ntiles = (R + 127) / 128;
+  const unsigned grid = (unsigned)std::min<long long>(ntiles, num_sms);
+  ffn_stream_kernel<128><<<grid, FS_THREADS, FfnStreamCfg<128>::TOTAL, s>>>(tmA, tmR, tmO, bw.tm_w1s, bw.lin2.tm, fa);
+  VV_CUDA(cudaGetLastError());
+  return VV_OK;
 }
 
 int pick_strip(long long total_rows, int rows) {

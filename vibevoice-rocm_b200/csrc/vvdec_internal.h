@@ -34,7 +34,8 @@ struct DenseW {                 // one packed GEMM weight: bf16 [N, K] K-major +
 struct BlockW {
   float *norm_w = nullptr, *dw_w = nullptr, *dw_b = nullptr, *gamma = nullptr, *ffn_norm_w = nullptr,
         *ffn_gamma = nullptr;
-  DenseW lin1, lin2;
+  DenseW lin1, lin2;            // lin1 is stored pre-scaled by 0.5 (weights and bias), see epilogue.cuh
+  CUtensorMap tm_w1s;           // lin1 through a [64 x 64] box (ffn_stream_kernel), C = 128 only
   long long state_off = 0;      // fp32 [6][C]
 };
 
