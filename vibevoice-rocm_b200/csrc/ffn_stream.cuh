@@ -8,13 +8,19 @@
 // W2 (128 KB each) do not fit in shared memory next to the tiles, so per 128-row tile the hidden dimension is
 // walked in NCH chunks of HC = 64 units and the weight chunks arrive through two TMA rings (they are L2-resident:
 // 256 KB per block):
-//   TMA :  a tile [128, C] bf16 (ring of NA);  W1 chunk [64, C] (ring S1);  W2 chunk [C, 64] (ring S2);
-//          residual in boxes of [128 rows, 32 fp32] (ring NY) — fine-grained so 2-3 boxes cover the HBM latency
-//   MMA :  D1[128, 64] = a * W1_chunk^T  (2 TMEM buffers);   D2[128, C] += H * W2_chunk^T  (2 TMEM buffers)
-//   E1  :  16 warps: tcgen05.ld D1 -> + b1 -> GELU -> bf16 -> 128B-swizzled smem H (A operand of GEMM 2), 2 buffers
-//   E2  :  4 warps, box by box: tcgen05.ld D2 -> + b2, * gamma, + residual (in the staged box, in place) -> TMA store
-// The single MMA thread issues G1(g+1) before G2(g) so the tensor pipe has work while E1 converts chunk g.
-// All hand-offs are mbarriers; there is no __syncthreads in the loop.
+//   warp 0  TMA : a tile [128, C] bf16 (ring of NA); W1 chunk [64, C] (ring S1); W2 chunk [C, 64] (ring S2)
+//   warp 1  G1  : D1[128, 64] = a * W1_chunk^T                  (tcgen05.mma, 2 accumulators in TMEM)
+//   warp 2  G2  : D2[128, C] += H * W2_chunk^T                  (tcgen05.mma, 2 accumulators in TMEM)
+//   warp 3  TMA : residual boxes [128 rows, 32 fp32] in (ring NY), finished boxes out; the reload of a slot is
+//                 issued by the same thread right after its store has read the slot
+//   E1, 2 x 8 warps alternating chunks: tcgen05.ld D1 -> + b1 -> GELU -> bf16 pairs -> tcgen05.st H (TENSOR memory,
+//       2 buffers): GEMM 2 reads its A operand from TMEM, so H costs no shared memory, no swizzled stores and no
+//       generic->async proxy fence (clock64 timeline: the st.shared + fence + arrive tail was ~500 cycles per chunk)
+//   E2, 4 warps, box by box: tcgen05.ld D2 -> + b2, * gamma, + residual (in the staged box, in place)
+// Two separate issuing threads for the two GEMMs: measured on B200, ONE thread issuing 12 MMAs + 6 barrier
+// waits + 6 commits per chunk was the bottleneck of this kernel (0.8 us per chunk with every other stage removed;
+// the descriptor and barrier bookkeeping of a single warp issues at ~6 cycles per instruction).  All hand-offs are
+// mbarriers; there is no __syncthreads in the loop.  Loop counters are 32-bit and all ring sizes powers of two.
 #pragma once
 #include <cuda.h>
 #include "ptx.cuh"
@@ -23,9 +29,19 @@
 
 namespace vv {
 
+#ifdef VV_FS_TRACE     // timeline instrumentation (A/B builds only): clock64 stamps of CTA 0 for chunks [TR_G0, TR_G0+32)
+__device__ long long vv_fs_trace[32 * 16];
+#define VV_TR(slot, g)                                                                              \
+  do {                                                                                              \
+    if (blockIdx.x == 0 && (g) >= 256 && (g) < 288) vv_fs_trace[((g) - 256) * 16 + (slot)] = clock64(); \
+  } while (0)
+#else
+#define VV_TR(slot, g) do { } while (0)
+#endif
+
 constexpr int FS_E1_WARPS = 16;
 constexpr int FS_E2_WARPS = 4;
-constexpr int FS_THREADS = (4 + FS_E1_WARPS + FS_E2_WARPS) * 32;   // warps 0..3: TMA a/W, MMA, TMA residual, TMA store
+constexpr int FS_THREADS = (4 + FS_E1_WARPS + FS_E2_WARPS) * 32;
 
 template <int C>
 struct FfnStreamCfg {
@@ -34,7 +50,8 @@ struct FfnStreamCfg {
   static constexpr int NCH = 4 * C / HC;           // chunks per tile
   static constexpr int KB = C / 64;                // 64-wide K blocks of the a tile / a W1 chunk
   static constexpr int NBOX = C / 32;              // residual / output boxes per tile
-  static constexpr int NA = 2, S1 = 3, S2 = 3, NY = 2;
+  static constexpr int NA = 2, S1 = 4, S2 = 2, NY = 4, ND1 = 2;
+  static constexpr int WLAG = 2;                   // the producer issues W2 chunk g - WLAG after W1 chunk g
   static constexpr int A_BYTES = 128 * C * 2;      // KB blocks of [128 rows x 128 B]
   static constexpr int W1_BYTES = HC * C * 2;      // KB blocks of [64 rows x 128 B]
   static constexpr int W2_BYTES = C * HC * 2;      // [C rows x 128 B]
@@ -44,14 +61,15 @@ struct FfnStreamCfg {
   static constexpr int OFF_W1 = OFF_A + NA * A_BYTES;
   static constexpr int OFF_W2 = OFF_W1 + S1 * W1_BYTES;
   static constexpr int OFF_H = OFF_W2 + S2 * W2_BYTES;
-  static constexpr int OFF_Y = OFF_H + 2 * H_BYTES;
+  static constexpr int OFF_Y = OFF_H;              // H lives in tensor memory (no shared-memory copy)
   static constexpr int OFF_BAR = OFF_Y + NY * Y_BYTES;
-  static constexpr int NBARS = 2 * NA + 2 * S1 + 2 * S2 + 12 + 3 * NY;
+  static constexpr int NBARS = 2 * NA + 2 * S1 + 2 * S2 + 2 * ND1 + 8 + 2 * NY;
   static constexpr int TOTAL = OFF_BAR + 512 + 1024;   // + alignment slack
   static_assert(NBARS * 8 + 8 <= 512, "barrier block");
   static_assert(TOTAL <= 232448, "exceeds the 227 KB dynamic shared memory limit");
-  static constexpr uint32_t TMEM_COLS = 512;       // D1: 2 x 64 at column 0; D2: 2 x C at column 128
-  static constexpr uint32_t D2_COL0 = 128;
+  static constexpr uint32_t TMEM_COLS = 512;       // D1: 2 x 64 at column 0; H: 2 x 32 at 128; D2: 2 x C at 256
+  static constexpr uint32_t H_COL0 = 128;          // H chunk as packed bf16 pairs: 64 hidden units = 32 columns
+  static constexpr uint32_t D2_COL0 = 256;
 };
 
 template <int C>
@@ -61,12 +79,12 @@ ffn_stream_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
                   const __grid_constant__ CUtensorMap tmW2, const FfnFusedArgs p) {
   using L = FfnStreamCfg<C>;
   constexpr int NA = L::NA, S1 = L::S1, S2 = L::S2, NY = L::NY, NCH = L::NCH, KB = L::KB, NBOX = L::NBOX;
+  constexpr int ND1 = L::ND1;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   uint8_t* sA = smem + L::OFF_A;
   uint8_t* sW1 = smem + L::OFF_W1;
   uint8_t* sW2 = smem + L::OFF_W2;
-  uint8_t* sH = smem + L::OFF_H;
   uint8_t* sY = smem + L::OFF_Y;
   uint64_t* bars = (uint64_t*)(smem + L::OFF_BAR);
   uint64_t* a_full = bars;                 // [NA]
@@ -75,22 +93,27 @@ ffn_stream_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   uint64_t* w1_empty = w1_full + S1;       // [S1]
   uint64_t* w2_full = w1_empty + S1;       // [S2]
   uint64_t* w2_empty = w2_full + S2;       // [S2]
-  uint64_t* d1_full = w2_empty + S2;       // [2]
-  uint64_t* d1_empty = d1_full + 2;        // [2]
-  uint64_t* h_full = d1_empty + 2;         // [2]
+  uint64_t* d1_full = w2_empty + S2;       // [ND1]
+  uint64_t* d1_empty = d1_full + ND1;      // [ND1]
+  uint64_t* h_full = d1_empty + ND1;       // [2]
   uint64_t* h_empty = h_full + 2;          // [2]
   uint64_t* d2_full = h_empty + 2;         // [2]
   uint64_t* d2_empty = d2_full + 2;        // [2]
   uint64_t* y_full = d2_empty + 2;         // [NY] residual box landed
   uint64_t* y_ready = y_full + NY;         // [NY] E2 finished the box: ready to store
-  uint64_t* y_empty = y_ready + NY;        // [NY] the TMA store has read the box
-  uint32_t* tmem_slot = (uint32_t*)(y_empty + NY);
+  uint32_t* tmem_slot = (uint32_t*)(y_ready + NY);
 
-  const int warp = threadIdx.x >> 5;
+  // Role index: the four single-thread roles (TMA, G1, G2, residual ring) sit in the HIGHEST warps of the CTA.
+  // The SM's warp arbiter favours higher warp ids; with the issuers in warps 0..3 they lost most issue slots to
+  // the E1 warps of their scheduler and needed ~950 cycles per chunk for ~100 instructions (clock64 timeline).
+  const int hw_warp = threadIdx.x >> 5;
+  const int warp = (hw_warp >= FS_E1_WARPS + FS_E2_WARPS) ? hw_warp - (FS_E1_WARPS + FS_E2_WARPS) : hw_warp + 4;
   const int lane = threadIdx.x & 31;
   const long long ntiles = (p.R + 127) / 128;
-  const long long my_tiles = (ntiles > blockIdx.x) ? (ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
-  const long long total_g = my_tiles * NCH;
+  const int my_tiles = (ntiles > blockIdx.x) ? (int)((ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x) : 0;
+  const int total_g = my_tiles * NCH;
+  const int tile_step = (int)gridDim.x * 128;      // row distance between this CTA's consecutive tiles
+  const int row0 = (int)blockIdx.x * 128;          // (rows fit 31 bits: the host checks R < 2^31)
 
   if (threadIdx.x == 0) {
     tma_prefetch_desc(&tmA);
@@ -101,19 +124,14 @@ ffn_stream_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     for (int i = 0; i < NA; ++i) { mbar_init(&a_full[i], 1); mbar_init(&a_empty[i], 1); }
     for (int i = 0; i < S1; ++i) { mbar_init(&w1_full[i], 1); mbar_init(&w1_empty[i], 1); }
     for (int i = 0; i < S2; ++i) { mbar_init(&w2_full[i], 1); mbar_init(&w2_empty[i], 1); }
+    for (int i = 0; i < ND1; ++i) { mbar_init(&d1_full[i], 1); mbar_init(&d1_empty[i], FS_E1_WARPS / 2); }
     for (int i = 0; i < 2; ++i) {
-      mbar_init(&d1_full[i], 1);
-      mbar_init(&d1_empty[i], FS_E1_WARPS);
-      mbar_init(&h_full[i], FS_E1_WARPS);
+      mbar_init(&h_full[i], FS_E1_WARPS / 2);
       mbar_init(&h_empty[i], 1);
       mbar_init(&d2_full[i], 1);
       mbar_init(&d2_empty[i], FS_E2_WARPS);
     }
-    for (int i = 0; i < NY; ++i) {
-      mbar_init(&y_full[i], 1);
-      mbar_init(&y_ready[i], FS_E2_WARPS);
-      mbar_init(&y_empty[i], 1);
-    }
+    for (int i = 0; i < NY; ++i) { mbar_init(&y_full[i], 1); mbar_init(&y_ready[i], FS_E2_WARPS); }
     fence_mbar_init();
   }
   if (warp == 1) {
@@ -127,153 +145,170 @@ ffn_stream_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
 
   if (warp == 0) {
     // ===== TMA producer: a tiles and weight chunks ===================================================
+    // W2 chunks trail W1 by WLAG chunks (GEMM 2 runs behind GEMM 1); the single in-order producer cannot
+    // deadlock: every wait below depends only on loads issued earlier in this same order.
     if (elect_one()) {
-      long long g = 0;
-      for (long long it = 0; it < my_tiles; ++it) {
-        const long long tile = blockIdx.x + it * gridDim.x;
-        const int sa = (int)(it % NA);
+      auto load_w2 = [&](int gp) {
+        const int s2 = gp & (S2 - 1);
+        mbar_wait(&w2_empty[s2], (uint32_t)(((gp / S2) & 1) ^ 1));
+        mbar_expect_tx(&w2_full[s2], L::W2_BYTES);
+        tma_load_2d(sW2 + s2 * L::W2_BYTES, &tmW2, &w2_full[s2], (gp & (NCH - 1)) * L::HC, 0);
+      };
+      auto load_a = [&](int it) {               // a tiles are requested one whole tile ahead of their first use
+        const int sa = it & (NA - 1);
         mbar_wait(&a_empty[sa], (uint32_t)(((it / NA) & 1) ^ 1));
         mbar_expect_tx(&a_full[sa], L::A_BYTES);
 #pragma unroll
         for (int kb = 0; kb < KB; ++kb)
-          tma_load_2d(sA + sa * L::A_BYTES + kb * (128 * 128), &tmA, &a_full[sa], kb * 64, (int)(tile * 128));
+          tma_load_2d(sA + sa * L::A_BYTES + kb * (128 * 128), &tmA, &a_full[sa], kb * 64, row0 + it * tile_step);
+      };
+      int g = 0;
+      if (my_tiles > 0) load_a(0);
+      for (int it = 0; it < my_tiles; ++it) {
         for (int j = 0; j < NCH; ++j, ++g) {
-          const int s1 = (int)(g % S1), s2 = (int)(g % S2);
+          if (j == 1 && it + 1 < my_tiles) load_a(it + 1);
+          const int s1 = g & (S1 - 1);
           mbar_wait(&w1_empty[s1], (uint32_t)(((g / S1) & 1) ^ 1));
           mbar_expect_tx(&w1_full[s1], L::W1_BYTES);
 #pragma unroll
           for (int kb = 0; kb < KB; ++kb)
             tma_load_2d(sW1 + s1 * L::W1_BYTES + kb * (L::HC * 128), &tmW1, &w1_full[s1], kb * 64, j * L::HC);
-          mbar_wait(&w2_empty[s2], (uint32_t)(((g / S2) & 1) ^ 1));
-          mbar_expect_tx(&w2_full[s2], L::W2_BYTES);
-          tma_load_2d(sW2 + s2 * L::W2_BYTES, &tmW2, &w2_full[s2], j * L::HC, 0);
+          if (g >= L::WLAG) load_w2(g - L::WLAG);
         }
       }
+      for (int gp = (total_g > L::WLAG ? total_g - L::WLAG : 0); gp < total_g; ++gp) load_w2(gp);
     }
   } else if (warp == 1) {
-    // ===== MMA issuer ===============================================================================
+    // ===== GEMM 1 issuer: D1[g % ND1] = a * W1_chunk^T ==================================================
     if (elect_one()) {
       constexpr uint32_t idesc1 = umma_idesc_bf16(128, L::HC);
-      constexpr uint32_t idesc2 = umma_idesc_bf16(128, C);
-      for (long long g = 0; g <= total_g; ++g) {
-        if (g < total_g) {
-          const long long it = g / NCH;
-          const int j = (int)(g % NCH), sa = (int)(it % NA), db = (int)(g & 1), s1 = (int)(g % S1);
-          mbar_wait(&d1_empty[db], (uint32_t)(((g >> 1) & 1) ^ 1));
-          if (j == 0) mbar_wait(&a_full[sa], (uint32_t)((it / NA) & 1));
-          mbar_wait(&w1_full[s1], (uint32_t)((g / S1) & 1));
+      const uint64_t da0 = umma_smem_desc<128>(smem_u32(sA));
+      const uint64_t dw0 = umma_smem_desc<128>(smem_u32(sW1));
+      int g = 0;
+      for (int it = 0; it < my_tiles; ++it) {
+        const int sa = it & (NA - 1);
+        mbar_wait(&a_full[sa], (uint32_t)((it / NA) & 1));
+        const uint64_t da = da0 + (uint64_t)((sa * L::A_BYTES) >> 4);
+        for (int j = 0; j < NCH; ++j, ++g) {
+          const int db = g & (ND1 - 1), s1 = g & (S1 - 1);
+          mbar_wait2(&d1_empty[db], (uint32_t)(((g / ND1) & 1) ^ 1), &w1_full[s1], (uint32_t)((g / S1) & 1));
+          VV_TR(1, g);
           tc_fence_after();
+          const uint64_t dw = dw0 + (uint64_t)((s1 * L::W1_BYTES) >> 4);
+          const uint32_t d = tmem_base + (uint32_t)(db * L::HC);
 #pragma unroll
           for (int kb = 0; kb < KB; ++kb) {
-            const uint64_t da = umma_smem_desc<128>(smem_u32(sA + sa * L::A_BYTES + kb * (128 * 128)));
-            const uint64_t dw = umma_smem_desc<128>(smem_u32(sW1 + s1 * L::W1_BYTES + kb * (L::HC * 128)));
 #pragma unroll
             for (int kk = 0; kk < 4; ++kk)
-              umma_bf16(tmem_base + (uint32_t)(db * L::HC), da + (uint64_t)(kk * 2), dw + (uint64_t)(kk * 2), idesc1,
-                        (kb | kk) != 0);
+              umma_bf16(d, da + (uint64_t)(((kb * 128 * 128) >> 4) + kk * 2),
+                        dw + (uint64_t)(((kb * L::HC * 128) >> 4) + kk * 2), idesc1, (kb | kk) != 0);
           }
           umma_commit(&d1_full[db]);
           umma_commit(&w1_empty[s1]);
-          if (j == NCH - 1) umma_commit(&a_empty[sa]);
+          VV_TR(2, g);
         }
-        if (g >= 1) {
-          const long long gp = g - 1, it = gp / NCH;
-          const int j = (int)(gp % NCH), hb = (int)(gp & 1), d2b = (int)(it & 1), s2 = (int)(gp % S2);
-          mbar_wait(&h_full[hb], (uint32_t)((gp >> 1) & 1));
-          mbar_wait(&w2_full[s2], (uint32_t)((gp / S2) & 1));
-          if (j == 0) mbar_wait(&d2_empty[d2b], (uint32_t)(((it >> 1) & 1) ^ 1));
-          tc_fence_after();
-          const uint64_t dh = umma_smem_desc<128>(smem_u32(sH + hb * L::H_BYTES));
-          const uint64_t dw = umma_smem_desc<128>(smem_u32(sW2 + s2 * L::W2_BYTES));
-#pragma unroll
-          for (int kk = 0; kk < 4; ++kk)
-            umma_bf16(tmem_base + L::D2_COL0 + (uint32_t)(d2b * C), dh + (uint64_t)(kk * 2), dw + (uint64_t)(kk * 2),
-                      idesc2, (j | kk) != 0);
-          umma_commit(&h_empty[hb]);
-          umma_commit(&w2_empty[s2]);
-          if (j == NCH - 1) umma_commit(&d2_full[d2b]);
-        }
+        umma_commit(&a_empty[sa]);
       }
     }
   } else if (warp == 2) {
-    // ===== TMA producer: residual boxes ================================================================
+    // ===== GEMM 2 issuer: D2[it & 1] += H * W2_chunk^T ==================================================
     if (elect_one()) {
-      long long k = 0;
-      for (long long it = 0; it < my_tiles; ++it) {
-        const long long tile = blockIdx.x + it * gridDim.x;
-        for (int c = 0; c < NBOX; ++c, ++k) {
-          const int sy = (int)(k % NY);
-          mbar_wait(&y_empty[sy], (uint32_t)(((k / NY) & 1) ^ 1));
-          mbar_expect_tx(&y_full[sy], L::Y_BYTES);
-          tma_load_2d(sY + sy * L::Y_BYTES, &tmR, &y_full[sy], c * 32, (int)(tile * 128));
+      constexpr uint32_t idesc2 = umma_idesc_bf16(128, C);
+      const uint64_t dw0 = umma_smem_desc<128>(smem_u32(sW2));
+      int g = 0;
+      for (int it = 0; it < my_tiles; ++it) {
+        const int d2b = it & 1;
+        mbar_wait(&d2_empty[d2b], (uint32_t)(((it >> 1) & 1) ^ 1));
+        const uint32_t d = tmem_base + L::D2_COL0 + (uint32_t)(d2b * C);
+        for (int j = 0; j < NCH; ++j, ++g) {
+          const int hb = g & 1, s2 = g & (S2 - 1);
+          mbar_wait2(&w2_full[s2], (uint32_t)((g / S2) & 1), &h_full[hb], (uint32_t)((g >> 1) & 1));
+          VV_TR(4, g);
+          tc_fence_after();
+          const uint32_t ah = tmem_base + L::H_COL0 + (uint32_t)(hb * 32);   // A operand from tensor memory
+          const uint64_t dw = dw0 + (uint64_t)((s2 * L::W2_BYTES) >> 4);
+#pragma unroll
+          for (int kk = 0; kk < 4; ++kk)
+            umma_bf16_ts(d, ah + (uint32_t)(kk * 8), dw + (uint64_t)(kk * 2), idesc2, (j | kk) != 0);
+          umma_commit(&h_empty[hb]);
+          umma_commit(&w2_empty[s2]);
+          VV_TR(5, g);
         }
+        umma_commit(&d2_full[d2b]);
       }
     }
   } else if (warp == 3) {
-    // ===== TMA store issuer: finished box -> global, then the slot goes back to the residual ring =========
+    // ===== residual boxes in, finished boxes out (one thread owns the Y ring) =================================
     if (elect_one()) {
-      long long k = 0;
-      for (long long it = 0; it < my_tiles; ++it) {
-        const long long tile = blockIdx.x + it * gridDim.x;
-        for (int c = 0; c < NBOX; ++c, ++k) {
-          const int sy = (int)(k % NY);
-          mbar_wait(&y_ready[sy], (uint32_t)((k / NY) & 1));
-          tma_store_2d(&tmO, sY + sy * L::Y_BYTES, c * 32, (int)(tile * 128));
-          tma_store_commit();
-          tma_store_wait_read<0>();
-          mbar_arrive(&y_empty[sy]);
-        }
+      const int total_k = my_tiles * NBOX;
+      auto load_box = [&](int k) {
+        const int sy = k & (NY - 1);
+        mbar_expect_tx(&y_full[sy], L::Y_BYTES);
+        tma_load_2d(sY + sy * L::Y_BYTES, &tmR, &y_full[sy], (k & (NBOX - 1)) * 32, row0 + (k / NBOX) * tile_step);
+      };
+      for (int k = 0; k < NY && k < total_k; ++k) load_box(k);
+      for (int k = 0; k < total_k; ++k) {
+        const int sy = k & (NY - 1);
+        mbar_wait(&y_ready[sy], (uint32_t)((k / NY) & 1));
+        tma_store_2d(&tmO, sY + sy * L::Y_BYTES, (k & (NBOX - 1)) * 32, row0 + (k / NBOX) * tile_step);
+        tma_store_commit();
+        tma_store_wait_read<0>();               // the store has read the slot: refill it
+        if (k + NY < total_k) load_box(k + NY);
       }
       tma_store_wait_all<0>();
     }
   } else if (warp < 4 + FS_E1_WARPS) {
     // ===== E1: D1 -> bias + GELU -> bf16 -> swizzled smem (A operand of GEMM 2) ============================
+    // Two groups of 8 warps alternate chunks (group G owns H buffer G), so one group's TMEM-load / MUFU /
+    // barrier latency overlaps the other's math; within a chunk a warp owns 32 rows x 32 columns.
     const int q = warp & 3;                   // TMEM lane quarter
-    const int cg = (warp - 4) >> 2;           // 16-column group of the 64-column chunk (0..3)
-    const int r = q * 32 + lane;              // row in the tile
-    uint8_t* hrow_base = sH + (r >> 3) * 1024 + (r & 7) * 128;
-    for (long long g = 0; g < total_g; ++g) {
-      const int j = (int)(g % NCH), db = (int)(g & 1);
-      const float* bp = p.b1 + j * L::HC + cg * 16;
-      const float4 b0 = __ldg(reinterpret_cast<const float4*>(bp));
-      const float4 b1v = __ldg(reinterpret_cast<const float4*>(bp + 4));
-      const float4 b2v = __ldg(reinterpret_cast<const float4*>(bp + 8));
-      const float4 b3v = __ldg(reinterpret_cast<const float4*>(bp + 12));
-      mbar_wait(&d1_full[db], (uint32_t)((g >> 1) & 1));
+    const int grp = (warp - 4) >> 3;          // chunk parity this warp serves
+    const int ch = ((warp - 4) >> 2) & 1;     // 32-column half of the 64-column chunk
+    const uint32_t haddr = tmem_base + ((uint32_t)(q * 32) << 16) + L::H_COL0 + (uint32_t)(grp * 32 + ch * 16);
+    const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(ch * 32);
+    for (int g = grp; g < total_g; g += 2) {
+      const int j = g & (NCH - 1), db = g & (ND1 - 1);
+      const float* bp = p.b1 + j * L::HC + ch * 32;
+      if (q == 0 && ch == 0 && lane == 0) VV_TR(6, g);
+      mbar_wait(&d1_full[db], (uint32_t)((g / ND1) & 1));
+      if (q == 0 && ch == 0 && lane == 0) VV_TR(7, g);
       tc_fence_after();
-      uint32_t v[16];
-      tmem_ld_32x16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(db * L::HC + cg * 16), v);
+      uint32_t v[32];
+      tmem_ld_32x32(taddr + (uint32_t)(db * L::HC), v);
       tmem_ld_wait();
+      if (q == 0 && ch == 0 && lane == 0) VV_TR(8, g);
       tc_fence_before();
-      uint4 pk0, pk1;
-      pk0.x = gelu2_bias_pack(__uint_as_float(v[0]), __uint_as_float(v[1]), b0.x, b0.y);
-      pk0.y = gelu2_bias_pack(__uint_as_float(v[2]), __uint_as_float(v[3]), b0.z, b0.w);
-      pk0.z = gelu2_bias_pack(__uint_as_float(v[4]), __uint_as_float(v[5]), b1v.x, b1v.y);
-      pk0.w = gelu2_bias_pack(__uint_as_float(v[6]), __uint_as_float(v[7]), b1v.z, b1v.w);
-      pk1.x = gelu2_bias_pack(__uint_as_float(v[8]), __uint_as_float(v[9]), b2v.x, b2v.y);
-      pk1.y = gelu2_bias_pack(__uint_as_float(v[10]), __uint_as_float(v[11]), b2v.z, b2v.w);
-      pk1.z = gelu2_bias_pack(__uint_as_float(v[12]), __uint_as_float(v[13]), b3v.x, b3v.y);
-      pk1.w = gelu2_bias_pack(__uint_as_float(v[14]), __uint_as_float(v[15]), b3v.z, b3v.w);
-      mbar_wait(&h_empty[db], (uint32_t)(((g >> 1) & 1) ^ 1));
-      uint8_t* hrow = hrow_base + db * L::H_BYTES;
-      *reinterpret_cast<uint4*>(hrow + (((cg * 2 + 0) ^ (r & 7)) * 16)) = pk0;   // 128B swizzle: chunk XOR row-in-atom
-      *reinterpret_cast<uint4*>(hrow + (((cg * 2 + 1) ^ (r & 7)) * 16)) = pk1;
-      fence_proxy_async_smem();                 // generic-proxy smem writes -> visible to tcgen05.mma
       __syncwarp();
-      if (lane == 0) {
-        mbar_arrive(&d1_empty[db]);
-        mbar_arrive(&h_full[db]);
+      if (lane == 0) mbar_arrive(&d1_empty[db]);   // accumulator is in registers: a later G1 may overwrite it
+      uint32_t hv[16];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const float4 b0 = __ldg(reinterpret_cast<const float4*>(bp + i * 8));
+        const float4 b1v = __ldg(reinterpret_cast<const float4*>(bp + i * 8 + 4));
+        hv[i * 4 + 0] = gelu2_bias_pack(__uint_as_float(v[i * 8 + 0]), __uint_as_float(v[i * 8 + 1]), b0.x, b0.y);
+        hv[i * 4 + 1] = gelu2_bias_pack(__uint_as_float(v[i * 8 + 2]), __uint_as_float(v[i * 8 + 3]), b0.z, b0.w);
+        hv[i * 4 + 2] = gelu2_bias_pack(__uint_as_float(v[i * 8 + 4]), __uint_as_float(v[i * 8 + 5]), b1v.x, b1v.y);
+        hv[i * 4 + 3] = gelu2_bias_pack(__uint_as_float(v[i * 8 + 6]), __uint_as_float(v[i * 8 + 7]), b1v.z, b1v.w);
       }
+      if (q == 0 && ch == 0 && lane == 0) VV_TR(9, g);
+      mbar_wait(&h_empty[grp], (uint32_t)(((g >> 1) & 1) ^ 1));
+      if (q == 0 && ch == 0 && lane == 0) VV_TR(10, g);
+      tc_fence_after();
+      tmem_st_32x16(haddr, hv);                   // thread = row: packed pairs (k, k+1) -> one 32-bit column
+      tmem_st_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&h_full[grp]);
+      if (q == 0 && ch == 0 && lane == 0) VV_TR(11, g);
     }
   } else {
     // ===== E2: D2 -> + b2, * gamma, + residual (TMA-staged box, swizzled) -> in place -> TMA store ===========
     const int q = warp & 3;
     const int r = q * 32 + lane;
-    long long k = 0;
-    for (long long it = 0; it < my_tiles; ++it) {
-      const int d2b = (int)(it & 1);
-      const long long tile = blockIdx.x + it * gridDim.x;
-      const long long m = tile * 128 + r;
+    int k = 0;
+    for (int it = 0; it < my_tiles; ++it) {
+      const int d2b = it & 1;
+      const long long m = (long long)row0 + (long long)it * tile_step + r;
       const bool valid = m < p.R;
       long long brow = 0;
       if (p.out_bf16 != nullptr && valid) {
@@ -284,7 +319,7 @@ ffn_stream_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       tc_fence_after();
 #pragma unroll 1
       for (int c = 0; c < NBOX; ++c, ++k) {
-        const int sy = (int)(k % NY);
+        const int sy = k & (NY - 1);
         uint32_t v[32];
         tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + L::D2_COL0 + (uint32_t)(d2b * C + c * 32), v);
         mbar_wait(&y_full[sy], (uint32_t)((k / NY) & 1));

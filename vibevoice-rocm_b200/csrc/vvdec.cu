@@ -622,6 +622,7 @@ int launch_ffn_fused(vv_decoder* d, int C, const BlockW& bw, const __nv_bfloat16
   if (num_sms == 0) VV_CUDA(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, d->cfg.device));
   const long long ntiles = (R + 127) / 128;
   const unsigned grid = (unsigned)std::min<long long>(ntiles, num_sms);
+  if (R + 256LL * num_sms >= (1LL << 31)) { set_error("ffn_stream: %lld rows exceed the 31-bit row index", R); return VV_ERR_BAD_SHAPE; }
   ffn_stream_kernel<128><<<grid, FS_THREADS, FfnStreamCfg<128>::TOTAL, s>>>(tmA, tmR, tmO, bw.tm_w1s, bw.lin2.tm, fa);
   VV_CUDA(cudaGetLastError());
   return VV_OK;
@@ -1069,3 +1070,9 @@ extern "C" int32_t vv_test_gelu(const float* x, float* y, int32_t n, void* cuda_
   VV_CUDA(cudaGetLastError());
   return VV_OK;
 }
+
+#ifdef VV_FS_TRACE
+extern "C" int32_t vv_debug_read_trace(long long* host, int32_t n) {
+  return (int32_t)cudaMemcpyFromSymbol(host, vv::vv_fs_trace, sizeof(long long) * (size_t)n);
+}
+#endif
