@@ -66,10 +66,12 @@ typedef struct vv_config {
   int32_t kernel_size;                /* 7 (depthwise mixer, stem, head)                        */
   float   eps;                        /* layernorm_eps 1e-5                                     */
   int32_t device;                     /* CUDA device ordinal                                    */
-  int32_t gemm_path;                  /* 0 = product path (fused tcgen05 FFN at C<=64, tcgen05 GEMMs
-                                         elsewhere); 1 = CUDA-core validation GEMM everywhere;
+  int32_t gemm_path;                  /* 0 = product path (whole-Block1D kernel at C<=64, fused FFN with
+                                         streamed weights at C=128, tcgen05 GEMMs elsewhere);
+                                         1 = CUDA-core validation GEMM everywhere;
                                          2 = unfused tcgen05 GEMMs everywhere (A/B against 0);
-                                         3 = as 2 but only the non-persistent GEMM kernel       */
+                                         3 = as 2 but only the non-persistent GEMM kernel;
+                                         4 = as 0 but mixer and FFN halves as separate kernels  */
 } vv_config;
 
 typedef struct vv_decoder vv_decoder; /* opaque: packed weights + launch plan                    */
@@ -132,7 +134,7 @@ int64_t vv_decoder_take_launch_count(vv_decoder* dec);
  */
 typedef enum vv_kernel_kind {
   VV_K_PREP = 0, VV_K_STEM = 1, VV_K_MIXER = 2, VV_K_FFN1 = 3, VV_K_FFN2 = 4, VV_K_HALO = 5,
-  VV_K_UPSAMPLE = 6, VV_K_HEAD = 7, VV_K_STATE = 8, VV_K_FFN_FUSED = 9
+  VV_K_UPSAMPLE = 6, VV_K_HEAD = 7, VV_K_STATE = 8, VV_K_FFN_FUSED = 9, VV_K_BLOCK_FUSED = 10
 } vv_kernel_kind;
 typedef struct vv_profile_record {
   int32_t kind;        /* vv_kernel_kind */
@@ -164,6 +166,10 @@ int32_t vv_kernel_mixer(vv_decoder* dec, int32_t stage, int32_t block, const flo
  * a: bf16 [B*rows, C]; hidden: bf16 scratch [B*rows, 4C]; resid/out: fp32 [B*rows, C] (may alias). */
 int32_t vv_kernel_ffn(vv_decoder* dec, int32_t stage, int32_t block, const void* a, const float* resid,
                       float* out, void* hidden, int32_t B, int32_t rows, void* cuda_stream);
+/* Whole Block1D (mixer half + FFN half, :927-942) in ONE kernel, stages with C <= 64 only (VV_ERR_UNSUPPORTED
+ * otherwise): x, out fp32 [B, rows, C]; out must not alias x. */
+int32_t vv_kernel_block(vv_decoder* dec, int32_t stage, int32_t block, const float* x, float* out,
+                        int32_t B, int32_t rows, void* cuda_stream);
 /* Polyphase transposed conv INTO stage `stage` (1..n_stages-1), (:875-878 + trim :563-571):
  * xb: bf16 [B, rows+1, Cin], rows 1..rows = input, row 0 = causal context (zeroed by this call);
  * y: fp32 [B, rows*ratio, Cout]. */

@@ -78,6 +78,34 @@ def test_ffn_half(full_decoder, stage, B, rows):
     assert m["snr_db"] > 50 and m["rel_max"] < 5e-3, m
 
 
+@pytest.mark.parametrize("stage,B,rows", [(6, 2, 300), (5, 1, 129), (6, 1, 1), (5, 3, 5), (6, 1, 6), (5, 2, 127),
+                                          (6, 3, 40001), (5, 2, 60001)])
+def test_block_fused(full_decoder, stage, B, rows):
+    """Whole Block1D in one kernel (C <= 64) against the oracle's mixer half followed by its FFN half."""
+    dec, w = full_decoder
+    Cc = FULL.stage_channels(stage)
+    x = (_rng(31000 + stage * 100 + rows).standard_normal((B, rows, Cc)).astype(np.float32) * 1.7)
+    p = f"decoder.stages.{stage}.0."
+    xc = x.transpose(0, 2, 1)
+    h = O.rms_norm_channels(xc, w[p + "norm.weight"], FULL.eps)
+    h, _ = O.sconv1d(h, w[p + "mixer.conv.conv.conv.weight"], w[p + "mixer.conv.conv.conv.bias"], groups=Cc)
+    y = xc + h * w[p + "gamma"][None, :, None]
+    a = O.rms_norm_channels(y, w[p + "ffn_norm.weight"], FULL.eps).transpose(0, 2, 1)        # [B, rows, C]
+    f = O.ffn(a, w[p + "ffn.linear1.weight"], w[p + "ffn.linear1.bias"], w[p + "ffn.linear2.weight"],
+              w[p + "ffn.linear2.bias"])
+    ref = y.transpose(0, 2, 1) + f * w[p + "ffn_gamma"][None, None, :]
+    xt = torch.from_numpy(x).cuda()
+    out = torch.full_like(xt, float("nan"))
+    rc = dec._lib.vv_kernel_block(dec._h, stage, 0, _ptr(xt), _ptr(out), B, rows, _stream())
+    _check(dec, rc, "vv_kernel_block")
+    torch.cuda.synchronize()
+    o = out.cpu().numpy()
+    assert np.isfinite(o).all()
+    m = O.parity_metrics(o, ref)
+    # roundings: a and the hidden activation to bf16 (2^-9 relative each), fp32 everywhere else
+    assert m["snr_db"] > 45 and m["rel_max"] < 2e-2, m
+
+
 @pytest.mark.parametrize("stage,B,rows", [(1, 2, 5), (2, 1, 17), (3, 2, 40), (4, 1, 130), (5, 2, 200), (6, 1, 300),
                                           (6, 3, 1), (1, 130, 1)])
 def test_polyphase_upsample(full_decoder, stage, B, rows):

@@ -20,7 +20,7 @@ from vvdec.synthetic import random_state_dict   # noqa: E402
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--kind", default="ffn", choices=["mixer", "ffn", "upsample", "head"])
+    ap.add_argument("--kind", default="ffn", choices=["mixer", "ffn", "upsample", "head", "block"])
     ap.add_argument("--stage", type=int, default=6)
     ap.add_argument("--frames", type=int, default=2048)
     ap.add_argument("--iters", type=int, default=5)
@@ -51,6 +51,11 @@ def main():
         hid = torch.empty(rows, 4 * Cc, device="cuda", dtype=torch.bfloat16)
         call = lambda: lib.vv_kernel_ffn(h, a.stage, 0, P(ab), P(res), P(out), P(hid), 1, rows, st)
         moved = rows * Cc * 10
+    elif a.kind == "block":
+        x = torch.randn(1, rows, Cc, device="cuda")
+        out = torch.empty_like(x)
+        call = lambda: lib.vv_kernel_block(h, a.stage, 0, P(x), P(out), 1, rows, st)
+        moved = rows * Cc * 8
     elif a.kind == "upsample":
         cin = g.stage_channels(a.stage - 1)
         r = g.ratios[a.stage - 1]

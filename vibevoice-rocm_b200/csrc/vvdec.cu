@@ -11,6 +11,7 @@
 #include "rowops.cuh"
 #include "ffn_fused.cuh"
 #include "ffn_stream.cuh"
+#include "block_fused.cuh"
 #include "gemm_tc2.cuh"
 
 namespace vv {
@@ -586,7 +587,7 @@ int launch_ffn_fused_inst(vv_decoder* d, const CUtensorMap& tmA, const CUtensorM
 }
 
 bool ffn_fused_supported(const vv_decoder* d, int C) {
-  return d->cfg.gemm_path == 0 && (C == 32 || C == 64 || C == 128);
+  return (d->cfg.gemm_path == 0 || d->cfg.gemm_path == 4) && (C == 32 || C == 64 || C == 128);
 }
 
 int launch_ffn_fused(vv_decoder* d, int C, const BlockW& bw, const __nv_bfloat16* a, const float* resid, float* out,
@@ -626,6 +627,50 @@ int launch_ffn_fused(vv_decoder* d, int C, const BlockW& bw, const __nv_bfloat16
   ffn_stream_kernel<128><<<grid, FS_THREADS, FfnStreamCfg<128>::TOTAL, s>>>(tmA, tmR, tmO, bw.tm_w1s, bw.lin2.tm, fa);
   VV_CUDA(cudaGetLastError());
   return VV_OK;
+}
+
+// Whole Block1D (mixer + FFN) in one kernel (C = 32, 64; block_fused.cuh).  x: fp32 [nbatch, rows_pb, C];
+// out: fp32, same shape, must NOT alias x (tiles read 6 rows of their left neighbour).
+bool block_fused_supported(const vv_decoder* d, int C) {
+  return d->cfg.gemm_path == 0 && (C == 32 || C == 64);
+}
+
+template <int C>
+int launch_block_fused_inst(vv_decoder* d, const CUtensorMap& tmO, const BlockW& bw, const BlockFusedArgs& a,
+                            cudaStream_t s) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    VV_CUDA(cudaFuncSetAttribute(block_fused_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)BlockFusedCfg<C>::TOTAL));
+    attr_set = true;
+  }
+  static int num_sms = 0;
+  if (num_sms == 0) VV_CUDA(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, d->cfg.device));
+  const long long ntiles = (long long)a.nbatch * a.tiles_pb;
+  const unsigned grid = (unsigned)std::min<long long>(ntiles, num_sms);
+  block_fused_kernel<C><<<grid, BlockFusedCfg<C>::THREADS, BlockFusedCfg<C>::TOTAL, s>>>(tmO, bw.lin1.tm, bw.lin2.tm, a);
+  VV_CUDA(cudaGetLastError());
+  return VV_OK;
+}
+
+int launch_block_fused(vv_decoder* d, int C, const BlockW& bw, const float* x, float* out, __nv_bfloat16* out_bf16,
+                       int nbatch, int rows_pb, vv_state* st, const int32_t* slots, cudaStream_t s) {
+  if (x == out) { set_error("block_fused: input and output must not alias"); return VV_ERR_INVALID_ARG; }
+  BlockFusedArgs a;
+  a.x = x; a.nbatch = nbatch; a.rows_pb = rows_pb; a.tiles_pb = (rows_pb + 127) / 128; a.eps = d->cfg.eps;
+  a.norm_w = bw.norm_w; a.dw_w = bw.dw_w; a.dw_b = bw.dw_b; a.gamma = bw.gamma; a.ffn_norm_w = bw.ffn_norm_w;
+  a.b1 = bw.lin1.bias; a.b2 = bw.lin2.bias; a.ffn_gamma = bw.ffn_gamma; a.out_bf16 = out_bf16;
+  a.st = make_state_ref(st, slots, bw.state_off);
+  if ((long long)nbatch * a.tiles_pb >= (1LL << 31) / 8) { set_error("block_fused: too many tiles"); return VV_ERR_BAD_SHAPE; }
+  CUtensorMap tmO;                                   // output fp32 [nbatch, rows_pb, C], boxes of [128 rows, 32 floats]
+  const uint64_t dims[3] = {(uint64_t)C, (uint64_t)rows_pb, (uint64_t)nbatch};
+  const uint64_t strides[2] = {(uint64_t)C * 4, (uint64_t)rows_pb * C * 4};
+  const uint32_t box[3] = {32u, 128u, 1u};
+  int rc = encode_map(&tmO, out, 3, dims, strides, box, true);
+  if (rc != VV_OK) return rc;
+  d->launches++;
+  if (C == 32) return launch_block_fused_inst<32>(d, tmO, bw, a, s);
+  return launch_block_fused_inst<64>(d, tmO, bw, a, s);
 }
 
 int pick_strip(long long total_rows, int rows) {
@@ -755,6 +800,15 @@ int run_pass(vv_decoder* d, const LatView& lat, int nb, int T, void* audio, int 
     const int nblk = (int)sw.blocks.size();
     for (int j = 0; j < nblk; ++j) {
       const BlockW& bw = sw.blocks[j];
+      if (block_fused_supported(d, C)) {
+        // whole block in one kernel, ping-pong between the two fp32 buffers of the stage (X holds the result)
+        const bool feeds = (j == nblk - 1) && (i + 1 < S);
+        rc = launch_block_fused(d, C, bw, X, Y, feeds ? XB : nullptr, nb, rows_pb, st, slots, s);
+        if (rc != VV_OK) return rc;
+        d->mark(VV_K_BLOCK_FUSED, i, s);
+        std::swap(X, Y);
+        continue;
+      }
       rc = launch_mixer(d, bw, C, X, Y, A, nb, rows_pb, st, slots, s);
       if (rc != VV_OK) return rc;
       d->mark(VV_K_MIXER, i, s);
@@ -1020,6 +1074,18 @@ extern "C" int32_t vv_kernel_ffn(vv_decoder* d, int32_t stage, int32_t block, co
   EpiOut e2;
   e2.epi = EPI_RESID; e2.gamma = bw.ffn_gamma; e2.resid = resid; e2.out_f32 = out;
   return launch_gemm(d, reinterpret_cast<const __nv_bfloat16*>(hidden), R, (int)R, 1, bw.lin2, e2, s);
+}
+
+extern "C" int32_t vv_kernel_block(vv_decoder* d, int32_t stage, int32_t block, const float* x, float* out,
+                                   int32_t B, int32_t rows, void* cuda_stream) {
+  int rc = check_block(d, stage, block);
+  if (rc != VV_OK) return rc;
+  if (!x || !out || B < 1 || rows < 1) { set_error("bad argument"); return VV_ERR_INVALID_ARG; }
+  VV_CUDA(cudaSetDevice(d->cfg.device));
+  const StageW& sw = d->stages[stage];
+  if (!block_fused_supported(d, sw.C)) { set_error("no fused block kernel for C=%d", sw.C); return VV_ERR_UNSUPPORTED; }
+  return launch_block_fused(d, sw.C, sw.blocks[block], x, out, nullptr, B, rows, nullptr, nullptr,
+                            reinterpret_cast<cudaStream_t>(cuda_stream));
 }
 
 extern "C" int32_t vv_kernel_upsample(vv_decoder* d, int32_t stage, void* xb, float* y, int32_t B, int32_t rows,

@@ -37,7 +37,8 @@ class VvProfileRecord(C.Structure):
     _fields_ = [("kind", C.c_int32), ("stage", C.c_int32), ("launches", C.c_int64), ("ms", C.c_double)]
 
 
-KERNEL_KINDS = ("prep", "stem", "mixer", "ffn1", "ffn2", "halo", "upsample", "head", "state", "ffn_fused")
+KERNEL_KINDS = ("prep", "stem", "mixer", "ffn1", "ffn2", "halo", "upsample", "head", "state", "ffn_fused",
+                "block_fused")
 
 # name -> (restype, argtypes): every symbol include/vvdec.h declares
 _P, _I32, _I64 = C.c_void_p, C.c_int32, C.c_int64
@@ -66,6 +67,7 @@ SIGNATURES = {
     "vv_state_import": (_I32, [_P, _I32, _P, _I64]),
     "vv_kernel_mixer": (_I32, [_P, _I32, _I32, _P, _P, _P, _I32, _I32, _P]),
     "vv_kernel_ffn": (_I32, [_P, _I32, _I32, _P, _P, _P, _P, _I32, _I32, _P]),
+    "vv_kernel_block": (_I32, [_P, _I32, _I32, _P, _P, _I32, _I32, _P]),
     "vv_kernel_upsample": (_I32, [_P, _I32, _P, _P, _I32, _I32, _P]),
     "vv_test_gelu": (_I32, [_P, _P, _I32, _P]),
     "vv_kernel_head": (_I32, [_P, _P, _P, _I32, _I32, _I32, _P]),
