@@ -96,6 +96,12 @@ __device__ __forceinline__ void group_sum7(float (&s)[7]) {
     for (int i = 0; i < 7; ++i) s[i] += __shfl_xor_sync(0xffffffffu, s[i], m);
   }
 }
+// 1/sqrt(mean + eps): one MUFU op (rsqrt.approx, 2 ulp; the statistic feeds a bf16 operand and a fp32 residual update)
+__device__ __forceinline__ float rstd_of(float ss, float inv_c, float eps) {
+  float r;
+  asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(fmaf(ss, inv_c, eps)));
+  return r;
+}
 template <int LPR>
 __device__ __forceinline__ float group_sum1(float s) {
 #pragma unroll
@@ -389,13 +395,16 @@ block_fused_kernel(const __grid_constant__ CUtensorMap tmO, const __grid_constan
     };
     // batch 0 of a tile = rows 8gi-6 .. 8gi (6 warm-up rows + the first output row); batch 1 = rows 8gi+1 .. 8gi+7
     auto load_rows = [&](int it, int bt, float4 (&dst)[7]) {
-#pragma unroll
-      for (int i = 0; i < 7; ++i) dst[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (it >= my_tiles) return;
+      if (it >= my_tiles) return;                                    // (nothing will consume dst)
       int b, t0;
       tile_of(it, b, t0);
       const int ts = t0 + gi * 8 + (bt ? 1 : -6);
-      const float* xb = p.x + (long long)b * p.rows_pb * C + c0;
+      const float* xb = p.x + ((long long)b * p.rows_pb + ts) * C + c0;
+      if (ts >= 0 && ts + 7 <= p.rows_pb) {                          // interior: 7 unpredicated loads off one pointer
+#pragma unroll
+        for (int i = 0; i < 7; ++i) dst[i] = __ldg(reinterpret_cast<const float4*>(xb + i * C));
+        return;
+      }
       const float* srd = nullptr;
       if (ts < 0 && p.st.base != nullptr) {
         const uint8_t* rd8;
@@ -406,8 +415,9 @@ block_fused_kernel(const __grid_constant__ CUtensorMap tmO, const __grid_constan
 #pragma unroll
       for (int i = 0; i < 7; ++i) {
         const int t = ts + i;
+        dst[i] = make_float4(0.f, 0.f, 0.f, 0.f);
         if (t < p.rows_pb) {
-          if (t >= 0) dst[i] = __ldg(reinterpret_cast<const float4*>(xb + (long long)t * C));
+          if (t >= 0) dst[i] = __ldg(reinterpret_cast<const float4*>(xb + i * C));
           else if (srd != nullptr) dst[i] = *reinterpret_cast<const float4*>(srd + (6 + t) * C);
         }
       }
@@ -452,7 +462,7 @@ block_fused_kernel(const __grid_constant__ CUtensorMap tmO, const __grid_constan
     // the stream's new context = last 6 raw rows of [old context, x]  (reference :371-382)
     auto state_row = [&](int t, const float4& raw) {
       const int dst = t - (p.rows_pb - 6);
-      if (st_wr != nullptr && dst >= 0 && t < p.rows_pb) *reinterpret_cast<float4*>(st_wr + dst * C) = raw;
+      if (dst >= 0 && t < p.rows_pb) *reinterpret_cast<float4*>(st_wr + dst * C) = raw;
     };
 
     float4 bufA[7], bufB[7];
@@ -483,8 +493,7 @@ block_fused_kernel(const __grid_constant__ CUtensorMap tmO, const __grid_constan
         float ss[7];
 #pragma unroll
         for (int i = 0; i < 7; ++i) {
-          if (i < 6) { if (ts + i < 0) state_row(ts + i, bufA[i]); }
-          else state_row(ts + i, bufA[i]);
+          if (st_wr != nullptr && (i == 6 || ts + i < 0)) state_row(ts + i, bufA[i]);
           rows[i].lo = f2_pack(bufA[i].x, bufA[i].y);
           rows[i].hi = f2_pack(bufA[i].z, bufA[i].w);
           ss[i] = dot4(rows[i]);
@@ -492,17 +501,17 @@ block_fused_kernel(const __grid_constant__ CUtensorMap tmO, const __grid_constan
         group_sum7<LPR>(ss);
 #pragma unroll
         for (int i = 0; i < 6; ++i) {
-          const float rstd = rsqrtf(ss[i] * inv_c + p.eps);
+          const float rstd = rstd_of(ss[i], inv_c, p.eps);
           const f32x2 rr = f2_pack(rstd, rstd);
           win[i].lo = f2_mul(rows[i].lo, rr);
           win[i].hi = f2_mul(rows[i].hi, rr);
         }
-        conv_row(6, rows[6], rsqrtf(ss[6] * inv_c + p.eps));
+        conv_row(6, rows[6], rstd_of(ss[6], inv_c, p.eps));
         const float s2 = group_sum1<LPR>(dot4(rows[6]));
         // the slots of this tile must be free before the first store
         mbar_wait(&a_empty[sa], (uint32_t)(((it / NA) & 1) ^ 1));
         mbar_wait(&y_empty[sy], (uint32_t)(((it / NY) & 1) ^ 1));
-        store_row(0, rows[6], rsqrtf(s2 * inv_c + p.eps), fw, ys, as);
+        store_row(0, rows[6], rstd_of(s2, inv_c, p.eps), fw, ys, as);
       }
       load_rows(it + 1, 0, bufA);                          // first batch of the next tile: in flight during batch 1
 
@@ -513,7 +522,7 @@ block_fused_kernel(const __grid_constant__ CUtensorMap tmO, const __grid_constan
         float ss[7];
 #pragma unroll
         for (int i = 0; i < 7; ++i) {
-          state_row(ts + i, bufB[i]);
+          if (st_wr != nullptr) state_row(ts + i, bufB[i]);
           rows[i].lo = f2_pack(bufB[i].x, bufB[i].y);
           rows[i].hi = f2_pack(bufB[i].z, bufB[i].w);
           ss[i] = dot4(rows[i]);
@@ -521,12 +530,12 @@ block_fused_kernel(const __grid_constant__ CUtensorMap tmO, const __grid_constan
         group_sum7<LPR>(ss);
 #pragma unroll
         for (int i = 0; i < 7; ++i) {
-          conv_row(i, rows[i], rsqrtf(ss[i] * inv_c + p.eps));
+          conv_row(i, rows[i], rstd_of(ss[i], inv_c, p.eps));
           ss[i] = dot4(rows[i]);
         }
         group_sum7<LPR>(ss);
 #pragma unroll
-        for (int i = 0; i < 7; ++i) store_row(i + 1, rows[i], rsqrtf(ss[i] * inv_c + p.eps), fw, ys, as);
+        for (int i = 0; i < 7; ++i) store_row(i + 1, rows[i], rstd_of(ss[i], inv_c, p.eps), fw, ys, as);
       }
       fence_proxy_async_smem();                 // a tile (generic-proxy stores) -> visible to tcgen05.mma
       __syncwarp();
