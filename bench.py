@@ -144,6 +144,8 @@ def kernel_work(geom, kind: str, stage: int):
         return bound, 2 * cm, 8 * C * cm, moved
     if kind == "ffn_fused":    # whole FFN half in one launch: a (bf16) + resid (fp32) in, out (fp32)
         return ("tensor" if C >= 128 else "hbm"), 4 * cm, 16 * C * cm, 10 * cm
+    if kind == "block_fused":  # whole Block1D in one launch (C <= 64): SURVEY's mixer half + FFN half = 8*C*M bytes;
+        return "hbm", 8 * cm, 20 * cm + 16 * C * cm, 8 * cm   # this design moves exactly that (fp32 x in, fp32 x out)
     if kind == "upsample":     # 2*(Cin*Min + Cout*Mout) bytes, 4*Cin*Cout*r*Min flop
         cin, r = geom.stage_channels(stage - 1), geom.ratios[stage - 1]
         min_ = M // r
@@ -314,7 +316,7 @@ def main():
     for r in prof:
         bound, abytes, aflop, moved = kernel_work(geom, r["kind"], r["stage"])
         n = max(1, r["launches"])
-        nblk = geom.depths[r["stage"]] if r["kind"] in ("mixer", "ffn1", "ffn2", "ffn_fused") else 1
+        nblk = geom.depths[r["stage"]] if r["kind"] in ("mixer", "ffn1", "ffn2", "ffn_fused", "block_fused") else 1
         passes = n // nblk                                   # decode passes the workspace split the batch into
         units = frames / passes                              # latent frames one launch processes
         ms_launch = r["ms"] / n
