@@ -134,7 +134,8 @@ int64_t vv_decoder_take_launch_count(vv_decoder* dec);
  */
 typedef enum vv_kernel_kind {
   VV_K_PREP = 0, VV_K_STEM = 1, VV_K_MIXER = 2, VV_K_FFN1 = 3, VV_K_FFN2 = 4, VV_K_HALO = 5,
-  VV_K_UPSAMPLE = 6, VV_K_HEAD = 7, VV_K_STATE = 8, VV_K_FFN_FUSED = 9, VV_K_BLOCK_FUSED = 10
+  VV_K_UPSAMPLE = 6, VV_K_HEAD = 7, VV_K_STATE = 8, VV_K_FFN_FUSED = 9, VV_K_BLOCK_FUSED = 10,
+  VV_K_ENC_STEM = 11, VV_K_DOWNSAMPLE = 12, VV_K_PAD = 13, VV_K_ENC_HEAD = 14   /* encoder path */
 } vv_kernel_kind;
 typedef struct vv_profile_record {
   int32_t kind;        /* vv_kernel_kind */
@@ -155,6 +156,35 @@ int32_t vv_state_zero(vv_state* st, const int32_t* slot_ids, int32_t n, void* cu
 /* checkpoint one slot to / from host memory (vv_state_bytes_per_slot bytes); synchronises. */
 int32_t vv_state_export(const vv_state* st, int32_t slot, void* host_dst, int64_t bytes);
 int32_t vv_state_import(vv_state* st, int32_t slot, const void* host_src, int64_t bytes);
+
+/* ---- encoder (replaces TokenizerEncoder.forward :810-813 under VibeVoiceAcousticTokenizerModel.encode :1081-1085) --
+ * The encoder mirrors the decoder's vv_config (same struct, decoder-order fields): stage i has n_filters * 2^i
+ * channels, depth depths[n_stages-1-i] and is entered through a strided conv of ratio ratios[n_stages-1-i]
+ * (:701, :1019-1028).  Tensor names are the reference's "encoder.*" keys.  Offline form only (cache=None /
+ * use_cache=False); the streaming form of the strided convs is not built. */
+typedef struct vv_encoder vv_encoder;
+int32_t vv_encoder_create(const vv_config* cfg, vv_encoder** out);
+int32_t vv_encoder_destroy(vv_encoder* enc);
+int32_t vv_encoder_load_tensor(vv_encoder* enc, const char* name, const void* data, int32_t dtype,
+                               const int64_t* shape, int32_t ndim, int32_t is_device);
+int32_t vv_encoder_finalize(vv_encoder* enc);
+int64_t vv_encoder_param_count(const vv_encoder* enc);
+int32_t vv_encoder_hop(const vv_encoder* enc);
+/* latent frames for L samples: ceil(L / hop) (each strided conv pads its input up to a whole stride, :127-133) */
+int64_t vv_encoder_frames(const vv_encoder* enc, int64_t L);
+int64_t vv_encoder_workspace_bytes(const vv_encoder* enc, int32_t B, int64_t L);
+/*
+ * audio : device, [B, L] (= the reference's [B, 1, L]) contiguous, f32 or bf16.
+ * mean  : device, fp32 [B, frames, vae_dim] contiguous — VibeVoiceTokenizerEncoderOutput.mean (:1084-1085; its
+ *         std is the config's fix_std, a host-side constant).
+ * A workspace smaller than vv_encoder_workspace_bytes(B, L) is honoured by encoding the utterances in groups;
+ * one utterance must fit (VV_ERR_WORKSPACE otherwise).
+ */
+int32_t vv_encode(vv_encoder* enc, const void* audio, int32_t audio_dtype, int32_t B, int64_t L, float* mean,
+                  void* workspace, int64_t workspace_bytes, void* cuda_stream);
+int64_t vv_encoder_take_launch_count(vv_encoder* enc);
+int32_t vv_encoder_set_profiling(vv_encoder* enc, int32_t enabled);
+int32_t vv_encoder_read_profile(vv_encoder* enc, vv_profile_record* out, int32_t cap);
 
 /* ---- per-kernel entry points (offline form; tests and bench.py's roofline leg time these alone) -- */
 /* Fused Block1D mixer half on a channels-last fp32 activation x [B, rows, C]:

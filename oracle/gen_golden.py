@@ -25,7 +25,7 @@ if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
 from oracle.geometry import FULL, TINY, DecoderGeometry          # noqa: E402
-from oracle.weights import make_weights, make_latents            # noqa: E402
+from oracle.weights import make_weights, make_latents, make_encoder_weights, make_audio   # noqa: E402
 from oracle.ref_shim import build_reference_model, import_reference   # noqa: E402
 
 GOLD = os.path.join(ROOT, "tests", "golden")
@@ -122,7 +122,52 @@ def streaming_case(name, geom, init, wseed, schedule, lseed, n_streams, model=No
     print(f"{name}: {len(outs)} decode calls recorded")
 
 
+def encoder_case(name, geom, init, wseed, B, L, aseed):
+    """Reference ``VibeVoiceAcousticTokenizerModel.encode(audio).mean`` (:1081-1085) on seeded weights / audio, plus
+    tap summaries of every downsample layer's output and of every stage's output (pre-hooks on the consumer)."""
+    import torch
+    t0 = time.time()
+    w = make_encoder_weights(geom, init, wseed)
+    model = build_reference_model(geom, w)
+    audio = make_audio(B, L, aseed)
+    taps, hooks = {}, []
+    enc = model.encoder
+    for i in range(geom.n_stages):
+        hooks.append(enc.downsample_layers[i][0].register_forward_hook(
+            lambda m, a, out, key=f"down{i}": taps.__setitem__(key, out.detach().numpy().copy())))
+        nxt = enc.downsample_layers[i + 1][0] if i + 1 < geom.n_stages else enc.head
+        hooks.append(nxt.register_forward_pre_hook(
+            lambda m, a, key=f"encoder.stages.{i}.{geom.enc_depth(i) - 1}.out": taps.__setitem__(key, a[0].detach().numpy().copy())))
+    with torch.no_grad():
+        out = model.encode(torch.from_numpy(audio))
+    for h in hooks:
+        h.remove()
+    mean = out.mean.numpy().astype(np.float32)
+    meta = dict(kind="encode", geom=geom.__dict__, init=init, wseed=wseed, B=B, L=L, aseed=aseed,
+                std=float(out.std), tap_names=sorted(taps.keys()))
+    arrs = {"mean": mean, "meta": np.array(json.dumps(meta))}
+    for k, v in taps.items():
+        arrs["tap:" + k] = tap_summary(v)
+    np.savez(os.path.join(GOLD, name + ".npz"), **arrs)
+    print(f"{name}: mean {mean.shape} peak {np.abs(mean).max():.4g} rms {np.sqrt((mean**2).mean()):.4g}  ({time.time()-t0:.1f}s)")
+
+
+def main_encoder():
+    """Encoder fixtures: ragged lengths exercise the right extra padding of every strided conv
+    (:127-133); an exact multiple of the hop exercises the no-padding path; default init pins the real init scale."""
+    os.makedirs(GOLD, exist_ok=True)
+    encoder_case("enc_full_stress_L6500", FULL, "stress", 4321, 1, 3200 * 2 + 100, 5)
+    encoder_case("enc_full_mild_B2_L12800", FULL, "mild", 99, 2, 3200 * 4, 6)
+    encoder_case("enc_full_default_L9999", FULL, "default", 0, 1, 9999, 7)
+    encoder_case("enc_full_stress_L1", FULL, "stress", 4321, 2, 1, 8)            # shorter than every kernel
+    encoder_case("enc_tiny_stress_L10117", TINY, "stress", 7, 2, 3200 * 3 + 517, 5)
+    # semantic tokenizer shape (N1): same encoder class with vae_dim 128
+    encoder_case("enc_sem128_stress_L7001", DecoderGeometry(vae_dim=128, depths=(2, 1, 1, 1, 1, 1, 2)), "stress", 11, 1, 7001, 9)
+
+
 def main():
+    if "--encoder-only" in sys.argv:
+        return main_encoder()
     os.makedirs(GOLD, exist_ok=True)
     # --- full geometry -------------------------------------------------------------------
     model, _ = offline_case("full_stress_T6", FULL, "stress", 1234, 1, 6, 11)
@@ -143,6 +188,7 @@ def main():
     streaming_case("tiny_stress_stream", TINY, "stress", 5, sched, 22, 4, model=model)
     # T == vae_dim layout ambiguity (:1102): [B, T, D] with T == D is read as [B, D, T]
     offline_case("tiny_stress_T16_ambiguous", TINY, "stress", 5, 1, 16, 15, with_taps=False)
+    main_encoder()
 
 
 if __name__ == "__main__":

@@ -82,6 +82,50 @@ class DecoderGeometry:
         specs.append(("decoder.head.conv.conv.bias", (self.channels,), "bias"))
         return specs
 
+    # ---- encoder (mirror stack, TokenizerEncoder :687-813) --------------------------------------------
+    def enc_stage_channels(self, i: int) -> int:
+        """channels of encoder stage i (:737-738, :765): n_filters * 2^i = decoder stage n-1-i"""
+        return self.n_filters * (2 ** i)
+
+    def enc_depth(self, i: int) -> int:
+        """encoder depths are the decoder's reversed (:1019-1028)"""
+        return self.depths[self.n_stages - 1 - i]
+
+    def enc_ratio(self, i: int) -> int:
+        """stride of the downsampling conv INTO encoder stage i >= 1: reversed(config.ratios)[i-1] (:701)"""
+        return self.ratios[self.n_stages - 1 - i]
+
+    def encoder_tensor_specs(self) -> List[Tuple[str, Tuple[int, ...], str]]:
+        """(state-dict name, shape, kind) of every encoder parameter, canonical order (names verified against
+        ``named_parameters()`` of the reference)."""
+        specs: List[Tuple[str, Tuple[int, ...], str]] = []
+        k = self.kernel_size
+        specs.append(("encoder.downsample_layers.0.0.conv.conv.weight", (self.n_filters, self.channels, k), "conv_w"))
+        specs.append(("encoder.downsample_layers.0.0.conv.conv.bias", (self.n_filters,), "bias"))
+        for i in range(self.n_stages):
+            c = self.enc_stage_channels(i)
+            if i > 0:
+                r = self.enc_ratio(i)
+                p = f"encoder.downsample_layers.{i}.0.conv.conv."
+                specs.append((p + "weight", (c, c // 2, 2 * r), "conv_w"))
+                specs.append((p + "bias", (c,), "bias"))
+            for j in range(self.enc_depth(i)):
+                p = f"encoder.stages.{i}.{j}."
+                specs.append((p + "gamma", (c,), "gamma"))
+                specs.append((p + "ffn_gamma", (c,), "gamma"))
+                specs.append((p + "norm.weight", (c,), "norm_w"))
+                specs.append((p + "ffn_norm.weight", (c,), "norm_w"))
+                specs.append((p + "mixer.conv.conv.conv.weight", (c, 1, k), "conv_w"))
+                specs.append((p + "mixer.conv.conv.conv.bias", (c,), "bias"))
+                specs.append((p + "ffn.linear1.weight", (self.ffn_expansion * c, c), "linear_w"))
+                specs.append((p + "ffn.linear1.bias", (self.ffn_expansion * c,), "bias"))
+                specs.append((p + "ffn.linear2.weight", (c, self.ffn_expansion * c), "linear_w"))
+                specs.append((p + "ffn.linear2.bias", (c,), "bias"))
+        cl = self.enc_stage_channels(self.n_stages - 1)
+        specs.append(("encoder.head.conv.conv.weight", (self.vae_dim, cl, k), "conv_w"))
+        specs.append(("encoder.head.conv.conv.bias", (self.vae_dim,), "bias"))
+        return specs
+
     def receptive_field_frames(self) -> int:
         """Left context, in latent frames, that influences an output sample.
 

@@ -251,6 +251,73 @@ class OracleDecoder:
 
 
 # --------------------------------------------------------------------------------------
+# the encoder walk (offline form)
+# --------------------------------------------------------------------------------------
+def sconv1d_strided(x: np.ndarray, w: np.ndarray, b: np.ndarray, stride: int) -> np.ndarray:
+    """SConv1d with stride, causal, pad_mode 'constant', non-streaming (:384-418).
+
+    padding_total = (k-1) - (stride-1) zeros on the left (:282), extra_padding zeros on the right so the last
+    window is complete (get_extra_padding_for_conv1d :127-133); then nn.Conv1d(stride).  [B,Cin,L] -> [B,Cout,ceil]
+    """
+    B, Cin, L = x.shape
+    Cout, _, k = w.shape
+    pt = (k - 1) - (stride - 1)
+    n_frames = (L - k + pt) / stride + 1
+    ideal = (math.ceil(n_frames) - 1) * stride + (k - pt)
+    extra = ideal - L
+    xp = np.pad(x, ((0, 0), (0, 0), (pt, extra)))
+    To = (xp.shape[2] - k) // stride + 1
+    y = np.zeros((B, Cout, To), dtype=F32)
+    for j in range(k):
+        y += np.matmul(w[:, :, j], xp[:, :, j:j + (To - 1) * stride + 1:stride])
+    return y + b[None, :, None]
+
+
+class OracleEncoder:
+    """TokenizerEncoder.forward (:810-813) + VibeVoiceAcousticTokenizerModel.encode (:1081-1085), offline."""
+
+    def __init__(self, weights: Dict[str, np.ndarray], geom: DecoderGeometry = FULL):
+        self.g = geom
+        self.w = {k: np.ascontiguousarray(v, dtype=F32) for k, v in weights.items()}
+
+    def _block(self, i, j, x, taps):
+        g, w = self.g, self.w
+        p = f"encoder.stages.{i}.{j}."
+        r = x                                                       # mixer half (:788-794)
+        h = rms_norm_channels(x, w[p + "norm.weight"], g.eps)
+        h = sconv1d(h, w[p + "mixer.conv.conv.conv.weight"], w[p + "mixer.conv.conv.conv.bias"], x.shape[1])[0]
+        x = r + h * w[p + "gamma"][None, :, None]
+        r = x                                                       # ffn half (:796-804)
+        h = rms_norm_channels(x, w[p + "ffn_norm.weight"], g.eps)
+        h = ffn(h.transpose(0, 2, 1), w[p + "ffn.linear1.weight"], w[p + "ffn.linear1.bias"],
+                w[p + "ffn.linear2.weight"], w[p + "ffn.linear2.bias"]).transpose(0, 2, 1)
+        x = r + h * w[p + "ffn_gamma"][None, :, None]
+        if taps is not None:
+            taps[p + "out"] = x
+        return x
+
+    def encode(self, audio: np.ndarray, taps: Optional[dict] = None) -> np.ndarray:
+        """audio [B, 1, L] (or [B, L]) -> mean [B, ceil(L / hop), vae_dim]  (:1084 permutes to [B, T, D])."""
+        g, w = self.g, self.w
+        x = np.asarray(audio, dtype=F32)
+        if x.ndim == 2:
+            x = x[:, None, :]
+        for i in range(g.n_stages):                                 # :775-806
+            p = f"encoder.downsample_layers.{i}.0.conv.conv."
+            if i == 0:
+                x = sconv1d(x, w[p + "weight"], w[p + "bias"])[0]    # stem k7 stride 1 (:732-734)
+            else:
+                x = sconv1d_strided(x, w[p + "weight"], w[p + "bias"], g.enc_ratio(i))   # k = 2r, stride r (:737-743)
+            if taps is not None:
+                taps[f"down{i}"] = x
+            for j in range(g.enc_depth(i)):
+                x = self._block(i, j, x, taps)
+        # self.norm is Identity (disable_last_norm, :767-770); head k7 (:771, :812)
+        x = sconv1d(x, w["encoder.head.conv.conv.weight"], w["encoder.head.conv.conv.bias"])[0]
+        return np.ascontiguousarray(x.transpose(0, 2, 1))
+
+
+# --------------------------------------------------------------------------------------
 # parity metrics (SURVEY.md §8c tolerance protocol)
 # --------------------------------------------------------------------------------------
 def parity_metrics(test: np.ndarray, ref: np.ndarray) -> Dict[str, float]:

@@ -89,6 +89,40 @@ def make_weights(geom: DecoderGeometry = FULL, init: str = "stress", seed: int =
     return out
 
 
+def make_encoder_weights(geom: DecoderGeometry = FULL, init: str = "stress", seed: int = 4321,
+                         bf16_round: bool = True) -> Dict[str, np.ndarray]:
+    """name -> fp32 ndarray for every ENCODER parameter (same distributions as make_weights)."""
+    assert init in ("stress", "default", "mild")
+    out: Dict[str, np.ndarray] = {}
+    for idx, (name, shape, kind) in enumerate(geom.encoder_tensor_specs()):
+        g = _rng(seed, idx)
+        n = int(np.prod(shape))
+        if kind in ("conv_w", "linear_w"):
+            fan_in = shape[1] if kind == "linear_w" else shape[1] * shape[2]
+            scale = 0.01 if init == "default" else 1.0 / np.sqrt(fan_in)
+            w = g.standard_normal(n, dtype=np.float32) * np.float32(scale)
+        elif kind == "bias":
+            w = np.zeros(n, dtype=np.float32) if init == "default" else \
+                g.standard_normal(n, dtype=np.float32) * np.float32(0.1)
+        elif kind == "norm_w":
+            w = np.ones(n, dtype=np.float32) if init == "default" else g.uniform(0.5, 1.5, size=n).astype(np.float32)
+        else:  # gamma
+            w = np.full(n, 1e-6, dtype=np.float32) if init == "default" else \
+                (g.uniform(0.05, 0.3, size=n) if init == "mild" else g.uniform(0.5, 1.5, size=n)).astype(np.float32)
+        w = w.reshape(shape)
+        out[name] = round_to_bf16(w) if bf16_round else w
+    return out
+
+
+def make_audio(B: int, L: int, seed: int = 5, bf16_round: bool = True) -> np.ndarray:
+    """[B, 1, L] synthetic audio: 0.1 * N(0,1), lightly low-passed."""
+    g = _rng(seed, 1 << 21)
+    x = g.standard_normal(B * (L + 4), dtype=np.float32).reshape(B, L + 4) * np.float32(0.1)
+    x = (x[:, 0:L] + 2 * x[:, 1:L + 1] + 3 * x[:, 2:L + 2] + 2 * x[:, 3:L + 3] + x[:, 4:L + 4]) / np.float32(9.0)
+    x = x.reshape(B, 1, L).astype(np.float32)
+    return round_to_bf16(x) if bf16_round else x
+
+
 def make_latents(B: int, T: int, dim: int = 64, seed: int = 1, bf16_round: bool = True) -> np.ndarray:
     """[B, T, dim] N(0,1) latents (SURVEY.md §8d synthetic inputs)."""
     g = _rng(seed, 1 << 20)

@@ -40,7 +40,9 @@ struct BlockFusedArgs {
   const float* b1;           // [4C]  (pre-scaled by 0.5 like W1, see epilogue.cuh)
   const float* b2;           // [C]
   const float* ffn_gamma;    // [C]
-  __nv_bfloat16* out_bf16;   // optional: [nbatch, rows_pb + 1, C], row 0 of each item is the upsampler halo
+  __nv_bfloat16* out_bf16;   // optional padded bf16 copy: [nbatch, ob_rpb, C], row t of an item lands at row ob_off + t
+  long long ob_rpb;          //   (decoder: ob_rpb = rows_pb + 1, ob_off = 1 = the upsampler halo row)
+  int ob_off;
   StateRef st;               // mixer context: fp32 [6][C] raw rows per stream (null base = offline)
 };
 
@@ -313,7 +315,7 @@ block_fused_kernel(const __grid_constant__ CUtensorMap tmO, const __grid_constan
       const int tile = (int)blockIdx.x + it * (int)gridDim.x;
       const int b = tile / p.tiles_pb, t = (tile - b * p.tiles_pb) * 128 + r;
       const bool valid = t < p.rows_pb;
-      const long long brow = (long long)b * (p.rows_pb + 1) + 1 + t;
+      const long long brow = (long long)b * p.ob_rpb + p.ob_off + t;
       mbar_wait(&y_full[sy], (uint32_t)((it / NY) & 1));
       mbar_wait(&d2_full[d2b], (uint32_t)((it >> 1) & 1));
       tc_fence_after();

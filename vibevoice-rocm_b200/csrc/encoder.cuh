@@ -1,0 +1,95 @@
+// encoder.cuh — the two small HBM-bound kernels the ENCODER path adds around the shared Block1D / GEMM kernels:
+// the stem SConv1d(1 -> 32, k7) and the zero padding of the bf16 operand copies the strided convolutions read.
+//
+// Reference: TokenizerEncoder (vibevoice/modular/modular_vibevoice_tokenizer.py:687-813).  The encoder walks the
+// decoder's stage list backwards (C = 32 ... 2048), so every Block1D launch is the decoder's kernel for that C;
+// the strided SConv1d(C/2 -> C, k = 2r, stride r) between stages (:737-743) has NON-overlapping taps in units of
+// r rows, so on a bf16 copy laid out as [item, (rows_out + 1) * r, C/2] — r zero rows in front (the causal left
+// pad, :282, :398-403), the stage output, then zero rows up to a multiple of r (get_extra_padding_for_conv1d,
+// :127-133) — it is exactly the 2-tap implicit GEMM the upsampler already uses, with K_tap = r * C/2:
+//     out[q] = b + W[:, 0:r*Cin] . xb[q] + W[:, r*Cin:2r*Cin] . xb[q + 1]       (xb rows of r*Cin elements)
+// The head SConv1d(2048 -> 64, k7) (:771, :812) is the 7-tap GEMM of the decoder's stem on a copy with 6 zero
+// rows in front.
+#pragma once
+#include <cuda_bf16.h>
+#include <stdint.h>
+
+namespace vv {
+
+// ---- stem: x[t][co] = b[co] + sum_j w[co][0][j] * audio[t - 6 + j]  (:732-734, causal left zero pad) ---------
+struct EncStemArgs {
+  const void* audio;          // [nbatch, L] fp32 or bf16
+  int audio_is_bf16;
+  long long audio_bstride;    // elements between items
+  const float* w;             // [7][32] tap-major
+  const float* b;             // [32]
+  float* x;                   // [nbatch, L, 32] fp32
+  int nbatch, L;
+};
+
+constexpr int ENC_STEM_ROWS = 4;   // rows per thread (the 10-sample window is shared between them)
+
+__global__ void __launch_bounds__(256) enc_stem_kernel(const EncStemArgs p) {
+  constexpr int C = 32, Q = C / 4, RT = ENC_STEM_ROWS;
+  const int quad = threadIdx.x % Q;                 // 4 channels of a row
+  float4 w[7];
+#pragma unroll
+  for (int j = 0; j < 7; ++j) w[j] = *reinterpret_cast<const float4*>(p.w + j * C + quad * 4);
+  const float4 bias = *reinterpret_cast<const float4*>(p.b + quad * 4);
+  const long long groups_pb = ((long long)p.L + RT - 1) / RT;          // groups of RT consecutive rows
+  const long long total = groups_pb * p.nbatch * Q;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const long long g = i / Q;
+    const int b = (int)(g / groups_pb);
+    const long long t0 = (g - (long long)b * groups_pb) * RT;
+    const long long base = (long long)b * p.audio_bstride;
+    float win[6 + RT];
+#pragma unroll
+    for (int k = 0; k < 6 + RT; ++k) {
+      const long long t = t0 - 6 + k;
+      float v = 0.f;
+      if (t >= 0 && t < p.L)
+        v = p.audio_is_bf16 ? __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(p.audio)[base + t])
+                            : reinterpret_cast<const float*>(p.audio)[base + t];
+      win[k] = v;
+    }
+    float* xo = p.x + ((long long)b * p.L + t0) * C + quad * 4;
+#pragma unroll
+    for (int r = 0; r < RT; ++r) {
+      if (t0 + r >= p.L) break;
+      float4 acc = bias;
+#pragma unroll
+      for (int j = 0; j < 7; ++j) {
+        acc.x = fmaf(w[j].x, win[r + j], acc.x);
+        acc.y = fmaf(w[j].y, win[r + j], acc.y);
+        acc.z = fmaf(w[j].z, win[r + j], acc.z);
+        acc.w = fmaf(w[j].w, win[r + j], acc.w);
+      }
+      *reinterpret_cast<float4*>(xo + (long long)r * C) = acc;
+    }
+  }
+}
+
+// ---- zero the pad rows of a padded bf16 copy [nbatch, rpb, C]: rows [0, off) and [off + rows, rpb) ------------
+struct EncPadArgs {
+  __nv_bfloat16* xb;
+  int nbatch, rows, off, C;
+  long long rpb;
+};
+
+__global__ void __launch_bounds__(256) enc_pad_kernel(const EncPadArgs p) {
+  const int c8 = p.C / 8;                                   // 16-byte cells per row
+  const long long pad_rows = p.rpb - p.rows;                // per item
+  const long long total = pad_rows * p.nbatch * c8;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const long long cell = i % c8, pr = i / c8;
+    const long long b = pr / pad_rows;
+    long long row = pr - b * pad_rows;
+    if (row >= p.off) row += p.rows;                        // tail pad
+    *reinterpret_cast<uint4*>(p.xb + (b * p.rpb + row) * p.C + cell * 8) = make_uint4(0u, 0u, 0u, 0u);
+  }
+}
+
+}  // namespace vv

@@ -34,7 +34,9 @@ struct FfnFusedArgs {
   const float* gamma;      // [C]
   const float* resid;      // [R, C] fp32
   float* out;              // [R, C] fp32 (may alias resid)
-  __nv_bfloat16* out_bf16; // optional: [batch, rows_pb + 1, C], row 0 of each item is the upsampler halo
+  __nv_bfloat16* out_bf16; // optional padded bf16 copy: [batch, ob_rpb, C], row t of an item lands at row ob_off + t
+  long long ob_rpb;        //   (decoder: ob_rpb = rows_pb + 1, ob_off = 1 = the upsampler halo row)
+  int ob_off;
 };
 
 template <int C>
@@ -266,7 +268,7 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       long long brow = 0;
       if (p.out_bf16 != nullptr && valid) {
         const long long b = m / p.rows_pb;
-        brow = b * (p.rows_pb + 1) + 1 + (m - b * p.rows_pb);
+        brow = b * p.ob_rpb + p.ob_off + (m - b * p.rows_pb);
       }
       mbar_wait(&r_full[sr], (uint32_t)((it / NR) & 1));
       mbar_wait(&d2_full[d2b], (uint32_t)((it >> 1) & 1));

@@ -313,7 +313,7 @@ ffn_stream_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       long long brow = 0;
       if (p.out_bf16 != nullptr && valid) {
         const long long b = m / p.rows_pb;
-        brow = b * (p.rows_pb + 1) + 1 + (m - b * p.rows_pb);
+        brow = b * p.ob_rpb + p.ob_off + (m - b * p.rows_pb);
       }
       mbar_wait(&d2_full[d2b], (uint32_t)((it >> 1) & 1));
       tc_fence_after();

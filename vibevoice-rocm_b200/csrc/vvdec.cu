@@ -13,6 +13,7 @@
 #include "ffn_stream.cuh"
 #include "block_fused.cuh"
 #include "gemm_tc2.cuh"
+#include "encoder.cuh"
 
 namespace vv {
 
@@ -148,9 +149,8 @@ extern "C" const char* vv_status_string(int32_t s) {
 // =====================================================================================================
 static int stage_channels(const vv_config& c, int i) { return c.n_filters << (c.n_stages - 1 - i); }
 
-extern "C" int32_t vv_decoder_create(const vv_config* cfg, vv_decoder** out) {
-  if (cfg == nullptr || out == nullptr) { set_error("null argument"); return VV_ERR_INVALID_ARG; }
-  *out = nullptr;
+// geometry / device checks shared by the decoder and the encoder (which mirrors the same config, :1019-1028)
+static int32_t init_core(const vv_config* cfg, vv_decoder* d) {
   if (cfg->n_stages < 2 || cfg->n_stages > VV_MAX_STAGES || cfg->kernel_size != 7) {
     set_error("unsupported geometry: n_stages=%d kernel_size=%d (path implements k=7, 2..%d stages)",
               cfg->n_stages, cfg->kernel_size, VV_MAX_STAGES);
@@ -176,7 +176,6 @@ extern "C" int32_t vv_decoder_create(const vv_config* cfg, vv_decoder** out) {
     set_error("device %d is sm_%d%d; this library only contains sm_100a code", cfg->device, prop.major, prop.minor);
     return VV_ERR_NO_DEVICE;
   }
-  vv_decoder* d = new vv_decoder();
   d->cfg = *cfg;
   d->hop = 1;
   for (int i = 0; i + 1 < cfg->n_stages; ++i) d->hop *= cfg->ratios[i];
@@ -189,9 +188,19 @@ extern "C" int32_t vv_decoder_create(const vv_config* cfg, vv_decoder** out) {
   }
   ctx += 6.0 / d->hop;
   d->halo = (int)std::ceil(ctx - 1e-9);
+  return VV_OK;
+}
+
+extern "C" int32_t vv_decoder_create(const vv_config* cfg, vv_decoder** out) {
+  if (cfg == nullptr || out == nullptr) { set_error("null argument"); return VV_ERR_INVALID_ARG; }
+  *out = nullptr;
+  vv_decoder* d = new vv_decoder();
+  const int32_t rc = init_core(cfg, d);
+  if (rc != VV_OK) { delete d; return rc; }
   *out = d;
   return VV_OK;
 }
+
 
 extern "C" int32_t vv_decoder_destroy(vv_decoder* d) {
   if (d == nullptr) return VV_OK;
@@ -211,11 +220,11 @@ extern "C" int64_t vv_decoder_take_launch_count(vv_decoder* d) {
   return n;
 }
 
-extern "C" int32_t vv_decoder_load_tensor(vv_decoder* d, const char* name, const void* data, int32_t dtype,
-                                          const int64_t* shape, int32_t ndim, int32_t is_device) {
+static int32_t stage_tensor(vv_decoder* d, const char* prefix, const char* name, const void* data, int32_t dtype,
+                            const int64_t* shape, int32_t ndim, int32_t is_device) {
   if (!d || !name || !data || !shape || ndim < 1 || ndim > 3) { set_error("bad argument"); return VV_ERR_INVALID_ARG; }
   if (dtype != VV_F32 && dtype != VV_BF16) { set_error("dtype %d", dtype); return VV_ERR_BAD_DTYPE; }
-  if (strncmp(name, "decoder.", 8) != 0) { set_error("'%s' is not a decoder parameter", name); return VV_ERR_UNKNOWN_TENSOR; }
+  if (strncmp(name, prefix, strlen(prefix)) != 0) { set_error("'%s' is not a '%s*' parameter", name, prefix); return VV_ERR_UNKNOWN_TENSOR; }
   int64_t n = 1;
   for (int i = 0; i < ndim; ++i) n *= shape[i];
   const size_t esz = dtype == VV_F32 ? 4 : 2;
@@ -240,6 +249,11 @@ extern "C" int32_t vv_decoder_load_tensor(vv_decoder* d, const char* name, const
   d->staged_shape[name].assign(shape, shape + ndim);
   d->finalized = false;
   return VV_OK;
+}
+
+extern "C" int32_t vv_decoder_load_tensor(vv_decoder* d, const char* name, const void* data, int32_t dtype,
+                                          const int64_t* shape, int32_t ndim, int32_t is_device) {
+  return stage_tensor(d, "decoder.", name, data, dtype, shape, ndim, is_device);
 }
 
 // =====================================================================================================
@@ -294,12 +308,51 @@ struct Packer {
     const uint32_t box[2] = {(uint32_t)w.BK, (uint32_t)w.BN};
     status = encode_map(&w.tm, w.w, 2, dims, strides, box);
   }
+  // one Block1D (:915-945) under state-dict prefix p: folded mixer vectors + the two FFN GEMM operands
+  bool block(const std::string& p, int C, BlockW& bw);
 };
 
 std::vector<uint16_t> to_bf16(const std::vector<float>& v) {
   std::vector<uint16_t> o(v.size());
   for (size_t i = 0; i < v.size(); ++i) o[i] = f32_to_bf16_rne(v[i]);
   return o;
+}
+
+bool Packer::block(const std::string& p, int C, BlockW& bw) {
+  const auto* g = get(p + "gamma", {C});
+  const auto* fg = get(p + "ffn_gamma", {C});
+  const auto* nw = get(p + "norm.weight", {C});
+  const auto* fnw = get(p + "ffn_norm.weight", {C});
+  const auto* dw = get(p + "mixer.conv.conv.conv.weight", {C, 1, 7});
+  const auto* db = get(p + "mixer.conv.conv.conv.bias", {C});
+  const auto* w1 = get(p + "ffn.linear1.weight", {4 * C, C});
+  const auto* b1 = get(p + "ffn.linear1.bias", {4 * C});
+  const auto* w2 = get(p + "ffn.linear2.weight", {C, 4 * C});
+  const auto* b2 = get(p + "ffn.linear2.bias", {C});
+  if (status != VV_OK) return false;
+  std::vector<float> dwt((size_t)7 * C);                 // tap-major [7][C]
+  for (int ch = 0; ch < C; ++ch)
+    for (int t = 0; t < 7; ++t) dwt[(size_t)t * C + ch] = (*dw)[(size_t)ch * 7 + t];
+  bw.gamma = upload(*g);
+  bw.ffn_gamma = upload(*fg);
+  bw.norm_w = upload(*nw);
+  bw.ffn_norm_w = upload(*fnw);
+  bw.dw_w = upload(dwt);
+  bw.dw_b = upload(*db);
+  {  // linear1 is packed PRE-SCALED by 0.5 (exact): every GELU epilogue works on z = x/2 (epilogue.cuh)
+    std::vector<float> w1h(*w1), b1h(*b1);
+    for (float& v : w1h) v *= 0.5f;
+    for (float& v : b1h) v *= 0.5f;
+    dense(bw.lin1, to_bf16(w1h), b1h, 4 * C, C, 1);
+  }
+  dense(bw.lin2, to_bf16(*w2), *b2, C, 4 * C, 1);
+  if (status == VV_OK && C == 128) {   // ffn_stream_kernel reads linear1 in chunks of 64 hidden units
+    const uint64_t dims[2] = {(uint64_t)C, (uint64_t)(4 * C)};
+    const uint64_t strides[1] = {(uint64_t)C * 2};
+    const uint32_t box[2] = {64u, 64u};
+    status = encode_map(&bw.tm_w1s, bw.lin1.w, 2, dims, strides, box);
+  }
+  return status == VV_OK;
 }
 
 }  // namespace
@@ -368,39 +421,7 @@ extern "C" int32_t vv_decoder_finalize(vv_decoder* d) {
     for (int j = 0; j < c.depths[i] && pk.status == VV_OK; ++j) {
       const std::string p = "decoder.stages." + std::to_string(i) + "." + std::to_string(j) + ".";
       BlockW bw;
-      const auto* g = pk.get(p + "gamma", {C});
-      const auto* fg = pk.get(p + "ffn_gamma", {C});
-      const auto* nw = pk.get(p + "norm.weight", {C});
-      const auto* fnw = pk.get(p + "ffn_norm.weight", {C});
-      const auto* dw = pk.get(p + "mixer.conv.conv.conv.weight", {C, 1, 7});
-      const auto* db = pk.get(p + "mixer.conv.conv.conv.bias", {C});
-      const auto* w1 = pk.get(p + "ffn.linear1.weight", {4 * C, C});
-      const auto* b1 = pk.get(p + "ffn.linear1.bias", {4 * C});
-      const auto* w2 = pk.get(p + "ffn.linear2.weight", {C, 4 * C});
-      const auto* b2 = pk.get(p + "ffn.linear2.bias", {C});
-      if (pk.status != VV_OK) break;
-      std::vector<float> dwt((size_t)7 * C);                 // tap-major [7][C]
-      for (int ch = 0; ch < C; ++ch)
-        for (int t = 0; t < 7; ++t) dwt[(size_t)t * C + ch] = (*dw)[(size_t)ch * 7 + t];
-      bw.gamma = pk.upload(*g);
-      bw.ffn_gamma = pk.upload(*fg);
-      bw.norm_w = pk.upload(*nw);
-      bw.ffn_norm_w = pk.upload(*fnw);
-      bw.dw_w = pk.upload(dwt);
-      bw.dw_b = pk.upload(*db);
-      {  // linear1 is packed PRE-SCALED by 0.5 (exact): every GELU epilogue works on z = x/2 (epilogue.cuh)
-        std::vector<float> w1h(*w1), b1h(*b1);
-        for (float& v : w1h) v *= 0.5f;
-        for (float& v : b1h) v *= 0.5f;
-        pk.dense(bw.lin1, to_bf16(w1h), b1h, 4 * C, C, 1);
-      }
-      pk.dense(bw.lin2, to_bf16(*w2), *b2, C, 4 * C, 1);
-      if (pk.status == VV_OK && C == 128) {   // ffn_stream_kernel reads linear1 in chunks of 64 hidden units
-        const uint64_t dims[2] = {(uint64_t)C, (uint64_t)(4 * C)};
-        const uint64_t strides[1] = {(uint64_t)C * 2};
-        const uint32_t box[2] = {64u, 64u};
-        pk.status = encode_map(&bw.tm_w1s, bw.lin1.w, 2, dims, strides, box);
-      }
+      if (!pk.block(p, C, bw)) break;
       bw.state_off = soff;
       soff += 6LL * C * 4;
       st.blocks.push_back(bw);
@@ -452,6 +473,7 @@ struct EpiOut {
   float* out_f32 = nullptr;
   __nv_bfloat16* out_bf16 = nullptr;
   int bf16_halo = 0;            // out_bf16 rows per batch item = rows + bf16_halo, first bf16_halo rows skipped
+  long long bf16_rpb = 0;       // when > 0: rows per batch item of out_bf16 (overrides rows + bf16_halo)
 };
 
 template <int BN, int BK>
@@ -484,7 +506,7 @@ int launch_gemm_impl(vv_decoder* d, const __nv_bfloat16* A, long long a_rpb, int
   g.rows = rows; g.nbatch = nbatch; g.n_taps = w.n_taps; g.kb_per_tap = w.Ktap / w.BK; g.N = w.N;
   g.epi = e.epi; g.bias = w.bias; g.gamma = e.gamma; g.resid = e.resid;
   g.out_f32 = e.out_f32; g.of_rpb = rows; g.of_off = 0;
-  g.out_bf16 = e.out_bf16; g.ob_rpb = rows + e.bf16_halo; g.ob_off = e.bf16_halo;
+  g.out_bf16 = e.out_bf16; g.ob_rpb = e.bf16_rpb > 0 ? e.bf16_rpb : rows + e.bf16_halo; g.ob_off = e.bf16_halo;
   const int nk = g.n_taps * g.kb_per_tap;
   const int per_stage = GEMM_BM * w.BK * 2 + w.BN * w.BK * 2;
   g.stages = std::max(1, std::min(std::min(nk, GEMM_MAX_STAGES), (96 * 1024) / per_stage));
@@ -590,9 +612,12 @@ bool ffn_fused_supported(const vv_decoder* d, int C) {
   return (d->cfg.gemm_path == 0 || d->cfg.gemm_path == 4) && (C == 32 || C == 64 || C == 128);
 }
 
+struct PadOut { long long rpb = 0; int off = 1; };   // padded bf16 copy geometry; rpb 0 = rows_pb + off
+
 int launch_ffn_fused(vv_decoder* d, int C, const BlockW& bw, const __nv_bfloat16* a, const float* resid, float* out,
-                     __nv_bfloat16* out_bf16, long long R, int rows_pb, cudaStream_t s) {
+                     __nv_bfloat16* out_bf16, long long R, int rows_pb, cudaStream_t s, PadOut po = PadOut()) {
   FfnFusedArgs fa;
+  fa.ob_rpb = po.rpb > 0 ? po.rpb : rows_pb + po.off; fa.ob_off = po.off;
   fa.R = R; fa.rows_pb = rows_pb; fa.b1 = bw.lin1.bias; fa.b2 = bw.lin2.bias; fa.gamma = bw.ffn_gamma;
   fa.resid = resid; fa.out = out; fa.out_bf16 = out_bf16;
   CUtensorMap tmA;
@@ -654,13 +679,15 @@ int launch_block_fused_inst(vv_decoder* d, const CUtensorMap& tmO, const BlockW&
 }
 
 int launch_block_fused(vv_decoder* d, int C, const BlockW& bw, const float* x, float* out, __nv_bfloat16* out_bf16,
-                       int nbatch, int rows_pb, vv_state* st, const int32_t* slots, cudaStream_t s) {
+                       int nbatch, int rows_pb, vv_state* st, const int32_t* slots, cudaStream_t s,
+                       PadOut po = PadOut()) {
   if (x == out) { set_error("block_fused: input and output must not alias"); return VV_ERR_INVALID_ARG; }
   BlockFusedArgs a;
   a.x = x; a.nbatch = nbatch; a.rows_pb = rows_pb; a.tiles_pb = (rows_pb + 127) / 128; a.eps = d->cfg.eps;
   a.norm_w = bw.norm_w; a.dw_w = bw.dw_w; a.dw_b = bw.dw_b; a.gamma = bw.gamma; a.ffn_norm_w = bw.ffn_norm_w;
   a.b1 = bw.lin1.bias; a.b2 = bw.lin2.bias; a.ffn_gamma = bw.ffn_gamma; a.out_bf16 = out_bf16;
   a.st = make_state_ref(st, slots, bw.state_off);
+  a.ob_rpb = po.rpb > 0 ? po.rpb : rows_pb + po.off; a.ob_off = po.off;
   if ((long long)nbatch * a.tiles_pb >= (1LL << 31) / 8) { set_error("block_fused: too many tiles"); return VV_ERR_BAD_SHAPE; }
   CUtensorMap tmO;                                   // output fp32 [nbatch, rows_pb, C], boxes of [128 rows, 32 floats]
   const uint64_t dims[3] = {(uint64_t)C, (uint64_t)rows_pb, (uint64_t)nbatch};
@@ -1142,3 +1169,8 @@ extern "C" int32_t vv_debug_read_trace(long long* host, int32_t n) {
   return (int32_t)cudaMemcpyFromSymbol(host, vv::vv_fs_trace, sizeof(long long) * (size_t)n);
 }
 #endif
+
+// =====================================================================================================
+// encoder path (TokenizerEncoder, :687-813)
+// =====================================================================================================
+#include "vvenc.inl"

@@ -1,9 +1,11 @@
-"""vvdec — B200-native (sm_100a) VibeVoice acoustic-tokenizer decoder behind the reference's decode() API.
+"""vvdec — B200-native (sm_100a) VibeVoice acoustic-tokenizer decoder behind the reference's decode() API
+(and the mirror encoder behind encode()).
 
 Importing this package loads libvvdec_b200.so; there is no CPU / PyTorch fallback.
 """
 from . import _capi
 from .decoder import B200AcousticDecoder, B200StreamingCache, Geometry, patch
+from .encoder import B200AcousticEncoder, B200TokenizerEncoderOutput
 from .shard import plan_shards, Shard
 
-__all__ = ["B200AcousticDecoder", "B200StreamingCache", "Geometry", "patch", "plan_shards", "Shard", "_capi"]
+__all__ = ["B200AcousticEncoder", "B200TokenizerEncoderOutput", "B200AcousticDecoder", "B200StreamingCache", "Geometry", "patch", "plan_shards", "Shard", "_capi"]

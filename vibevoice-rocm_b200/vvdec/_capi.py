@@ -38,7 +38,7 @@ class VvProfileRecord(C.Structure):
 
 
 KERNEL_KINDS = ("prep", "stem", "mixer", "ffn1", "ffn2", "halo", "upsample", "head", "state", "ffn_fused",
-                "block_fused")
+                "block_fused", "enc_stem", "downsample", "pad", "enc_head")
 
 # name -> (restype, argtypes): every symbol include/vvdec.h declares
 _P, _I32, _I64 = C.c_void_p, C.c_int32, C.c_int64
@@ -71,6 +71,18 @@ SIGNATURES = {
     "vv_kernel_upsample": (_I32, [_P, _I32, _P, _P, _I32, _I32, _P]),
     "vv_test_gelu": (_I32, [_P, _P, _I32, _P]),
     "vv_kernel_head": (_I32, [_P, _P, _P, _I32, _I32, _I32, _P]),
+    "vv_encoder_create": (_I32, [C.POINTER(VvConfig), C.POINTER(_P)]),
+    "vv_encoder_destroy": (_I32, [_P]),
+    "vv_encoder_load_tensor": (_I32, [_P, C.c_char_p, _P, _I32, C.POINTER(_I64), _I32, _I32]),
+    "vv_encoder_finalize": (_I32, [_P]),
+    "vv_encoder_param_count": (_I64, [_P]),
+    "vv_encoder_hop": (_I32, [_P]),
+    "vv_encoder_frames": (_I64, [_P, _I64]),
+    "vv_encoder_workspace_bytes": (_I64, [_P, _I32, _I64]),
+    "vv_encode": (_I32, [_P, _P, _I32, _I32, _I64, _P, _P, _I64, _P]),
+    "vv_encoder_take_launch_count": (_I64, [_P]),
+    "vv_encoder_set_profiling": (_I32, [_P, _I32]),
+    "vv_encoder_read_profile": (_I32, [_P, _P, _I32]),
 }
 
 _lib = None

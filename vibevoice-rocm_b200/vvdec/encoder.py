@@ -1,0 +1,192 @@
+"""Host-side mirror of the reference's ENCODE interface over the C ABI (include/vvdec.h, vv_encoder_* / vv_encode).
+
+Mirrors, by name and argument meaning:
+  * ``VibeVoiceAcousticTokenizerModel.encode(audio, cache=None, sample_indices=None, use_cache=False, debug=False)``
+    — vibevoice/modular/modular_vibevoice_tokenizer.py:1081-1085
+  * ``VibeVoiceTokenizerEncoderOutput`` (mean / std, ``sample``, ``kl``, ``mode``) — :954-1000
+  * ``VibeVoiceAcousticTokenizerModel.sampling`` — :1087-1097
+PyTorch is used for device memory, streams and the random draws of ``sample``; the encoder arithmetic runs in the
+CUDA library.  Offline form only: ``use_cache=True`` raises NotImplementedError (the streaming strided convs of
+SConv1d._forward_streaming are not built on this path yet).
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+from typing import Dict, Optional, Union
+
+import torch
+
+from . import _capi
+from .decoder import Geometry, _dtype_code
+
+
+@dataclass
+class B200TokenizerEncoderOutput:
+    """Gaussian with fixed std around ``mean`` [B, T, vae_dim] (VibeVoiceTokenizerEncoderOutput, :954-1000)."""
+    mean: torch.Tensor
+    std: Optional[Union[float, torch.Tensor]] = None
+
+    def sample(self, dist_type: str = "fix"):
+        if dist_type == "fix":                                                   # :976-978
+            return self.mean + self.std * torch.randn_like(self.mean), self.std
+        if dist_type == "gaussian":                                              # :979-988
+            value = self.std / 0.8
+            std = torch.randn(self.mean.size(0), device=self.mean.device, dtype=self.mean.dtype) * value
+            while std.dim() < self.mean.dim():
+                std = std.unsqueeze(-1)
+            return self.mean + std * torch.randn_like(self.mean), std
+        return self.mean, self.std                                               # :989-990
+
+    def kl(self):
+        return self.mean * self.mean                                             # mse against zeros, no reduction (:992-995)
+
+    def mode(self):
+        return self.mean
+
+
+class B200AcousticEncoder:
+    """Drop-in for the encode half of VibeVoiceAcousticTokenizerModel on one B200."""
+
+    def __init__(self, geometry: Geometry = Geometry(), device=None, gemm_path: int = 0,
+                 max_workspace_bytes: int = 24 << 30, fix_std: float = 0.5, std_dist_type: str = "gaussian"):
+        self._lib = _capi.load()
+        if not torch.cuda.is_available():
+            raise RuntimeError("vvdec needs a CUDA device (sm_100a); there is no CPU fallback")
+        self.device = torch.device("cuda", torch.cuda.current_device() if device is None else
+                                   (device if isinstance(device, int) else torch.device(device).index or 0))
+        self.geometry = geometry
+        if len(geometry.ratios) != len(geometry.depths) - 1 or len(geometry.depths) > _capi.VV_MAX_STAGES:
+            raise ValueError("geometry: len(ratios) must be len(depths) - 1 and at most 7")
+        cfg = _capi.VvConfig()
+        cfg.vae_dim, cfg.n_filters, cfg.n_stages = geometry.vae_dim, geometry.n_filters, len(geometry.depths)
+        for i, r in enumerate(geometry.ratios):
+            cfg.ratios[i] = r
+        for i, d in enumerate(geometry.depths):
+            cfg.depths[i] = d
+        cfg.kernel_size, cfg.eps, cfg.device, cfg.gemm_path = geometry.kernel_size, geometry.eps, self.device.index, gemm_path
+        h = C.c_void_p()
+        _capi.check(self._lib.vv_encoder_create(C.byref(cfg), C.byref(h)), "vv_encoder_create")
+        self._h = h
+        self.max_workspace_bytes = int(max_workspace_bytes)
+        self.fix_std = fix_std                       # config.fix_std (:1014)
+        self.std_dist_type = std_dist_type           # config.std_dist_type (:1015)
+        self._ws: Optional[torch.Tensor] = None
+        self.vae_dim = geometry.vae_dim
+        self.hop = geometry.hop
+
+    # -- weights -----------------------------------------------------------------------------------
+    def load_state_dict(self, sd: Dict[str, "torch.Tensor"], prefix: str = "") -> "B200AcousticEncoder":
+        """``sd`` uses the reference's names (``encoder.downsample_layers.0.0.conv.conv.weight`` ...), optionally
+        under ``prefix``; torch tensors (any device) or numpy arrays."""
+        n = 0
+        for k, v in sd.items():
+            if not k.startswith(prefix + "encoder."):
+                continue
+            t = torch.as_tensor(v)
+            if t.dtype not in (torch.float32, torch.bfloat16):
+                t = t.float()
+            t = t.detach().contiguous()
+            shape = (C.c_int64 * t.dim())(*t.shape)
+            _capi.check(self._lib.vv_encoder_load_tensor(self._h, k[len(prefix):].encode(), C.c_void_p(t.data_ptr()),
+                                                         _dtype_code(t.dtype), shape, t.dim(), 1 if t.is_cuda else 0),
+                        f"vv_encoder_load_tensor({k})")
+            n += 1
+        if n == 0:
+            raise ValueError(f"no '{prefix}encoder.*' tensors in the state dict")
+        _capi.check(self._lib.vv_encoder_finalize(self._h), "vv_encoder_finalize")
+        return self
+
+    @classmethod
+    def from_reference(cls, model, **kw) -> "B200AcousticEncoder":
+        """Build from a reference VibeVoiceAcousticTokenizerModel instance (weights are copied)."""
+        kw.setdefault("fix_std", getattr(model, "fix_std", 0.5))
+        kw.setdefault("std_dist_type", getattr(model, "std_dist_type", "gaussian"))
+        enc = cls(Geometry.from_config(model.config), **kw)
+        return enc.load_state_dict(model.state_dict())
+
+    @property
+    def param_count(self) -> int:
+        return int(self._lib.vv_encoder_param_count(self._h))
+
+    def frames(self, L: int) -> int:
+        return int(self._lib.vv_encoder_frames(self._h, int(L)))
+
+    def workspace_bytes(self, B: int, L: int) -> int:
+        return int(self._lib.vv_encoder_workspace_bytes(self._h, int(B), int(L)))
+
+    def set_profiling(self, enabled: bool) -> None:
+        _capi.check(self._lib.vv_encoder_set_profiling(self._h, 1 if enabled else 0), "vv_encoder_set_profiling")
+
+    def read_profile(self):
+        n = self._lib.vv_encoder_read_profile(self._h, None, 0)
+        buf = (_capi.VvProfileRecord * max(n, 1))()
+        n = min(n, self._lib.vv_encoder_read_profile(self._h, buf, n))
+        return [dict(kind=_capi.KERNEL_KINDS[buf[i].kind], stage=int(buf[i].stage), launches=int(buf[i].launches),
+                     ms=float(buf[i].ms)) for i in range(n)]
+
+    def take_launch_count(self) -> int:
+        return int(self._lib.vv_encoder_take_launch_count(self._h))
+
+    def _workspace(self, B: int, L: int) -> torch.Tensor:
+        need = min(self.workspace_bytes(B, L), max(self.max_workspace_bytes, self.workspace_bytes(1, L)))
+        if self._ws is None or self._ws.numel() < need + 1024:
+            self._ws = None
+            self._ws = torch.empty(need + 1024, dtype=torch.uint8, device=self.device)
+        return self._ws
+
+    # -- the reference entry points -------------------------------------------------------------------
+    @torch.no_grad()
+    def encode(self, audio, cache=None, sample_indices=None, use_cache=False, debug=False):
+        """Same contract as VibeVoiceAcousticTokenizerModel.encode (:1081-1085), offline form.
+
+        audio: [B, 1, L] (or [B, L]) float32 / bfloat16 on this encoder's device.  Returns
+        B200TokenizerEncoderOutput(mean [B, ceil(L / hop), vae_dim] in the audio's dtype, std=fix_std).
+        """
+        if use_cache and cache is not None:
+            raise NotImplementedError("streaming encode (use_cache=True) is not built on the B200 path; "
+                                      "encode whole utterances offline")
+        if not isinstance(audio, torch.Tensor) or audio.dim() not in (2, 3):
+            raise ValueError("audio must be a [B, 1, L] or [B, L] tensor")
+        if audio.dim() == 3:
+            if audio.shape[1] != 1:
+                raise ValueError(f"audio has {audio.shape[1]} channels; the tokenizer takes mono (channels=1)")
+            audio = audio[:, 0, :]
+        if not audio.is_cuda:
+            raise RuntimeError("audio must live on the CUDA device; vvdec has no CPU path")
+        if audio.dtype not in (torch.float32, torch.bfloat16):
+            audio = audio.float()
+        B, L = audio.shape
+        T = self.frames(L) if L > 0 else 0
+        if B == 0 or L == 0:
+            return B200TokenizerEncoderOutput(mean=audio.new_zeros((B, T, self.vae_dim)), std=self.fix_std)
+        audio = audio.contiguous()
+        mean = torch.empty((B, T, self.vae_dim), dtype=torch.float32, device=self.device)
+        ws = self._workspace(B, L)
+        ws_ptr = (ws.data_ptr() + 1023) & ~1023
+        ws_bytes = ws.numel() - (ws_ptr - ws.data_ptr())
+        stream = torch.cuda.current_stream(self.device).cuda_stream
+        rc = self._lib.vv_encode(self._h, C.c_void_p(audio.data_ptr()), _dtype_code(audio.dtype), int(B), int(L),
+                                 C.c_void_p(mean.data_ptr()), C.c_void_p(ws_ptr), int(ws_bytes), C.c_void_p(stream))
+        _capi.check(rc, "vv_encode")
+        self._keep = audio                              # alive until the stream has consumed it
+        return B200TokenizerEncoderOutput(mean=mean if audio.dtype == torch.float32 else mean.to(audio.dtype),
+                                          std=self.fix_std)
+
+    __call__ = encode
+
+    @torch.no_grad()
+    def sampling(self, encoder_output, dist_type=None):
+        """VibeVoiceAcousticTokenizerModel.sampling (:1087-1097)."""
+        dist_type = dist_type or self.std_dist_type
+        if dist_type not in ("fix", "gaussian"):
+            raise ValueError(f"Unsupported dist_type: {dist_type}, expected 'fix' or 'gaussian'")
+        return encoder_output.sample(dist_type=dist_type)
+
+    def __del__(self):
+        try:
+            if getattr(self, "_h", None):
+                self._lib.vv_encoder_destroy(self._h)
+                self._h = None
+        except Exception:
+            pass
