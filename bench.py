@@ -212,6 +212,109 @@ def streaming_leg(dec, geom, dev, n_streams=256, steps=300, warmup=30):
     return out
 
 
+def enc_kernel_work(geom, kind: str, stage: int):
+    """Encoder counterpart of kernel_work: per SAMPLE-ROW of the stage (not per frame) -> (bound, algorithmic bytes,
+    flop, bytes moved) per row.  Stage i has C = n_filters * 2^i channels."""
+    n = len(geom.depths)
+    C = geom.n_filters * 2 ** stage
+    if kind == "mixer":
+        return "hbm", 4 * C, 20 * C, 10 * C
+    if kind in ("ffn1", "ffn2"):
+        moved = (2 * C + 8 * C) if kind == "ffn1" else (8 * C + 4 * C + 4 * C)
+        return ("tensor" if C >= 128 else "hbm"), 2 * C, 8 * C * C, moved
+    if kind == "ffn_fused":
+        return ("tensor" if C >= 128 else "hbm"), 4 * C, 16 * C * C, 10 * C
+    if kind == "block_fused":
+        return "hbm", 8 * C, 20 * C + 16 * C * C, 8 * C
+    if kind == "downsample":   # per OUTPUT row: reads r rows of C/2 bf16, writes C fp32 (algorithmic: bf16 out)
+        r = geom.ratios[n - 1 - stage]
+        cin = C // 2
+        return ("tensor" if cin >= 256 else "hbm"), 2 * r * cin + 2 * C, 2 * 2 * r * cin * C, 2 * r * cin + 4 * C
+    if kind == "enc_stem":
+        return "hbm", 2 + 2 * C, 2 * 7 * C, 4 + 4 * C
+    if kind == "enc_head":
+        return "hbm", 2 * C + 2 * geom.vae_dim, 2 * 7 * C * geom.vae_dim, 2 * C + 4 * geom.vae_dim
+    return "hbm", 0, 0, 0
+
+
+def encoder_leg(geom, dev, pk, steps, warmup, B=32, L=720_000, kernels_out=""):
+    """BASELINE.json configs[4]: acoustic tokenizer ENCODER on voice prompts, batch 32 x 30 s, through
+    B200AcousticEncoder.encode (the C ABI's vv_encode).  Device-resident throughput, an end-to-end figure with pinned
+    host buffers, and the per-kernel table of one profiled pass."""
+    import torch
+    import vvdec
+    from vvdec.synthetic import random_encoder_state_dict
+    enc = vvdec.B200AcousticEncoder(geom, device=dev.index)
+    enc.load_state_dict(random_encoder_state_dict(geom))
+    gen = torch.Generator().manual_seed(5)
+    a_host = (torch.randn(B, 1, L, generator=gen) * 0.1).to(torch.bfloat16).pin_memory()
+    audio = a_host.to(dev)
+    T = enc.frames(L)
+    m_host = torch.empty((B, T, geom.vae_dim), dtype=torch.bfloat16).pin_memory()
+    for _ in range(max(2, warmup)):
+        enc.encode(audio)
+    torch.cuda.synchronize()
+    enc.take_launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        enc.encode(audio)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / steps
+    launches = enc.take_launch_count() // steps
+
+    def e2e_step():
+        m_host.copy_(enc.encode(a_host.to(dev, non_blocking=True)).mean, non_blocking=True)
+    e2e_step()
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(steps):
+        e2e_step()
+    e1.record()
+    torch.cuda.synchronize()
+    ms_e2e = e0.elapsed_time(e1) / steps
+    audio_s = B * L / 24000.0
+    enc.set_profiling(True)
+    enc.encode(audio)
+    prof = enc.read_profile()
+    enc.set_profiling(False)
+    total = sum(r["ms"] for r in prof) or 1.0
+    n = len(geom.depths)
+    rows_of = [L]
+    for i in range(1, n):
+        r = geom.ratios[n - 1 - i]
+        rows_of.append(-(-rows_of[-1] // r))
+    table = []
+    for r in prof:
+        bound, abytes, aflop, moved = enc_kernel_work(geom, r["kind"], r["stage"])
+        nl = max(1, r["launches"])
+        nblk = geom.depths[n - 1 - r["stage"]] if r["kind"] in ("mixer", "ffn1", "ffn2", "ffn_fused", "block_fused") else 1
+        passes = max(1, nl // nblk)
+        units = B * rows_of[r["stage"]] / passes
+        msl = r["ms"] / nl
+        table.append(dict(kind=r["kind"], stage=r["stage"], launches=nl, ms_total=r["ms"], share=r["ms"] / total,
+                          ms_per_launch=msl, rows_per_launch=units, bound=bound,
+                          gbs_algorithmic=abytes * units / (msl * 1e-3) / 1e9 if msl > 0 else 0.0,
+                          gbs_moved=moved * units / (msl * 1e-3) / 1e9 if msl > 0 else 0.0,
+                          tflops=aflop * units / (msl * 1e-3) / 1e12 if msl > 0 else 0.0))
+    table.sort(key=lambda r: -r["ms_total"])
+    top = table[0]
+    if kernels_out:
+        with open(kernels_out, "w") as f:
+            json.dump({"config": {"B": B, "L": L, "ms_per_step": ms}, "kernels": table}, f, indent=1)
+    del enc
+    return {"workload": f"acoustic tokenizer encoder, batch {B} x {L / 24000:.0f} s ({L} samples -> {T} frames), bf16 audio in",
+            "value": audio_s / (ms / 1e3), "unit": "encoded audio-s/s", "ms_per_step": ms, "gpu_launches": int(launches),
+            "e2e": {"value": audio_s / (ms_e2e / 1e3), "ms_per_step": ms_e2e, "h2d_bytes_per_step": a_host.numel() * 2,
+                    "d2h_bytes_per_step": m_host.numel() * 2},
+            "top_kernel": {"kernel": f"{top['kind']}@stage{top['stage']}", "share": top["share"], "bound": top["bound"],
+                           "ms_per_launch": top["ms_per_launch"],
+                           "achieved": top["tflops"] if top["bound"] == "tensor" else top["gbs_algorithmic"],
+                           "peak": pk["tf_sustained"] if top["bound"] == "tensor" else pk["hbm_gbs"],
+                           "unit": "TFLOP/s" if top["bound"] == "tensor" else "GB/s"}}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -223,6 +326,8 @@ def main():
     ap.add_argument("--workspace-gb", type=float, default=24.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-streaming", action="store_true")
+    ap.add_argument("--no-encoder", action="store_true")
+    ap.add_argument("--encoder-kernels-out", default="", help="per-kernel table of the encoder leg (JSON)")
     ap.add_argument("--kernels-out", default="", help="write the per-kernel timing table (JSON) here")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
@@ -346,6 +451,17 @@ def main():
         del y
         streaming = streaming_leg(dec, geom, dev)
 
+    # ---- encoder leg (BASELINE.json configs[4]) ---------------------------------------------------------
+    encoder = None
+    if not args.no_encoder:
+        y = None
+        dec._ws = None                                          # release the decode workspace
+        torch.cuda.empty_cache()
+        try:
+            encoder = encoder_leg(geom, dev, pk, args.steps, args.warmup, kernels_out=args.encoder_kernels_out)
+        except Exception as e:                                  # report, do not hide
+            encoder = {"error": f"{type(e).__name__}: {e}"[:300]}
+
     # ---- CPU baseline (reported, not the target): bounded sample on the host cores -----------------
     cpu = None
     if not args.no_cpu_baseline:
@@ -363,7 +479,7 @@ def main():
                    "l2": "inputs >> L2 (each pass streams >700 MB of activations per utterance group)",
                    "sharding": "utterances per rank, no data-path collective"},
         "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roof, "cpu_baseline": cpu,
-        "streaming": streaming,
+        "streaming": streaming, "encoder": encoder,
     }
     print(json.dumps(line), flush=True)
     if world > 1:
