@@ -81,8 +81,8 @@ struct BlockFusedCfg {
   // with (threads x launch registers), not the whole register file: with 768 threads x 80 registers a 144-register
   // mixer (total 65536) hung on B200, 128 (total 61440) runs.
   static constexpr int REG_LAUNCH = (65536 / THREADS) / 8 * 8;      // what __launch_bounds__(THREADS, 1) yields
-  static constexpr int REG_E = 64, REG_CTRL = 32, REG_MX = (C == 64) ? 128 : 168;
-  static_assert(32 * ((BF_E1_WARPS + BF_E2_WARPS) * REG_E + 4 * REG_CTRL + MXW * REG_MX) <= THREADS * REG_LAUNCH,
+  static constexpr int REG_E = 64, REG_E2 = 64, REG_CTRL = 32, REG_MX = (C == 64) ? 128 : 168;   // (136 / 56 / 24 at C = 64: spill-free mixer, not faster)
+  static_assert(32 * (BF_E1_WARPS * REG_E + BF_E2_WARPS * REG_E2 + 4 * REG_CTRL + MXW * REG_MX) <= THREADS * REG_LAUNCH,
                 "setmaxnreg budget exceeds the CTA's launch allocation");
 };
 
@@ -111,7 +111,9 @@ __device__ __forceinline__ float group_sum1(float s) {
   return s;
 }
 
-template <int C>
+// STATE = false is the offline form (no stream context): the context pointers and their per-row checks are compiled
+// out of the mixer loop (they cost registers and tie their spill reloads to the scoreboards of the prefetch loads).
+template <int C, bool STATE>
 __global__ void __launch_bounds__(BlockFusedCfg<C>::THREADS, 1)
 block_fused_kernel(const __grid_constant__ CUtensorMap tmO, const __grid_constant__ CUtensorMap tmW1,
                    const __grid_constant__ CUtensorMap tmW2, const BlockFusedArgs p) {
@@ -198,7 +200,7 @@ block_fused_kernel(const __grid_constant__ CUtensorMap tmO, const __grid_constan
         int g = 0;
         for (int it = 0; it < my_tiles; ++it) {
           const int sa = it % NA;
-          mbar_wait(&a_full[sa], (uint32_t)((it / NA) & 1));
+          mbar_wait_sleep(&a_full[sa], (uint32_t)((it / NA) & 1), 64);
           const uint64_t da = da0 + (uint64_t)((sa * L::A_BYTES) >> 4);
 #pragma unroll 1
           for (int j = 0; j < NCH; ++j, ++g) {
@@ -224,7 +226,7 @@ block_fused_kernel(const __grid_constant__ CUtensorMap tmO, const __grid_constan
         int g = 0;
         for (int it = 0; it < my_tiles; ++it) {
           const int d2b = it & 1;
-          mbar_wait(&d2_empty[d2b], (uint32_t)(((it >> 1) & 1) ^ 1));
+          mbar_wait_sleep(&d2_empty[d2b], (uint32_t)(((it >> 1) & 1) ^ 1), 64);
           const uint32_t d = tmem_base + L::D2_COL0 + (uint32_t)(d2b * C);
 #pragma unroll 1
           for (int j = 0; j < NCH; ++j, ++g) {
@@ -248,7 +250,7 @@ block_fused_kernel(const __grid_constant__ CUtensorMap tmO, const __grid_constan
           const int sy = it % NY;
           const int tile = (int)blockIdx.x + it * (int)gridDim.x;
           const int b = tile / p.tiles_pb, t0 = (tile - b * p.tiles_pb) * 128;
-          mbar_wait(&y_ready[sy], (uint32_t)((it / NY) & 1));
+          mbar_wait_sleep(&y_ready[sy], (uint32_t)((it / NY) & 1), 128);
 #pragma unroll
           for (int c = 0; c < NBOX; ++c) tma_store_3d(&tmO, sY + sy * L::Y_BYTES + c * (128 * 128), c * 32, t0, b);
           tma_store_commit();
@@ -307,7 +309,7 @@ block_fused_kernel(const __grid_constant__ CUtensorMap tmO, const __grid_constan
     }
   } else if (warp < WARP_MX) {
     // ===== E2: D2 -> + b2, * ffn_gamma, + y (staged by the mixer warps, swizzled) -> in place -> TMA store ========
-    reg_dec<L::REG_E>();
+    reg_dec<L::REG_E2>();
     const int q = warp & 3;
     const int r = q * 32 + lane;
     for (int it = 0; it < my_tiles; ++it) {
@@ -396,10 +398,8 @@ block_fused_kernel(const __grid_constant__ CUtensorMap tmO, const __grid_constan
       t0 = (tile - b * p.tiles_pb) * 128;
     };
     // batch 0 of a tile = rows 8gi-6 .. 8gi (6 warm-up rows + the first output row); batch 1 = rows 8gi+1 .. 8gi+7
-    auto load_rows = [&](int it, int bt, float4 (&dst)[7]) {
+    auto load_rows = [&](int it, int b, int t0, int bt, float4 (&dst)[7]) {
       if (it >= my_tiles) return;                                    // (nothing will consume dst)
-      int b, t0;
-      tile_of(it, b, t0);
       const int ts = t0 + gi * 8 + (bt ? 1 : -6);
       const float* xb = p.x + ((long long)b * p.rows_pb + ts) * C + c0;
       if (ts >= 0 && ts + 7 <= p.rows_pb) {                          // interior: 7 unpredicated loads off one pointer
@@ -408,7 +408,7 @@ block_fused_kernel(const __grid_constant__ CUtensorMap tmO, const __grid_constan
         return;
       }
       const float* srd = nullptr;
-      if (ts < 0 && p.st.base != nullptr) {
+      if (STATE && ts < 0 && p.st.base != nullptr) {
         const uint8_t* rd8;
         uint8_t* wr8;
         p.st.resolve(b, rd8, wr8);
@@ -467,13 +467,17 @@ block_fused_kernel(const __grid_constant__ CUtensorMap tmO, const __grid_constan
       if (dst >= 0 && t < p.rows_pb) *reinterpret_cast<float4*>(st_wr + dst * C) = raw;
     };
 
+    // (tried and measured slower on B200: the folded taps read back from shared memory per use, 1.87 -> 2.21 ms at
+    //  C = 64; the next-tile prefetch staged through shared memory with cp.async instead of registers, 1.87 -> 2.03 ms)
     float4 bufA[7], bufB[7];
-    load_rows(0, 0, bufA);
+    int b, t0, nb = 0, nt0 = 0;
+    tile_of(0, b, t0);
+    load_rows(0, b, t0, 0, bufA);
     for (int it = 0; it < my_tiles; ++it) {
       const int sa = it % NA, sy = it % NY;
-      int b, t0;
-      tile_of(it, b, t0);
-      if (p.st.base != nullptr) {
+      if (it > 0) { b = nb; t0 = nt0; }
+      tile_of(it + 1, nb, nt0);
+      if (STATE && p.st.base != nullptr) {
         const uint8_t* rd8;
         uint8_t* wr8;
         p.st.resolve(b, rd8, wr8);
@@ -486,7 +490,7 @@ block_fused_kernel(const __grid_constant__ CUtensorMap tmO, const __grid_constan
       P4 fw;
       fw.lo = f2_pack(fw4.x, fw4.y);
       fw.hi = f2_pack(fw4.z, fw4.w);
-      load_rows(it, 1, bufB);                              // second batch of this tile: in flight during batch 0
+      load_rows(it, b, t0, 1, bufB);                       // second batch of this tile: in flight during batch 0
 
       // ---- batch 0: six warm-up rows rebuild the window, then output row k = 0 ---------------------------------
       {
@@ -495,7 +499,7 @@ block_fused_kernel(const __grid_constant__ CUtensorMap tmO, const __grid_constan
         float ss[7];
 #pragma unroll
         for (int i = 0; i < 7; ++i) {
-          if (st_wr != nullptr && (i == 6 || ts + i < 0)) state_row(ts + i, bufA[i]);
+          if (STATE && st_wr != nullptr && (i == 6 || ts + i < 0)) state_row(ts + i, bufA[i]);
           rows[i].lo = f2_pack(bufA[i].x, bufA[i].y);
           rows[i].hi = f2_pack(bufA[i].z, bufA[i].w);
           ss[i] = dot4(rows[i]);
@@ -515,7 +519,7 @@ block_fused_kernel(const __grid_constant__ CUtensorMap tmO, const __grid_constan
         mbar_wait(&y_empty[sy], (uint32_t)(((it / NY) & 1) ^ 1));
         store_row(0, rows[6], rstd_of(s2, inv_c, p.eps), fw, ys, as);
       }
-      load_rows(it + 1, 0, bufA);                          // first batch of the next tile: in flight during batch 1
+      load_rows(it + 1, nb, nt0, 0, bufA);                 // first batch of the next tile: in flight during batch 1
 
       // ---- batch 1: output rows k = 1..7 ------------------------------------------------------------------------
       {
@@ -524,7 +528,7 @@ block_fused_kernel(const __grid_constant__ CUtensorMap tmO, const __grid_constan
         float ss[7];
 #pragma unroll
         for (int i = 0; i < 7; ++i) {
-          if (st_wr != nullptr) state_row(ts + i, bufB[i]);
+          if (STATE && st_wr != nullptr) state_row(ts + i, bufB[i]);
           rows[i].lo = f2_pack(bufB[i].x, bufB[i].y);
           rows[i].hi = f2_pack(bufB[i].z, bufB[i].w);
           ss[i] = dot4(rows[i]);

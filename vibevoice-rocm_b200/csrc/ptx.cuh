@@ -59,6 +59,16 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   }
 }
 
+// Same, for waits that are long and not latency critical (a whole tile time): back off with nanosleep between polls
+// so the polling warp does not take issue slots from the compute warps of its scheduler partition.
+__device__ __forceinline__ void mbar_wait_sleep(uint64_t* bar, uint32_t parity, uint32_t ns) {
+  uint32_t spins = 0;
+  while (!mbar_try_wait(bar, parity)) {
+    __nanosleep(ns);
+    if (++spins > (1u << 24)) __trap();
+  }
+}
+
 // Wait for two barriers at once: both try_waits are in flight together, so their latencies overlap (a satisfied
 // try_wait still costs ~100-200 cycles on the issuing thread; measured with clock64 stamps on B200).
 __device__ __forceinline__ void mbar_wait2(uint64_t* bar_a, uint32_t par_a, uint64_t* bar_b, uint32_t par_b) {

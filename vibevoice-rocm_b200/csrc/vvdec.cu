@@ -660,12 +660,12 @@ bool block_fused_supported(const vv_decoder* d, int C) {
   return d->cfg.gemm_path == 0 && (C == 32 || C == 64);
 }
 
-template <int C>
+template <int C, bool STATE>
 int launch_block_fused_inst(vv_decoder* d, const CUtensorMap& tmO, const BlockW& bw, const BlockFusedArgs& a,
                             cudaStream_t s) {
   static bool attr_set = false;
   if (!attr_set) {
-    VV_CUDA(cudaFuncSetAttribute(block_fused_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    VV_CUDA(cudaFuncSetAttribute(block_fused_kernel<C, STATE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  (int)BlockFusedCfg<C>::TOTAL));
     attr_set = true;
   }
@@ -673,7 +673,7 @@ int launch_block_fused_inst(vv_decoder* d, const CUtensorMap& tmO, const BlockW&
   if (num_sms == 0) VV_CUDA(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, d->cfg.device));
   const long long ntiles = (long long)a.nbatch * a.tiles_pb;
   const unsigned grid = (unsigned)std::min<long long>(ntiles, num_sms);
-  block_fused_kernel<C><<<grid, BlockFusedCfg<C>::THREADS, BlockFusedCfg<C>::TOTAL, s>>>(tmO, bw.lin1.tm, bw.lin2.tm, a);
+  block_fused_kernel<C, STATE><<<grid, BlockFusedCfg<C>::THREADS, BlockFusedCfg<C>::TOTAL, s>>>(tmO, bw.lin1.tm, bw.lin2.tm, a);
   VV_CUDA(cudaGetLastError());
   return VV_OK;
 }
@@ -696,8 +696,9 @@ int launch_block_fused(vv_decoder* d, int C, const BlockW& bw, const float* x, f
   int rc = encode_map(&tmO, out, 3, dims, strides, box, true);
   if (rc != VV_OK) return rc;
   d->launches++;
-  if (C == 32) return launch_block_fused_inst<32>(d, tmO, bw, a, s);
-  return launch_block_fused_inst<64>(d, tmO, bw, a, s);
+  const bool streaming = a.st.base != nullptr;
+  if (C == 32) return streaming ? launch_block_fused_inst<32, true>(d, tmO, bw, a, s) : launch_block_fused_inst<32, false>(d, tmO, bw, a, s);
+  return streaming ? launch_block_fused_inst<64, true>(d, tmO, bw, a, s) : launch_block_fused_inst<64, false>(d, tmO, bw, a, s);
 }
 
 int pick_strip(long long total_rows, int rows) {
