@@ -212,6 +212,72 @@ def streaming_leg(dec, geom, dev, n_streams=256, steps=300, warmup=30):
     return out
 
 
+def longform_leg(dec, geom, dev, world, rank, dist, steps, frames=40_500):
+    """BASELINE.json configs[2]: one 90-minute utterance (40,500 latent frames) split into time chunks across the ranks,
+    each rank recomputing its causal halo (58 frames); no collective on the data path, one NCCL gather of the finished
+    waveform slices to rank 0 at the end (strong scaling: the utterance is fixed, N varies).  All ranks call this."""
+    import torch
+    from vvdec.shard import plan_shards
+    halo, hop, D = dec.halo_frames, geom.hop, geom.vae_dim
+    shards = plan_shards([frames], world, halo)
+    mine = sorted((s for s in shards if s.rank == rank), key=lambda s: s.start)
+    gen = torch.Generator().manual_seed(3)
+    lat_all = torch.randn(1, frames, D, generator=gen)
+    seg = frames // 4
+    for k, mu in enumerate((-0.5, 0.0, 0.5, 1.0)):                    # four "speakers": four segments, shifted means
+        lat_all[:, k * seg:(k + 1) * seg if k < 3 else frames] += mu
+    lats = [lat_all[:, s.start - s.halo:s.end].to(torch.bfloat16).to(dev) for s in mine]
+    owned = sum(s.frames for s in mine)
+    per_rank = [sum(s.frames for s in shards if s.rank == r) for r in range(world)]
+    cap = max(per_rank) * hop
+    buf = torch.zeros(cap, dtype=torch.bfloat16, device=dev)
+    gl = [torch.empty(cap, dtype=torch.bfloat16, device=dev) for _ in range(world)] if (rank == 0 and world > 1) else None
+    final = torch.empty(frames * hop, dtype=torch.bfloat16, device=dev) if rank == 0 else None
+
+    def step():
+        off = 0
+        for s, x in zip(mine, lats):
+            y = dec.decode(x)                                         # [1, 1, (halo + owned) * hop]
+            n = s.frames * hop
+            buf[off:off + n].copy_(y.view(-1)[s.halo * hop:])
+            off += n
+
+    def gather():
+        if world > 1:
+            dist.gather(buf, gl, dst=0)
+        if rank == 0:
+            offs = [0] * world
+            for s in sorted(shards, key=lambda s: (s.rank, s.start)):
+                src = gl[s.rank] if world > 1 else buf
+                n = s.frames * hop
+                final[s.start * hop:s.start * hop + n].copy_(src[offs[s.rank]:offs[s.rank] + n])
+                offs[s.rank] += n
+
+    def sync():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+    step(); gather(); sync()
+    e0, e1, e2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+    t_dec = t_all = 0.0
+    for _ in range(steps):
+        sync()
+        e0.record(); step(); e1.record(); gather(); e2.record()
+        sync()
+        t_dec += e0.elapsed_time(e1); t_all += e0.elapsed_time(e2)
+    t = torch.tensor([t_dec / steps, t_all / steps], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_dec, ms_all = float(t[0]), float(t[1])
+    ok = bool(torch.isfinite(final.float()).all()) if rank == 0 else True
+    return {"workload": f"one {frames / FRAME_RATE / 60:.0f}-minute utterance ({frames} frames), time-chunk shards with a "
+                        f"{halo}-frame recomputed halo, waveform gathered to rank 0",
+            "scaling": "strong", "n_gpus": world, "shards": len(shards), "halo_frames": halo,
+            "frames_owned_rank0": owned, "recomputed_halo_frames_total": sum(s.halo for s in shards),
+            "ms_decode": ms_dec, "ms_decode_plus_gather": ms_all, "gather_bytes": (frames * hop * 2 if world > 1 else 0),
+            "value": frames / FRAME_RATE / (ms_all / 1e3), "unit": UNIT, "finite": ok}
+
+
 def enc_kernel_work(geom, kind: str, stage: int):
     """Encoder counterpart of kernel_work: per SAMPLE-ROW of the stage (not per frame) -> (bound, algorithmic bytes,
     flop, bytes moved) per row.  Stage i has C = n_filters * 2^i channels."""
@@ -237,7 +303,7 @@ def enc_kernel_work(geom, kind: str, stage: int):
     return "hbm", 0, 0, 0
 
 
-def encoder_leg(geom, dev, pk, steps, warmup, B=32, L=720_000, kernels_out=""):
+def encoder_leg(geom, dev, pk, steps, warmup, B=32, L=720_000, kernels_out="", cpu_baseline=True):
     """BASELINE.json configs[4]: acoustic tokenizer ENCODER on voice prompts, batch 32 x 30 s, through
     B200AcousticEncoder.encode (the C ABI's vv_encode).  Device-resident throughput, an end-to-end figure with pinned
     host buffers, and the per-kernel table of one profiled pass."""
@@ -245,7 +311,8 @@ def encoder_leg(geom, dev, pk, steps, warmup, B=32, L=720_000, kernels_out=""):
     import vvdec
     from vvdec.synthetic import random_encoder_state_dict
     enc = vvdec.B200AcousticEncoder(geom, device=dev.index)
-    enc.load_state_dict(random_encoder_state_dict(geom))
+    sd_cpu = random_encoder_state_dict(geom)
+    enc.load_state_dict(sd_cpu)
     gen = torch.Generator().manual_seed(5)
     a_host = (torch.randn(B, 1, L, generator=gen) * 0.1).to(torch.bfloat16).pin_memory()
     audio = a_host.to(dev)
@@ -304,7 +371,22 @@ def encoder_leg(geom, dev, pk, steps, warmup, B=32, L=720_000, kernels_out=""):
         with open(kernels_out, "w") as f:
             json.dump({"config": {"B": B, "L": L, "ms_per_step": ms}, "kernels": table}, f, indent=1)
     del enc
-    return {"workload": f"acoustic tokenizer encoder, batch {B} x {L / 24000:.0f} s ({L} samples -> {T} frames), bf16 audio in",
+    cpu = None
+    if cpu_baseline:
+        # reported CPU figure for the encoder: the numpy port on a bounded sample (batch 1 x 2 s), all host threads
+        from oracle.geometry import FULL
+        from oracle.vv_oracle import OracleEncoder
+        from oracle.weights import make_audio
+        oe = OracleEncoder({k: v.numpy() for k, v in sd_cpu.items()}, FULL)
+        a = make_audio(1, 48_000, 5)
+        oe.encode(a[:, :, :6400])
+        t0 = time.perf_counter()
+        oe.encode(a)
+        sec = time.perf_counter() - t0
+        cpu = {"value": 2.0 / sec, "unit": "encoded audio-s/s", "cores": os.cpu_count(), "kind": "port",
+               "sample": f"batch 1 x 2 s (48000 samples), numpy fp32 port, {sec:.2f} s"}
+    return {"cpu_baseline": cpu,
+            "workload": f"acoustic tokenizer encoder, batch {B} x {L / 24000:.0f} s ({L} samples -> {T} frames), bf16 audio in",
             "value": audio_s / (ms / 1e3), "unit": "encoded audio-s/s", "ms_per_step": ms, "gpu_launches": int(launches),
             "e2e": {"value": audio_s / (ms_e2e / 1e3), "ms_per_step": ms_e2e, "h2d_bytes_per_step": a_host.numel() * 2,
                     "d2h_bytes_per_step": m_host.numel() * 2},
@@ -327,6 +409,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-streaming", action="store_true")
     ap.add_argument("--no-encoder", action="store_true")
+    ap.add_argument("--no-longform", action="store_true")
     ap.add_argument("--encoder-kernels-out", default="", help="per-kernel table of the encoder leg (JSON)")
     ap.add_argument("--kernels-out", default="", help="write the per-kernel timing table (JSON) here")
     args = ap.parse_args()
@@ -404,6 +487,17 @@ def main():
     e2e = {"value": world * audio_s / (ms_e2e / 1e3), "unit": UNIT, "ms_per_step": ms_e2e,
            "h2d_bytes_per_step": lat_host.numel() * 2, "d2h_bytes_per_step": out_host.numel() * 2}
 
+    # ---- long-form decode sharded in time (BASELINE.json configs[2]); every rank takes part -------------------
+    longform = None
+    if not args.no_longform:
+        y = None
+        try:
+            longform = longform_leg(dec, geom, dev, world, rank, dist, max(2, args.steps // 2))
+        except Exception as e:                                  # report, do not hide
+            longform = {"error": f"{type(e).__name__}: {e}"[:300]}
+            if world > 1:
+                raise
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -448,7 +542,7 @@ def main():
     # ---- streaming per-frame latency (second half of BASELINE.json's metric) ---------------------------
     streaming = None
     if not args.no_streaming:
-        del y
+        y = None
         streaming = streaming_leg(dec, geom, dev)
 
     # ---- encoder leg (BASELINE.json configs[4]) ---------------------------------------------------------
@@ -458,7 +552,8 @@ def main():
         dec._ws = None                                          # release the decode workspace
         torch.cuda.empty_cache()
         try:
-            encoder = encoder_leg(geom, dev, pk, args.steps, args.warmup, kernels_out=args.encoder_kernels_out)
+            encoder = encoder_leg(geom, dev, pk, args.steps, args.warmup, kernels_out=args.encoder_kernels_out,
+                                  cpu_baseline=not args.no_cpu_baseline)
         except Exception as e:                                  # report, do not hide
             encoder = {"error": f"{type(e).__name__}: {e}"[:300]}
 
@@ -479,7 +574,7 @@ def main():
                    "l2": "inputs >> L2 (each pass streams >700 MB of activations per utterance group)",
                    "sharding": "utterances per rank, no data-path collective"},
         "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roof, "cpu_baseline": cpu,
-        "streaming": streaming, "encoder": encoder,
+        "streaming": streaming, "encoder": encoder, "longform": longform,
     }
     print(json.dumps(line), flush=True)
     if world > 1:

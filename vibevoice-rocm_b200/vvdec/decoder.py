@@ -328,10 +328,15 @@ class B200AcousticDecoder:
             pass
 
 
-def patch(model, **kw) -> B200AcousticDecoder:
+def patch(model, encode: bool = False, **kw) -> B200AcousticDecoder:
     """Swap ``decode`` of a reference tokenizer (or of ``model.model.acoustic_tokenizer`` inside the full
     VibeVoice model) for the B200 path, in place; ``generate()`` (modeling_vibevoice_inference.py:635-641)
-    then runs unmodified.  Returns the decoder object."""
+    then runs unmodified.  Returns the decoder object.
+
+    ``encode=True`` also swaps ``encode`` (the offline voice-prompt prefill, modeling_vibevoice_inference.py:154)
+    for the B200 encoder (``tok._b200_encoder``).  Streaming encode calls (``use_cache=True`` with a cache) are not
+    built on this path and raise NotImplementedError, so only patch ``encode`` on a tokenizer whose callers use the
+    offline form (the acoustic tokenizer; not the semantic tokenizer inside ``generate()``)."""
     tok = model
     for attr in ("model", "acoustic_tokenizer"):
         if hasattr(tok, attr) and not hasattr(tok, "decoder"):
@@ -342,4 +347,12 @@ def patch(model, **kw) -> B200AcousticDecoder:
     dec = B200AcousticDecoder.from_reference(tok, device=dev if dev.type == "cuda" else None, **kw)
     tok._b200_decoder = dec
     tok.decode = dec.decode
+    if encode:
+        if not hasattr(tok, "encoder"):
+            raise ValueError("the tokenizer has no .encoder to replace")
+        from .encoder import B200AcousticEncoder
+        ekw = {k: v for k, v in kw.items() if k in ("gemm_path",)}
+        enc = B200AcousticEncoder.from_reference(tok, device=dev if dev.type == "cuda" else None, **ekw)
+        tok._b200_encoder = enc
+        tok.encode = enc.encode
     return dec
