@@ -533,7 +533,17 @@ def main():
     else:
         roof = {"bound": "hbm", "achieved": top["gbs_algorithmic"], "peak": pk["hbm_gbs"], "unit": "GB/s",
                 "frac": top["gbs_algorithmic"] / pk["hbm_gbs"], "moved_gbs": top["gbs_moved"]}
-    roof.update({"kernel": f"{top['kind']}@stage{top['stage']}", "share_of_step": top["share"], "traffic": None,
+    kname = f"{top['kind']}@stage{top['stage']}"
+    traffic, traffic_src = None, None
+    try:                                                      # DRAM bytes per launch from the committed ncu capture
+        with open(os.path.join(ROOT, "profiles", "traffic_r01.json")) as f:
+            tr = json.load(f).get(kname)
+        if tr:
+            traffic, traffic_src = tr["dram_bytes_per_frame"] * top["frames_per_launch"], tr["source"]
+    except OSError:
+        pass
+    roof.update({"kernel": kname, "share_of_step": top["share"], "traffic": traffic, "traffic_source": traffic_src,
+                 "algorithmic_bytes_per_launch": kernel_work(geom, top["kind"], top["stage"])[1] * top["frames_per_launch"],
                  "peak_source": pk["source"], "ms_per_launch": top["ms_per_launch"]})
     if args.kernels_out:
         with open(args.kernels_out, "w") as f:
