@@ -144,6 +144,8 @@ def kernel_work(geom, kind: str, stage: int):
         return bound, 2 * cm, 8 * C * cm, moved
     if kind == "ffn_fused":    # whole FFN half in one launch: a (bf16) + resid (fp32) in, out (fp32)
         return ("tensor" if C >= 128 else "hbm"), 4 * cm, 16 * C * cm, 10 * cm
+    if kind == "ffn_pair":     # both GEMMs in L2-resident row chunks: the hidden tensor never reaches HBM
+        return "tensor", 4 * cm, 16 * C * cm, 10 * cm
     if kind == "block_fused":  # whole Block1D in one launch (C <= 64): SURVEY's mixer half + FFN half = 8*C*M bytes;
         return "hbm", 8 * cm, 20 * cm + 16 * C * cm, 8 * cm   # this design moves exactly that (fp32 x in, fp32 x out)
     if kind == "upsample":     # 2*(Cin*Min + Cout*Mout) bytes, 4*Cin*Cout*r*Min flop
@@ -288,7 +290,7 @@ def enc_kernel_work(geom, kind: str, stage: int):
     if kind in ("ffn1", "ffn2"):
         moved = (2 * C + 8 * C) if kind == "ffn1" else (8 * C + 4 * C + 4 * C)
         return ("tensor" if C >= 128 else "hbm"), 2 * C, 8 * C * C, moved
-    if kind == "ffn_fused":
+    if kind in ("ffn_fused", "ffn_pair"):
         return ("tensor" if C >= 128 else "hbm"), 4 * C, 16 * C * C, 10 * C
     if kind == "block_fused":
         return "hbm", 8 * C, 20 * C + 16 * C * C, 8 * C
@@ -356,7 +358,7 @@ def encoder_leg(geom, dev, pk, steps, warmup, B=32, L=720_000, kernels_out="", c
     for r in prof:
         bound, abytes, aflop, moved = enc_kernel_work(geom, r["kind"], r["stage"])
         nl = max(1, r["launches"])
-        nblk = geom.depths[n - 1 - r["stage"]] if r["kind"] in ("mixer", "ffn1", "ffn2", "ffn_fused", "block_fused") else 1
+        nblk = geom.depths[n - 1 - r["stage"]] if r["kind"] in ("mixer", "ffn1", "ffn2", "ffn_fused", "block_fused", "ffn_pair") else 1
         passes = max(1, nl // nblk)
         units = B * rows_of[r["stage"]] / passes
         msl = r["ms"] / nl
@@ -515,7 +517,7 @@ def main():
     for r in prof:
         bound, abytes, aflop, moved = kernel_work(geom, r["kind"], r["stage"])
         n = max(1, r["launches"])
-        nblk = geom.depths[r["stage"]] if r["kind"] in ("mixer", "ffn1", "ffn2", "ffn_fused", "block_fused") else 1
+        nblk = geom.depths[r["stage"]] if r["kind"] in ("mixer", "ffn1", "ffn2", "ffn_fused", "block_fused", "ffn_pair") else 1
         passes = n // nblk                                   # decode passes the workspace split the batch into
         units = frames / passes                              # latent frames one launch processes
         ms_launch = r["ms"] / n

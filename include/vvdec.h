@@ -135,7 +135,8 @@ int64_t vv_decoder_take_launch_count(vv_decoder* dec);
 typedef enum vv_kernel_kind {
   VV_K_PREP = 0, VV_K_STEM = 1, VV_K_MIXER = 2, VV_K_FFN1 = 3, VV_K_FFN2 = 4, VV_K_HALO = 5,
   VV_K_UPSAMPLE = 6, VV_K_HEAD = 7, VV_K_STATE = 8, VV_K_FFN_FUSED = 9, VV_K_BLOCK_FUSED = 10,
-  VV_K_ENC_STEM = 11, VV_K_DOWNSAMPLE = 12, VV_K_PAD = 13, VV_K_ENC_HEAD = 14   /* encoder path */
+  VV_K_ENC_STEM = 11, VV_K_DOWNSAMPLE = 12, VV_K_PAD = 13, VV_K_ENC_HEAD = 14,  /* encoder path */
+  VV_K_FFN_PAIR = 15   /* both FFN GEMMs of a block run in L2-resident row chunks: one record for the pair */
 } vv_kernel_kind;
 typedef struct vv_profile_record {
   int32_t kind;        /* vv_kernel_kind */

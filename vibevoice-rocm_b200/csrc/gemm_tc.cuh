@@ -51,6 +51,10 @@ struct GemmArgs {
   __nv_bfloat16* out_bf16;
   long long ob_rpb;
   int ob_off;
+  // When ob_rows_pb > 0 the launch covers a FLAT row range [ob_row0, ob_row0 + rows) of a [items, ob_rows_pb] tensor
+  // (nbatch = 1): the padded bf16 copy then addresses item = m / ob_rows_pb, t = m % ob_rows_pb (gemm_tc2 only).
+  int ob_rows_pb;
+  long long ob_row0;
 };
 
 template <int BN, int BK>

@@ -235,7 +235,13 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
             const int b = tile_b * bb + (r >> g.bt_log2);
             const int t = tile_t * bt + (r & (bt - 1));
             if (b < g.nbatch && t < g.rows) {
-              __nv_bfloat16* op = g.out_bf16 + ((long long)b * g.ob_rpb + g.ob_off + t) * g.N + n;
+              long long brow = (long long)b * g.ob_rpb + g.ob_off + t;
+              if (g.ob_rows_pb > 0) {                      // flat row range of a [items, rows_pb] tensor
+                const long long m = g.ob_row0 + t;
+                const long long item = m / g.ob_rows_pb;
+                brow = item * g.ob_rpb + g.ob_off + (m - item * g.ob_rows_pb);
+              }
+              __nv_bfloat16* op = g.out_bf16 + brow * g.N + n;
 #pragma unroll
               for (int i = 0; i < 4; ++i) {
                 uint4 pk;

@@ -474,6 +474,8 @@ struct EpiOut {
   __nv_bfloat16* out_bf16 = nullptr;
   int bf16_halo = 0;            // out_bf16 rows per batch item = rows + bf16_halo, first bf16_halo rows skipped
   long long bf16_rpb = 0;       // when > 0: rows per batch item of out_bf16 (overrides rows + bf16_halo)
+  int bf16_rows_pb = 0;         // when > 0: the launch is a flat row range starting at bf16_row0 of [items, bf16_rows_pb]
+  long long bf16_row0 = 0;
 };
 
 template <int BN, int BK>
@@ -507,6 +509,7 @@ int launch_gemm_impl(vv_decoder* d, const __nv_bfloat16* A, long long a_rpb, int
   g.epi = e.epi; g.bias = w.bias; g.gamma = e.gamma; g.resid = e.resid;
   g.out_f32 = e.out_f32; g.of_rpb = rows; g.of_off = 0;
   g.out_bf16 = e.out_bf16; g.ob_rpb = e.bf16_rpb > 0 ? e.bf16_rpb : rows + e.bf16_halo; g.ob_off = e.bf16_halo;
+  g.ob_rows_pb = e.bf16_rows_pb; g.ob_row0 = e.bf16_row0;
   const int nk = g.n_taps * g.kb_per_tap;
   const int per_stage = GEMM_BM * w.BK * 2 + w.BN * w.BK * 2;
   g.stages = std::max(1, std::min(std::min(nk, GEMM_MAX_STAGES), (96 * 1024) / per_stage));
@@ -701,6 +704,61 @@ int launch_block_fused(vv_decoder* d, int C, const BlockW& bw, const float* x, f
   return streaming ? launch_block_fused_inst<64, true>(d, tmO, bw, a, s) : launch_block_fused_inst<64, false>(d, tmO, bw, a, s);
 }
 
+// FFN half as two GEMMs (C >= 256).  At C = 256 the pair is HBM-bound by the bf16 hidden tensor's round trip (26 bytes
+// per element), so an L2-resident variant exists: run the pair in row chunks whose hidden slice fits the 126 MB L2 and
+// reuse one hidden buffer.  MEASURED SLOWER on B200 (K2 stage 3, 15 blocks: 31.2 ms unchunked, 43.5 / 47.5 / 65.5 ms
+// with 64 / 32 / 16 MB chunks — 70+ short persistent launches per block cost more in prologue and tile quantisation
+// than the saved traffic), so it is off by default; VV_FFN_CHUNK_MB=<MB> turns it on for experiments.
+//   a: bf16 [R, C]; resid (y), out (x): fp32 [R, C]; h: bf16 scratch [R, 4C]; optional padded bf16 copy.
+long long ffn_chunk_rows(const vv_decoder* d, int C, long long R) {
+  static long long chunk_mb = -1;
+  if (chunk_mb < 0) {
+    const char* e = getenv("VV_FFN_CHUNK_MB");
+    chunk_mb = e ? atoll(e) : 0;
+  }
+  const bool tc2 = d->cfg.gemm_path == 0 || d->cfg.gemm_path == 4 || d->cfg.gemm_path == 2;
+  if (!tc2 || chunk_mb <= 0 || C > 256 || R * C * 8 <= chunk_mb * (1LL << 20) * 2) return R;
+  const long long rows = (chunk_mb << 20) / ((long long)C * 8);
+  return std::max<long long>(128, rows / 128 * 128);
+}
+
+int launch_ffn_pair(vv_decoder* d, int C, const BlockW& bw, const __nv_bfloat16* A, const float* Y, float* X,
+                    __nv_bfloat16* H, __nv_bfloat16* XB, PadOut po, int nb, int rows_pb, int stage, cudaStream_t s) {
+  const long long R = (long long)nb * rows_pb;
+  const long long chunk = ffn_chunk_rows(d, C, R);
+  int rc;
+  if (chunk >= R) {
+    EpiOut e1;
+    e1.epi = EPI_GELU_BF16; e1.out_bf16 = H;
+    rc = launch_gemm(d, A, R, (int)R, 1, bw.lin1, e1, s, VV_K_FFN1, stage);
+    if (rc != VV_OK) return rc;
+    EpiOut e2;
+    e2.epi = EPI_RESID; e2.gamma = bw.ffn_gamma; e2.resid = Y; e2.out_f32 = X;
+    if (XB != nullptr) {
+      e2.out_bf16 = XB; e2.bf16_halo = po.off; e2.bf16_rpb = po.rpb > 0 ? po.rpb : rows_pb + po.off;
+      return launch_gemm(d, H, rows_pb, rows_pb, nb, bw.lin2, e2, s, VV_K_FFN2, stage);
+    }
+    return launch_gemm(d, H, R, (int)R, 1, bw.lin2, e2, s, VV_K_FFN2, stage);
+  }
+  for (long long r0 = 0; r0 < R; r0 += chunk) {
+    const int n = (int)std::min(chunk, R - r0);
+    EpiOut e1;
+    e1.epi = EPI_GELU_BF16; e1.out_bf16 = H;
+    rc = launch_gemm(d, A + r0 * C, n, n, 1, bw.lin1, e1, s);
+    if (rc != VV_OK) return rc;
+    EpiOut e2;
+    e2.epi = EPI_RESID; e2.gamma = bw.ffn_gamma; e2.resid = Y + r0 * C; e2.out_f32 = X + r0 * C;
+    if (XB != nullptr) {
+      e2.out_bf16 = XB; e2.bf16_halo = po.off; e2.bf16_rpb = po.rpb > 0 ? po.rpb : rows_pb + po.off;
+      e2.bf16_rows_pb = rows_pb; e2.bf16_row0 = r0;
+    }
+    rc = launch_gemm(d, H, n, n, 1, bw.lin2, e2, s);
+    if (rc != VV_OK) return rc;
+  }
+  d->mark(VV_K_FFN_PAIR, stage, s);  // one profiling record for the whole chunked pair
+  return VV_OK;
+}
+
 int pick_strip(long long total_rows, int rows) {
   // longer strips amortise the 6 warm-up rows; shorter ones keep the machine full on small problems
   int strip = 113;
@@ -847,18 +905,7 @@ int run_pass(vv_decoder* d, const LatView& lat, int nb, int T, void* audio, int 
         d->mark(VV_K_FFN_FUSED, i, s);
         continue;
       }
-      EpiOut e1;
-      e1.epi = EPI_GELU_BF16; e1.out_bf16 = H;
-      rc = launch_gemm(d, A, (long long)nb * rows_pb, nb * rows_pb, 1, bw.lin1, e1, s, VV_K_FFN1, i);
-      if (rc != VV_OK) return rc;
-      EpiOut e2;
-      e2.epi = EPI_RESID; e2.gamma = bw.ffn_gamma; e2.resid = Y; e2.out_f32 = X;
-      if (feeds_up) {
-        e2.out_bf16 = XB; e2.bf16_halo = 1;
-        rc = launch_gemm(d, H, rows_pb, rows_pb, nb, bw.lin2, e2, s, VV_K_FFN2, i);
-      } else {
-        rc = launch_gemm(d, H, (long long)nb * rows_pb, nb * rows_pb, 1, bw.lin2, e2, s, VV_K_FFN2, i);
-      }
+      rc = launch_ffn_pair(d, C, bw, A, Y, X, H, feeds_up ? XB : nullptr, PadOut(), nb, rows_pb, i, s);
       if (rc != VV_OK) return rc;
     }
     if (nblk == 0 && i + 1 < S) { set_error("stage %d has no blocks", i); return VV_ERR_UNSUPPORTED; }

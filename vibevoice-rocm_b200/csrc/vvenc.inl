@@ -137,18 +137,7 @@ int enc_run_pass(vv_encoder* e, const void* audio, int audio_is_bf16, long long 
         d->mark(VV_K_FFN_FUSED, i, s);
         continue;
       }
-      EpiOut e1;
-      e1.epi = EPI_GELU_BF16; e1.out_bf16 = H;
-      rc = launch_gemm(d, A, (long long)nb * rows_pb, nb * rows_pb, 1, bw.lin1, e1, s, VV_K_FFN1, i);
-      if (rc != VV_OK) return rc;
-      EpiOut e2;
-      e2.epi = EPI_RESID; e2.gamma = bw.ffn_gamma; e2.resid = Y; e2.out_f32 = X;
-      if (last) {
-        e2.out_bf16 = XB; e2.bf16_halo = bo.xb_off; e2.bf16_rpb = bo.xb_rpb;
-        rc = launch_gemm(d, H, rows_pb, rows_pb, nb, bw.lin2, e2, s, VV_K_FFN2, i);
-      } else {
-        rc = launch_gemm(d, H, (long long)nb * rows_pb, nb * rows_pb, 1, bw.lin2, e2, s, VV_K_FFN2, i);
-      }
+      rc = launch_ffn_pair(d, C, bw, A, Y, X, H, last ? XB : nullptr, po, nb, rows_pb, i, s);
       if (rc != VV_OK) return rc;
     }
     if (i == S - 1) {   // self.norm is Identity (disable_last_norm, :767-770); head k7 -> mean [nb, T, vae_dim]

@@ -38,7 +38,7 @@ class VvProfileRecord(C.Structure):
 
 
 KERNEL_KINDS = ("prep", "stem", "mixer", "ffn1", "ffn2", "halo", "upsample", "head", "state", "ffn_fused",
-                "block_fused", "enc_stem", "downsample", "pad", "enc_head")
+                "block_fused", "enc_stem", "downsample", "pad", "enc_head", "ffn_pair")
 
 # name -> (restype, argtypes): every symbol include/vvdec.h declares
 _P, _I32, _I64 = C.c_void_p, C.c_int32, C.c_int64
