@@ -161,8 +161,7 @@ int32_t vv_state_import(vv_state* st, int32_t slot, const void* host_src, int64_
 /* ---- encoder (replaces TokenizerEncoder.forward :810-813 under VibeVoiceAcousticTokenizerModel.encode :1081-1085) --
  * The encoder mirrors the decoder's vv_config (same struct, decoder-order fields): stage i has n_filters * 2^i
  * channels, depth depths[n_stages-1-i] and is entered through a strided conv of ratio ratios[n_stages-1-i]
- * (:701, :1019-1028).  Tensor names are the reference's "encoder.*" keys.  Offline form only (cache=None /
- * use_cache=False); the streaming form of the strided convs is not built. */
+ * (:701, :1019-1028).  Tensor names are the reference's "encoder.*" keys. */
 typedef struct vv_encoder vv_encoder;
 int32_t vv_encoder_create(const vv_config* cfg, vv_encoder** out);
 int32_t vv_encoder_destroy(vv_encoder* enc);
@@ -178,11 +177,18 @@ int64_t vv_encoder_workspace_bytes(const vv_encoder* enc, int32_t B, int64_t L);
  * audio : device, [B, L] (= the reference's [B, 1, L]) contiguous, f32 or bf16.
  * mean  : device, fp32 [B, frames, vae_dim] contiguous — VibeVoiceTokenizerEncoderOutput.mean (:1084-1085; its
  *         std is the config's fix_std, a host-side constant).
+ * state : NULL for offline encode (cache=None / use_cache=False).  Otherwise a state made by vv_encoder_state_create
+ *         (all vv_state_* calls apply); slot_ids (device int32 [B]) = sample_indices.  Each layer's left context comes
+ *         from the slot and is updated in place (SConv1d._forward_streaming :327-382); a zeroed slot = first chunk.
+ *         Streaming chunks must be whole hops (L % hop == 0, VV_ERR_BAD_SHAPE otherwise): then no strided conv pads
+ *         on the right and the stream reproduces the offline result.
  * A workspace smaller than vv_encoder_workspace_bytes(B, L) is honoured by encoding the utterances in groups;
  * one utterance must fit (VV_ERR_WORKSPACE otherwise).
  */
+int32_t vv_encoder_state_create(const vv_encoder* enc, int32_t n_slots, vv_state** out);   /* zero-filled */
 int32_t vv_encode(vv_encoder* enc, const void* audio, int32_t audio_dtype, int32_t B, int64_t L, float* mean,
-                  void* workspace, int64_t workspace_bytes, void* cuda_stream);
+                  void* workspace, int64_t workspace_bytes, vv_state* state, const int32_t* slot_ids,
+                  void* cuda_stream);
 int64_t vv_encoder_take_launch_count(vv_encoder* enc);
 int32_t vv_encoder_set_profiling(vv_encoder* enc, int32_t enabled);
 int32_t vv_encoder_read_profile(vv_encoder* enc, vv_profile_record* out, int32_t cap);

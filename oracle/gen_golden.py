@@ -152,6 +152,36 @@ def encoder_case(name, geom, init, wseed, B, L, aseed):
     print(f"{name}: mean {mean.shape} peak {np.abs(mean).max():.4g} rms {np.sqrt((mean**2).mean()):.4g}  ({time.time()-t0:.1f}s)")
 
 
+def encoder_stream_case(name, geom, init, wseed, n_streams, schedule, aseed):
+    """Replay streaming encode calls (modeling_vibevoice_inference.py:656-662 pattern) against the reference.
+    schedule: list of ["encode", [sample indices], hops] | ["zero", [sample indices]]; call s of stream i reads the
+    next `hops` * hop samples of that stream's seeded audio."""
+    import torch
+    _, _, Cache = import_reference()
+    w = make_encoder_weights(geom, init, wseed)
+    model = build_reference_model(geom, w)
+    total = sum(st[2] for st in schedule if st[0] == "encode") * geom.hop
+    audio = make_audio(n_streams, total, aseed)
+    pos = [0] * n_streams
+    cache = Cache()
+    outs = {}
+    for s, step in enumerate(schedule):
+        if step[0] == "zero":
+            cache.set_to_zero(torch.tensor(step[1]))
+            continue
+        idx, n = step[1], step[2] * geom.hop
+        x = np.stack([audio[i, :, pos[i]:pos[i] + n] for i in idx])
+        for i in idx:
+            pos[i] += n
+        with torch.no_grad():
+            y = model.encode(torch.from_numpy(x), cache=cache, sample_indices=torch.tensor(idx), use_cache=True).mean
+        outs[f"out:{s}"] = y.numpy().astype(np.float32)
+    meta = dict(kind="encode_stream", geom=geom.__dict__, init=init, wseed=wseed, aseed=aseed, n_streams=n_streams,
+                schedule=schedule, total=total)
+    np.savez(os.path.join(GOLD, name + ".npz"), meta=np.array(json.dumps(meta)), **outs)
+    print(f"{name}: {len(outs)} encode calls recorded")
+
+
 def main_encoder():
     """Encoder fixtures: ragged lengths exercise the right extra padding of every strided conv
     (:127-133); an exact multiple of the hop exercises the no-padding path; default init pins the real init scale."""
@@ -163,6 +193,11 @@ def main_encoder():
     encoder_case("enc_tiny_stress_L10117", TINY, "stress", 7, 2, 3200 * 3 + 517, 5)
     # semantic tokenizer shape (N1): same encoder class with vae_dim 128
     encoder_case("enc_sem128_stress_L7001", DecoderGeometry(vae_dim=128, depths=(2, 1, 1, 1, 1, 1, 2)), "stress", 11, 1, 7001, 9)
+    # streaming encode: steady state, a late joiner (all-or-nothing get, :204-207), set_to_zero, multi-hop chunks
+    sched = [["encode", [0, 1], 1], ["encode", [0, 1], 1], ["encode", [0], 2], ["zero", [1]], ["encode", [0, 1], 1],
+             ["encode", [0, 1, 2], 1], ["encode", [2, 0], 3]]
+    encoder_stream_case("enc_stream_stress", DecoderGeometry(depths=(2, 1, 1, 1, 1, 1, 2)), "stress", 13, 3, sched, 10)
+    encoder_stream_case("enc_stream_tiny", TINY, "stress", 7, 3, sched, 10)
 
 
 def main():

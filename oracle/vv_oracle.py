@@ -273,19 +273,50 @@ def sconv1d_strided(x: np.ndarray, w: np.ndarray, b: np.ndarray, stride: int) ->
     return y + b[None, :, None]
 
 
+def sconv1d_strided_streaming(x: np.ndarray, w: np.ndarray, b: np.ndarray, stride: int,
+                              state: np.ndarray) -> Tuple[np.ndarray, np.ndarray]:
+    """SConv1d._forward_streaming (:327-382) with stride: context_size = (k-1) - (stride-1) cached inputs are put in
+    front of x, the conv runs without padding (trailing samples that do not fill a window are dropped by nn.Conv1d,
+    :359), the new state = last context_size columns of [state, x] (:370-372)."""
+    k = w.shape[2]
+    xin = np.concatenate([state, x], axis=2)
+    To = (xin.shape[2] - k) // stride + 1
+    y = np.zeros((x.shape[0], w.shape[0], max(To, 0)), dtype=F32)
+    for j in range(k):
+        if To > 0:
+            y += np.matmul(w[:, :, j], xin[:, :, j:j + (To - 1) * stride + 1:stride])
+    ctx = state.shape[2]
+    return y + b[None, :, None], xin[:, :, xin.shape[2] - ctx:].copy()
+
+
 class OracleEncoder:
-    """TokenizerEncoder.forward (:810-813) + VibeVoiceAcousticTokenizerModel.encode (:1081-1085), offline."""
+    """TokenizerEncoder.forward (:810-813) + VibeVoiceAcousticTokenizerModel.encode (:1081-1085), offline and streaming."""
 
     def __init__(self, weights: Dict[str, np.ndarray], geom: DecoderGeometry = FULL):
         self.g = geom
         self.w = {k: np.ascontiguousarray(v, dtype=F32) for k, v in weights.items()}
 
-    def _block(self, i, j, x, taps):
+    def _sconv(self, layer_id, x, w, b, groups, stride, cache, idx):
+        if cache is None:
+            return sconv1d(x, w, b, groups)[0] if stride == 1 else sconv1d_strided(x, w, b, stride)
+        ctx = (w.shape[2] - 1) - (stride - 1)                        # :282
+        st = cache.get(layer_id, idx)
+        if st is None:                                              # :337-340 zeros context
+            st = np.zeros((x.shape[0], x.shape[1], ctx), dtype=F32)
+        if stride == 1:
+            y, ns = sconv1d(x, w, b, groups, state=st)
+        else:
+            y, ns = sconv1d_strided_streaming(x, w, b, stride, st)
+        cache.set(layer_id, idx, ns)                                # :380
+        return y
+
+    def _block(self, i, j, x, taps, cache=None, idx=None):
         g, w = self.g, self.w
         p = f"encoder.stages.{i}.{j}."
         r = x                                                       # mixer half (:788-794)
         h = rms_norm_channels(x, w[p + "norm.weight"], g.eps)
-        h = sconv1d(h, w[p + "mixer.conv.conv.conv.weight"], w[p + "mixer.conv.conv.conv.bias"], x.shape[1])[0]
+        h = self._sconv(p + "mixer", h, w[p + "mixer.conv.conv.conv.weight"], w[p + "mixer.conv.conv.conv.bias"],
+                        x.shape[1], 1, cache, idx)
         x = r + h * w[p + "gamma"][None, :, None]
         r = x                                                       # ffn half (:796-804)
         h = rms_norm_channels(x, w[p + "ffn_norm.weight"], g.eps)
@@ -296,24 +327,29 @@ class OracleEncoder:
             taps[p + "out"] = x
         return x
 
-    def encode(self, audio: np.ndarray, taps: Optional[dict] = None) -> np.ndarray:
-        """audio [B, 1, L] (or [B, L]) -> mean [B, ceil(L / hop), vae_dim]  (:1084 permutes to [B, T, D])."""
+    def encode(self, audio: np.ndarray, taps: Optional[dict] = None, cache: Optional[OracleStreamingCache] = None,
+               sample_indices: Optional[Sequence[int]] = None, use_cache: bool = False) -> np.ndarray:
+        """audio [B, 1, L] (or [B, L]) -> mean [B, frames, vae_dim]  (:1084 permutes to [B, T, D]); frames =
+        ceil(L / hop) offline, floor((ctx + L - k) / stride) + 1 per strided layer when streaming."""
         g, w = self.g, self.w
         x = np.asarray(audio, dtype=F32)
         if x.ndim == 2:
             x = x[:, None, :]
+        streaming = use_cache and cache is not None
+        idx = [int(i) for i in sample_indices] if streaming else None
+        if streaming:
+            assert len(idx) == x.shape[0]
+        c = cache if streaming else None
         for i in range(g.n_stages):                                 # :775-806
             p = f"encoder.downsample_layers.{i}.0.conv.conv."
-            if i == 0:
-                x = sconv1d(x, w[p + "weight"], w[p + "bias"])[0]    # stem k7 stride 1 (:732-734)
-            else:
-                x = sconv1d_strided(x, w[p + "weight"], w[p + "bias"], g.enc_ratio(i))   # k = 2r, stride r (:737-743)
+            stride = 1 if i == 0 else g.enc_ratio(i)                 # stem k7 stride 1 (:732-734); k = 2r, stride r (:737-743)
+            x = self._sconv(p, x, w[p + "weight"], w[p + "bias"], 1, stride, c, idx)
             if taps is not None:
                 taps[f"down{i}"] = x
             for j in range(g.enc_depth(i)):
-                x = self._block(i, j, x, taps)
+                x = self._block(i, j, x, taps, c, idx)
         # self.norm is Identity (disable_last_norm, :767-770); head k7 (:771, :812)
-        x = sconv1d(x, w["encoder.head.conv.conv.weight"], w["encoder.head.conv.conv.bias"])[0]
+        x = self._sconv("encoder.head", x, w["encoder.head.conv.conv.weight"], w["encoder.head.conv.conv.bias"], 1, 1, c, idx)
         return np.ascontiguousarray(x.transpose(0, 2, 1))
 
 

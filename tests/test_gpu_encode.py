@@ -126,8 +126,12 @@ def test_encode_sampling_and_errors(shallow):
     assert out.mode() is out.mean and torch.equal(out.kl(), out.mean ** 2)
     with pytest.raises(ValueError):
         enc.sampling(out, dist_type="laplace")
-    with pytest.raises(NotImplementedError):
-        enc.encode(audio, cache=object(), sample_indices=[0, 1], use_cache=True)
+    with pytest.raises(AssertionError):
+        enc.encode(audio, cache=enc.new_cache(4), use_cache=True)            # sample_indices missing (:321)
+    with pytest.raises(AssertionError):
+        enc.encode(audio, cache=enc.new_cache(4), sample_indices=[0], use_cache=True)   # length mismatch (:322-323)
+    with pytest.raises(ValueError):
+        enc.encode(audio[:, :, :5000].contiguous(), cache=enc.new_cache(4), sample_indices=[0, 1], use_cache=True)  # ragged hop
     with pytest.raises(ValueError):
         enc.encode(torch.zeros(1, 2, 6400, device="cuda"))                   # stereo
     with pytest.raises(RuntimeError):
@@ -151,5 +155,54 @@ def test_vv_encode_workspace_too_small(shallow):
     ws = torch.empty(1 << 20, dtype=torch.uint8, device="cuda")
     p = (ws.data_ptr() + 1023) & ~1023
     rc = lib.vv_encode(enc._h, C.c_void_p(audio.data_ptr()), 0, 1, L, C.c_void_p(mean.data_ptr()), C.c_void_p(p),
-                       (1 << 20) - 1024, None)
+                       (1 << 20) - 1024, None, None, None)
     assert rc == -6 and b"cannot hold one utterance" in lib.vv_last_error()
+
+
+def test_streaming_encode_replay_matches_reference():
+    """Replays the reference's streaming encode call pattern (late joiner -> all-or-nothing reset :204-207, set_to_zero
+    :234-241, multi-hop chunks) recorded in tests/golden/enc_stream_stress.npz, in strict-quirk mode."""
+    from test_oracle_encoder import replay_encode_stream
+    z, meta = load_golden("enc_stream_stress")
+    geom = geom_from_meta(meta)
+    enc = _encoder(geom, make_encoder_weights(geom, meta["init"], meta["wseed"]), strict_reference_quirks=True)
+    cache = enc.new_cache(8)
+
+    def run(x, idx):
+        return enc.encode(torch.from_numpy(x).cuda(), cache=cache, sample_indices=idx, use_cache=True).mean.cpu().numpy()
+    n = 0
+    for s, y, ref in replay_encode_stream(z, meta, run, cache.set_to_zero):
+        assert y.shape == ref.shape
+        print(s, _assert_parity(y, ref, f"step {s}"))
+        n += 1
+    assert n == 6
+
+
+def test_streaming_encode_equals_offline(shallow):
+    """Whole-hop chunks of any size, fed through the device state, reproduce the offline latents; a foreign cache object
+    (standing in for a genuine VibeVoiceTokenizerStreamingCache) gets the state hung off it; streams are independent."""
+    geom, w, enc = shallow
+    B, hops = 3, 9
+    audio = torch.from_numpy(make_audio(B, 3200 * hops, 41)).cuda()
+    off = enc.encode(audio).mean
+
+    class ForeignCache:                                   # the reference cache's surface that generate() touches
+        def set_to_zero(self, idx):
+            self.zeroed = list(idx)
+    cache = ForeignCache()
+    idx = torch.tensor([5, 0, 2], dtype=torch.int32, device="cuda")         # device indices: no host sync
+    outs = []
+    for a, b in ((0, 1), (1, 2), (2, 6), (6, 7), (7, 9)):
+        outs.append(enc.encode(audio[:, :, 3200 * a:3200 * b].contiguous(), cache=cache, sample_indices=idx, use_cache=True).mean)
+    st = torch.cat(outs, 1)
+    scale = float(off.abs().max())
+    assert float((st - off).abs().max()) <= 1e-3 * scale, float((st - off).abs().max()) / scale
+    # set_to_zero through the foreign object restarts only that stream; the others continue
+    cache.set_to_zero(torch.tensor([0], device="cuda"))
+    assert cache.zeroed == [0] or len(cache.zeroed) == 1
+    nxt = torch.from_numpy(make_audio(B, 3200, 42)).cuda()
+    y = enc.encode(nxt, cache=cache, sample_indices=idx, use_cache=True).mean
+    fresh = enc.encode(nxt[1:2]).mean                                        # stream 0 restarted from silence
+    assert float((y[1:2] - fresh).abs().max()) <= 1e-3 * scale
+    cont = enc.encode(torch.cat([audio, nxt], 2)).mean[:, hops:]             # streams 5 and 2 continued
+    assert float((y[0] - cont[0]).abs().max()) <= 1e-3 * scale and float((y[2] - cont[2]).abs().max()) <= 1e-3 * scale

@@ -10,9 +10,16 @@
 //     out[q] = b + W[:, 0:r*Cin] . xb[q] + W[:, r*Cin:2r*Cin] . xb[q + 1]       (xb rows of r*Cin elements)
 // The head SConv1d(2048 -> 64, k7) (:771, :812) is the 7-tap GEMM of the decoder's stem on a copy with 6 zero
 // rows in front.
+//
+// Streaming form (SConv1d._forward_streaming, :327-382): a call's left context is the stream's cached last
+// `context_size` inputs instead of zeros (stem / head: 6 rows; strided conv: k - 1 - (r - 1) = r rows), and the cache
+// becomes the last `context_size` rows of [context, input].  With chunks that are whole hops no strided conv ever
+// needs right padding, and the stream reproduces the offline result (reference: 2e-6, verified).  The context rows
+// live in the same padded bf16 copies, filled from the device state by enc_context_kernel.
 #pragma once
 #include <cuda_bf16.h>
 #include <stdint.h>
+#include "mixer.cuh"
 
 namespace vv {
 
@@ -25,6 +32,7 @@ struct EncStemArgs {
   const float* b;             // [32]
   float* x;                   // [nbatch, L, 32] fp32
   int nbatch, L;
+  StateRef st;                // stream context: fp32 [6] last samples (null base = offline, zeros)
 };
 
 constexpr int ENC_STEM_ROWS = 4;   // rows per thread (the 10-sample window is shared between them)
@@ -44,6 +52,13 @@ __global__ void __launch_bounds__(256) enc_stem_kernel(const EncStemArgs p) {
     const int b = (int)(g / groups_pb);
     const long long t0 = (g - (long long)b * groups_pb) * RT;
     const long long base = (long long)b * p.audio_bstride;
+    const float* ctx = nullptr;
+    if (t0 < 6 && p.st.base != nullptr) {
+      const uint8_t* rd8;
+      uint8_t* wr8;
+      p.st.resolve(b, rd8, wr8);
+      ctx = reinterpret_cast<const float*>(rd8);
+    }
     float win[6 + RT];
 #pragma unroll
     for (int k = 0; k < 6 + RT; ++k) {
@@ -52,6 +67,8 @@ __global__ void __launch_bounds__(256) enc_stem_kernel(const EncStemArgs p) {
       if (t >= 0 && t < p.L)
         v = p.audio_is_bf16 ? __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(p.audio)[base + t])
                             : reinterpret_cast<const float*>(p.audio)[base + t];
+      else if (t < 0 && ctx != nullptr)
+        v = ctx[6 + t];
       win[k] = v;
     }
     float* xo = p.x + ((long long)b * p.L + t0) * C + quad * 4;
@@ -69,26 +86,66 @@ __global__ void __launch_bounds__(256) enc_stem_kernel(const EncStemArgs p) {
       *reinterpret_cast<float4*>(xo + (long long)r * C) = acc;
     }
   }
+  // new context = last 6 samples of [old context, audio]  (:371-382)
+  if (p.st.base != nullptr) {
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < p.nbatch * 6; i += gridDim.x * blockDim.x) {
+      const int b = i / 6, j = i - b * 6;
+      const uint8_t* rd8;
+      uint8_t* wr8;
+      p.st.resolve(b, rd8, wr8);
+      const long long t = (long long)p.L - 6 + j;
+      float v;
+      if (t >= 0) {
+        const long long off = (long long)b * p.audio_bstride + t;
+        v = p.audio_is_bf16 ? __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(p.audio)[off])
+                            : reinterpret_cast<const float*>(p.audio)[off];
+      } else {
+        v = reinterpret_cast<const float*>(rd8)[6 + t];
+      }
+      reinterpret_cast<float*>(wr8)[j] = v;
+    }
+  }
 }
 
-// ---- zero the pad rows of a padded bf16 copy [nbatch, rpb, C]: rows [0, off) and [off + rows, rpb) ------------
-struct EncPadArgs {
+// ---- context / pad rows of a padded bf16 copy [nbatch, rpb, C]: data rows [off, off + rows) were written by the
+// producing epilogue; rows [0, off) = the consumer conv's left context (zeros offline, the stream's cached rows
+// otherwise), rows [off + rows, rpb) = right padding (zeros; offline only).  With a state the stream's new context =
+// the last `off` rows of [context, data] is written to the other bank.
+struct EncContextArgs {
   __nv_bfloat16* xb;
   int nbatch, rows, off, C;
   long long rpb;
+  StateRef st;                // bf16 [off][C] (null base = offline)
 };
 
-__global__ void __launch_bounds__(256) enc_pad_kernel(const EncPadArgs p) {
+__global__ void __launch_bounds__(256) enc_context_kernel(const EncContextArgs p) {
   const int c8 = p.C / 8;                                   // 16-byte cells per row
-  const long long pad_rows = p.rpb - p.rows;                // per item
+  const long long pad_rows = p.rpb - p.rows;                // per item: off context rows + tail rows
   const long long total = pad_rows * p.nbatch * c8;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
        i += (long long)gridDim.x * blockDim.x) {
     const long long cell = i % c8, pr = i / c8;
-    const long long b = pr / pad_rows;
-    long long row = pr - b * pad_rows;
-    if (row >= p.off) row += p.rows;                        // tail pad
-    *reinterpret_cast<uint4*>(p.xb + (b * p.rpb + row) * p.C + cell * 8) = make_uint4(0u, 0u, 0u, 0u);
+    const int b = (int)(pr / pad_rows);
+    const long long row = pr - (long long)b * pad_rows;     // 0 .. off-1: context; >= off: tail
+    __nv_bfloat16* item = p.xb + (long long)b * p.rpb * p.C;
+    const uint8_t* rd8 = nullptr;
+    uint8_t* wr8 = nullptr;
+    if (p.st.base != nullptr) p.st.resolve(b, rd8, wr8);
+    uint4 v = make_uint4(0u, 0u, 0u, 0u);
+    if (row < p.off) {
+      if (rd8 != nullptr) v = *reinterpret_cast<const uint4*>(rd8 + (row * p.C + cell * 8) * 2);
+      *reinterpret_cast<uint4*>(item + row * p.C + cell * 8) = v;
+      if (wr8 != nullptr) {
+        // new context row `row` = row (rows + row) of [context | data]: a data row, or (short chunk) an old context row
+        const long long src = p.rows + row;
+        uint4 nv;
+        if (src < p.off) nv = rd8 ? *reinterpret_cast<const uint4*>(rd8 + (src * p.C + cell * 8) * 2) : make_uint4(0u, 0u, 0u, 0u);
+        else nv = *reinterpret_cast<const uint4*>(item + src * p.C + cell * 8);
+        *reinterpret_cast<uint4*>(wr8 + (row * p.C + cell * 8) * 2) = nv;
+      }
+    } else {
+      *reinterpret_cast<uint4*>(item + (row + p.rows) * p.C + cell * 8) = v;
+    }
   }
 }
 

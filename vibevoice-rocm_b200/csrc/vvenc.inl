@@ -1,6 +1,6 @@
 // vvenc.inl — host side of the ENCODER path behind the C ABI (included at the end of vvdec.cu: it reuses that file's
 // weight packer and launch helpers).  Replaces TokenizerEncoder.forward (modular_vibevoice_tokenizer.py:810-813) as
-// called by VibeVoiceAcousticTokenizerModel.encode (:1081-1085), offline form (cache=None / use_cache=False).
+// called by VibeVoiceAcousticTokenizerModel.encode (:1081-1085), offline and streaming form (whole-hop chunks).
 //
 // The encoder is the decoder's stage list walked backwards: stage i has C = n_filters * 2^i channels, the decoder's
 // depth of stage n-1-i (:1019-1028) and is entered through a strided SConv1d with the decoder's ratio n-1-i (:701).
@@ -10,6 +10,9 @@ struct vv_encoder {
   float* stem_w = nullptr;      // [7][32] tap-major
   float* stem_b = nullptr;      // [32]
   vv::DenseW head;              // SConv1d(C_last -> vae_dim, k7) as a 7-tap GEMM
+  // stream-state layout inside a slot (core.state_slot_bytes): stem fp32 [6]; per stage i >= 1 (StageW::up_state_off)
+  // bf16 [r][C/2] = the strided conv's context; per block fp32 [6][C] (BlockW::state_off); head bf16 [6][C_last]
+  long long stem_state_off = 0, head_state_off = 0;
 };
 
 namespace {
@@ -64,7 +67,7 @@ long long enc_pass_bytes(const vv_encoder* e, long long nb, long long L) {
 }
 
 int enc_run_pass(vv_encoder* e, const void* audio, int audio_is_bf16, long long audio_bstride, int nb, long long L,
-                 float* mean, uint8_t* ws, cudaStream_t s) {
+                 float* mean, uint8_t* ws, vv_state* st, const int32_t* slots, cudaStream_t s) {
   vv_decoder* d = &e->core;
   const vv_config& c = d->cfg;
   const int S = c.n_stages;
@@ -91,6 +94,7 @@ int enc_run_pass(vv_encoder* e, const void* audio, int audio_is_bf16, long long 
       EncStemArgs p;
       p.audio = audio; p.audio_is_bf16 = audio_is_bf16; p.audio_bstride = audio_bstride;
       p.w = e->stem_w; p.b = e->stem_b; p.x = X; p.nbatch = nb; p.L = rows_pb;
+      p.st = make_state_ref(st, slots, e->stem_state_off);
       const long long threads = ((long long)rows_pb + ENC_STEM_ROWS - 1) / ENC_STEM_ROWS * nb * 8;
       enc_stem_kernel<<<(unsigned)std::min<long long>((threads + 255) / 256, 148LL * 64), 256, 0, s>>>(p);
       d->launches++;
@@ -105,15 +109,6 @@ int enc_run_pass(vv_encoder* e, const void* audio, int audio_is_bf16, long long 
       rc = launch_gemm(d, PXB, rows[i] + 1, rows_pb, nb, sw.up, eo, s, VV_K_DOWNSAMPLE, i);
       if (rc != VV_OK) return rc;
     }
-    {  // pad rows of this stage's bf16 copy (the last block's epilogue fills the rest)
-      EncPadArgs pp;
-      pp.xb = XB; pp.nbatch = nb; pp.rows = rows_pb; pp.off = bo.xb_off; pp.C = C; pp.rpb = bo.xb_rpb;
-      const long long cells = (bo.xb_rpb - rows_pb) * nb * (C / 8);
-      enc_pad_kernel<<<(unsigned)std::max<long long>(1, std::min<long long>((cells + 255) / 256, 148LL * 16)), 256, 0, s>>>(pp);
-      d->launches++;
-      VV_CUDA(cudaGetLastError());
-      d->mark(VV_K_PAD, i, s);
-    }
     PadOut po;
     po.rpb = bo.xb_rpb; po.off = bo.xb_off;
     const int nblk = (int)sw.blocks.size();
@@ -122,13 +117,13 @@ int enc_run_pass(vv_encoder* e, const void* audio, int audio_is_bf16, long long 
       const BlockW& bw = sw.blocks[j];
       const bool last = (j == nblk - 1);
       if (block_fused_supported(d, C)) {
-        rc = launch_block_fused(d, C, bw, X, Y, last ? XB : nullptr, nb, rows_pb, nullptr, nullptr, s, po);
+        rc = launch_block_fused(d, C, bw, X, Y, last ? XB : nullptr, nb, rows_pb, st, slots, s, po);
         if (rc != VV_OK) return rc;
         d->mark(VV_K_BLOCK_FUSED, i, s);
         std::swap(X, Y);
         continue;
       }
-      rc = launch_mixer(d, bw, C, X, Y, A, nb, rows_pb, nullptr, nullptr, s);
+      rc = launch_mixer(d, bw, C, X, Y, A, nb, rows_pb, st, slots, s);
       if (rc != VV_OK) return rc;
       d->mark(VV_K_MIXER, i, s);
       if (ffn_fused_supported(d, C)) {
@@ -140,12 +135,29 @@ int enc_run_pass(vv_encoder* e, const void* audio, int audio_is_bf16, long long 
       rc = launch_ffn_pair(d, C, bw, A, Y, X, H, last ? XB : nullptr, po, nb, rows_pb, i, s);
       if (rc != VV_OK) return rc;
     }
+    {  // context rows (zeros, or the stream's cached rows) and right padding of this stage's bf16 copy; the data rows
+       // were written by the last block's epilogue.  With a state this also saves the stream's new context.
+      EncContextArgs cp;
+      cp.xb = XB; cp.nbatch = nb; cp.rows = rows_pb; cp.off = bo.xb_off; cp.C = C; cp.rpb = bo.xb_rpb;
+      cp.st = make_state_ref(st, slots, i + 1 < S ? d->stages[i + 1].up_state_off : e->head_state_off);
+      const long long cells = (bo.xb_rpb - rows_pb) * nb * (C / 8);
+      enc_context_kernel<<<(unsigned)std::max<long long>(1, std::min<long long>((cells + 255) / 256, 148LL * 16)), 256, 0, s>>>(cp);
+      d->launches++;
+      VV_CUDA(cudaGetLastError());
+      d->mark(VV_K_PAD, i, s);
+    }
     if (i == S - 1) {   // self.norm is Identity (disable_last_norm, :767-770); head k7 -> mean [nb, T, vae_dim]
       EpiOut eo;
       eo.epi = EPI_BIAS_F32; eo.out_f32 = mean;
       rc = launch_gemm(d, XB, rows[i] + 6, rows_pb, nb, e->head, eo, s, VV_K_ENC_HEAD, i);
       if (rc != VV_OK) return rc;
     }
+  }
+  if (st != nullptr) {
+    state_flip_kernel<<<(nb + 127) / 128, 128, 0, s>>>(slots, nb, st->parity);
+    d->launches++;
+    VV_CUDA(cudaGetLastError());
+    d->mark(VV_K_STATE, 0, s);
   }
   return VV_OK;
 }
@@ -189,6 +201,9 @@ extern "C" int32_t vv_encoder_finalize(vv_encoder* e) {
   d->param_count = 0;
   const vv_config& c = d->cfg;
   Packer pk{d};
+  long long soff = 0;
+  e->stem_state_off = soff;
+  soff += 32;                                               // fp32 [6], padded to 32 B
   {  // stem SConv1d(1 -> n_filters, k7) (:732-734), fp32 tap-major
     const int C = enc_channels(c, 0);
     const auto* w = pk.get("encoder.downsample_layers.0.0.conv.conv.weight", {C, 1, 7});
@@ -221,10 +236,14 @@ extern "C" int32_t vv_encoder_finalize(vv_encoder* e) {
             wp[(size_t)co * K + (size_t)j * Cin + ci] = f32_to_bf16_rne((*w)[((size_t)co * Cin + ci) * (2 * r) + j]);
       pk.dense(st.up, wp, *b, C, r * Cin, 2);
       st.ratio = r;
+      st.up_state_off = soff;                               // bf16 [r][Cin]: context_size = k - 1 - (r - 1) = r rows (:282)
+      soff += align_up((long long)r * Cin * 2, 16);
     }
     for (int j = 0; j < enc_depth(c, i) && pk.status == VV_OK; ++j) {
       BlockW bw;
       if (!pk.block("encoder.stages." + std::to_string(i) + "." + std::to_string(j) + ".", C, bw)) break;
+      bw.state_off = soff;
+      soff += 6LL * C * 4;
       st.blocks.push_back(bw);
     }
     d->stages.push_back(st);
@@ -240,9 +259,12 @@ extern "C" int32_t vv_encoder_finalize(vv_encoder* e) {
           for (int j = 0; j < 7; ++j)
             wp[(size_t)co * 7 * C + (size_t)j * C + ci] = f32_to_bf16_rne((*w)[((size_t)co * C + ci) * 7 + j]);
       pk.dense(e->head, wp, *b, D, C, 7);
+      e->head_state_off = soff;                             // bf16 [6][C_last]
+      soff += align_up(6LL * C * 2, 16);
     }
   }
   if (pk.status != VV_OK) return pk.status;
+  d->state_slot_bytes = align_up(soff, 256);
   d->staged.clear();
   d->staged_shape.clear();
   d->finalized = true;
@@ -272,14 +294,27 @@ extern "C" int64_t vv_encoder_workspace_bytes(const vv_encoder* e, int32_t B, in
   return enc_pass_bytes(e, B, L);
 }
 
+extern "C" int32_t vv_encoder_state_create(const vv_encoder* e, int32_t n_slots, vv_state** out) {
+  if (!e) { set_error("null encoder"); return VV_ERR_INVALID_ARG; }
+  return vv_state_create(&e->core, n_slots, out);
+}
+
 extern "C" int32_t vv_encode(vv_encoder* e, const void* audio, int32_t audio_dtype, int32_t B, int64_t L, float* mean,
-                             void* workspace, int64_t workspace_bytes, void* cuda_stream) {
+                             void* workspace, int64_t workspace_bytes, vv_state* state, const int32_t* slot_ids,
+                             void* cuda_stream) {
   if (!e || !audio || !mean || !workspace) { set_error("null argument"); return VV_ERR_INVALID_ARG; }
   vv_decoder* d = &e->core;
   if (!d->finalized) { set_error("vv_encoder_finalize has not succeeded"); return VV_ERR_NOT_FINALIZED; }
   if (B < 1 || L < 1 || L >= (1LL << 31)) { set_error("B=%d L=%lld", B, (long long)L); return VV_ERR_BAD_SHAPE; }
   if (audio_dtype != VV_F32 && audio_dtype != VV_BF16) { set_error("audio dtype must be f32 or bf16"); return VV_ERR_BAD_DTYPE; }
   if (((uintptr_t)workspace & 1023) != 0) { set_error("workspace must be 1 KB aligned"); return VV_ERR_INVALID_ARG; }
+  if (state != nullptr && slot_ids == nullptr) { set_error("state given without slot_ids"); return VV_ERR_INVALID_ARG; }
+  if (state != nullptr && state->dec != d) { set_error("state belongs to another encoder / decoder"); return VV_ERR_INVALID_ARG; }
+  if (state != nullptr && L % d->hop != 0) {
+    // a ragged chunk would be right-padded by every strided conv in mid-stream (:127-133): not the same signal
+    set_error("streaming encode takes whole hops: L=%lld is not a multiple of %d", (long long)L, d->hop);
+    return VV_ERR_BAD_SHAPE;
+  }
   VV_CUDA(cudaSetDevice(d->cfg.device));
   cudaStream_t s = reinterpret_cast<cudaStream_t>(cuda_stream);
   uint8_t* ws = reinterpret_cast<uint8_t*>(workspace);
@@ -287,7 +322,7 @@ extern "C" int32_t vv_encode(vv_encoder* e, const void* audio, int32_t audio_dty
   const long long T = vv_encoder_frames(e, L);
   int32_t rc = VV_OK;
   if (enc_pass_bytes(e, 1, L) > workspace_bytes) {
-    // one utterance must fit: splitting in time needs the streaming form of the strided convs (not built yet)
+    // one utterance must fit; a caller with less memory feeds whole-hop chunks through a stream state
     set_error("workspace of %lld bytes cannot hold one utterance of %lld samples (%lld needed)",
               (long long)workspace_bytes, (long long)L, enc_pass_bytes(e, 1, L));
     rc = VV_ERR_WORKSPACE;
@@ -297,7 +332,7 @@ extern "C" int32_t vv_encode(vv_encoder* e, const void* audio, int32_t audio_dty
     for (int b0 = 0; b0 < B && rc == VV_OK; b0 += nb) {
       const int n = std::min(nb, B - b0);
       rc = enc_run_pass(e, reinterpret_cast<const uint8_t*>(audio) + (size_t)b0 * L * asz, audio_dtype == VV_BF16, L, n, L,
-                        mean + (size_t)b0 * T * d->cfg.vae_dim, ws, s);
+                        mean + (size_t)b0 * T * d->cfg.vae_dim, ws, state, state ? slot_ids + b0 : nullptr, s);
     }
   }
   prof_collect(d, s);

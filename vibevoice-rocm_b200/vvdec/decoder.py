@@ -75,7 +75,8 @@ def _dtype_code(dt: torch.dtype) -> int:
 
 
 class B200StreamingCache:
-    """Device-resident per-stream conv state (replaces VibeVoiceTokenizerStreamingCache, :193-256).
+    """Device-resident per-stream conv state (replaces VibeVoiceTokenizerStreamingCache, :193-256).  ``decoder`` is a
+    B200AcousticDecoder or a B200AcousticEncoder (each keeps its own state: the reference keys its dict by layer id).
 
     One slot per ``sample_idx``; every stateful layer's causal context lives in one allocation and is
     updated in place by the decode kernels.  ``set_to_zero`` / ``clear`` keep the reference's meaning.
@@ -85,7 +86,8 @@ class B200StreamingCache:
         self._dec = decoder
         self._lib = _capi.load()
         h = C.c_void_p()
-        _capi.check(self._lib.vv_state_create(decoder._h, int(n_slots), C.byref(h)), "vv_state_create")
+        create = getattr(self._lib, getattr(decoder, "_STATE_CREATE", "vv_state_create"))   # encoder: vv_encoder_state_create
+        _capi.check(create(decoder._h, int(n_slots), C.byref(h)), "vv_state_create")
         self._h = h
         self.n_slots = int(n_slots)
         self.seen = set()            # sample indices that own live state (host view, for the strict quirk)
@@ -334,9 +336,8 @@ def patch(model, encode: bool = False, **kw) -> B200AcousticDecoder:
     then runs unmodified.  Returns the decoder object.
 
     ``encode=True`` also swaps ``encode`` (the offline voice-prompt prefill, modeling_vibevoice_inference.py:154)
-    for the B200 encoder (``tok._b200_encoder``).  Streaming encode calls (``use_cache=True`` with a cache) are not
-    built on this path and raise NotImplementedError, so only patch ``encode`` on a tokenizer whose callers use the
-    offline form (the acoustic tokenizer; not the semantic tokenizer inside ``generate()``)."""
+    for the B200 encoder (``tok._b200_encoder``).  Streaming encode calls (``use_cache=True`` with a cache) must
+    feed whole hops (multiples of 3200 samples), which is what ``generate()`` does (:656-662)."""
     tok = model
     for attr in ("model", "acoustic_tokenizer"):
         if hasattr(tok, attr) and not hasattr(tok, "decoder"):

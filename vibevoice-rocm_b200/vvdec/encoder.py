@@ -6,8 +6,9 @@ Mirrors, by name and argument meaning:
   * ``VibeVoiceTokenizerEncoderOutput`` (mean / std, ``sample``, ``kl``, ``mode``) — :954-1000
   * ``VibeVoiceAcousticTokenizerModel.sampling`` — :1087-1097
 PyTorch is used for device memory, streams and the random draws of ``sample``; the encoder arithmetic runs in the
-CUDA library.  Offline form only: ``use_cache=True`` raises NotImplementedError (the streaming strided convs of
-SConv1d._forward_streaming are not built on this path yet).
+CUDA library.  Streaming (``use_cache=True`` with a cache and ``sample_indices``, SConv1d._forward_streaming :327-382)
+takes chunks that are whole hops (multiples of 3200 samples — what generate() feeds the semantic tokenizer,
+modeling_vibevoice_inference.py:656-662); ragged streaming chunks raise ValueError.
 """
 from __future__ import annotations
 
@@ -18,7 +19,7 @@ from typing import Dict, Optional, Union
 import torch
 
 from . import _capi
-from .decoder import Geometry, _dtype_code
+from .decoder import B200StreamingCache, Geometry, _dtype_code
 
 
 @dataclass
@@ -46,10 +47,14 @@ class B200TokenizerEncoderOutput:
 
 
 class B200AcousticEncoder:
-    """Drop-in for the encode half of VibeVoiceAcousticTokenizerModel on one B200."""
+    """Drop-in for the encode half of VibeVoiceAcousticTokenizerModel (and, with vae_dim=128, for
+    VibeVoiceSemanticTokenizerModel.encode, :1118-1186 — the same TokenizerEncoder) on one B200."""
+
+    _STATE_CREATE = "vv_encoder_state_create"
 
     def __init__(self, geometry: Geometry = Geometry(), device=None, gemm_path: int = 0,
-                 max_workspace_bytes: int = 24 << 30, fix_std: float = 0.5, std_dist_type: str = "gaussian"):
+                 max_workspace_bytes: int = 24 << 30, fix_std: float = 0.5, std_dist_type: str = "gaussian",
+                 default_slots: int = 256, strict_reference_quirks: bool = False):
         self._lib = _capi.load()
         if not torch.cuda.is_available():
             raise RuntimeError("vvdec needs a CUDA device (sm_100a); there is no CPU fallback")
@@ -71,6 +76,8 @@ class B200AcousticEncoder:
         self.max_workspace_bytes = int(max_workspace_bytes)
         self.fix_std = fix_std                       # config.fix_std (:1014)
         self.std_dist_type = std_dist_type           # config.std_dist_type (:1015)
+        self.default_slots = int(default_slots)
+        self.strict_reference_quirks = bool(strict_reference_quirks)
         self._ws: Optional[torch.Tensor] = None
         self.vae_dim = geometry.vae_dim
         self.hop = geometry.hop
@@ -128,6 +135,40 @@ class B200AcousticEncoder:
     def take_launch_count(self) -> int:
         return int(self._lib.vv_encoder_take_launch_count(self._h))
 
+    # -- streaming state ------------------------------------------------------------------------------
+    def _indices_list(self, sample_indices):
+        if isinstance(sample_indices, torch.Tensor):
+            return [int(i) for i in sample_indices.tolist()]
+        return [int(i) for i in sample_indices]
+
+    def _indices_tensor(self, sample_indices) -> torch.Tensor:
+        if isinstance(sample_indices, torch.Tensor):
+            return sample_indices.to(device=self.device, dtype=torch.int32).contiguous()
+        return torch.tensor(list(sample_indices), dtype=torch.int32, device=self.device)
+
+    def new_cache(self, n_slots: Optional[int] = None) -> B200StreamingCache:
+        return B200StreamingCache(self, n_slots or self.default_slots)
+
+    def _state_for(self, cache) -> B200StreamingCache:
+        """Our cache, or any object the caller uses as the reference cache (a genuine VibeVoiceTokenizerStreamingCache):
+        the encoder's device state hangs off it and its set_to_zero / clear are forwarded (same as the decoder)."""
+        if isinstance(cache, B200StreamingCache):
+            if cache._dec is not self:
+                raise ValueError("this cache belongs to another decoder / encoder")
+            return cache
+        st = getattr(cache, "_b200_enc_state", None)
+        if st is None or st._dec is not self:
+            st = self.new_cache()
+            cache._b200_enc_state = st
+            for name in ("set_to_zero", "clear"):
+                orig = getattr(cache, name, None)
+
+                def fwd(*a, _orig=orig, _name=name, **k):
+                    getattr(st, _name)(*a, **k)
+                    return _orig(*a, **k) if _orig is not None else None
+                setattr(cache, name, fwd)
+        return st
+
     def _workspace(self, B: int, L: int) -> torch.Tensor:
         need = min(self.workspace_bytes(B, L), max(self.max_workspace_bytes, self.workspace_bytes(1, L)))
         if self._ws is None or self._ws.numel() < need + 1024:
@@ -138,14 +179,13 @@ class B200AcousticEncoder:
     # -- the reference entry points -------------------------------------------------------------------
     @torch.no_grad()
     def encode(self, audio, cache=None, sample_indices=None, use_cache=False, debug=False):
-        """Same contract as VibeVoiceAcousticTokenizerModel.encode (:1081-1085), offline form.
+        """Same contract as VibeVoiceAcousticTokenizerModel.encode (:1081-1085).
 
         audio: [B, 1, L] (or [B, L]) float32 / bfloat16 on this encoder's device.  Returns
         B200TokenizerEncoderOutput(mean [B, ceil(L / hop), vae_dim] in the audio's dtype, std=fix_std).
+        With ``use_cache=True`` and a cache the call continues the streams named by ``sample_indices``
+        (L must be a multiple of the hop).
         """
-        if use_cache and cache is not None:
-            raise NotImplementedError("streaming encode (use_cache=True) is not built on the B200 path; "
-                                      "encode whole utterances offline")
         if not isinstance(audio, torch.Tensor) or audio.dim() not in (2, 3):
             raise ValueError("audio must be a [B, 1, L] or [B, L] tensor")
         if audio.dim() == 3:
@@ -161,15 +201,35 @@ class B200AcousticEncoder:
         if B == 0 or L == 0:
             return B200TokenizerEncoderOutput(mean=audio.new_zeros((B, T, self.vae_dim)), std=self.fix_std)
         audio = audio.contiguous()
+        state_h, slots = None, None
+        if use_cache and cache is not None:             # :317
+            if sample_indices is None:
+                raise AssertionError("sample_indices must be provided for streaming mode")       # :321
+            st = self._state_for(cache)
+            slots = self._indices_tensor(sample_indices)
+            if slots.numel() != B:
+                raise AssertionError("len(sample_indices) must match batch size")                 # :322-323
+            if L % self.hop != 0:
+                raise ValueError(f"streaming encode takes whole hops: L={L} is not a multiple of {self.hop}")
+            host_view = not (isinstance(sample_indices, torch.Tensor) and sample_indices.is_cuda)
+            if self.strict_reference_quirks or host_view:
+                idx = self._indices_list(sample_indices)
+                if max(idx) >= st.n_slots or min(idx) < 0:
+                    raise IndexError(f"sample index out of range for a cache of {st.n_slots} slots")
+                if self.strict_reference_quirks and any(i not in st.seen for i in idx):
+                    st.set_to_zero(slots)               # all-or-nothing get(): everyone restarts (:204-207)
+                st.seen.update(idx)
+            state_h = st._h
         mean = torch.empty((B, T, self.vae_dim), dtype=torch.float32, device=self.device)
         ws = self._workspace(B, L)
         ws_ptr = (ws.data_ptr() + 1023) & ~1023
         ws_bytes = ws.numel() - (ws_ptr - ws.data_ptr())
         stream = torch.cuda.current_stream(self.device).cuda_stream
         rc = self._lib.vv_encode(self._h, C.c_void_p(audio.data_ptr()), _dtype_code(audio.dtype), int(B), int(L),
-                                 C.c_void_p(mean.data_ptr()), C.c_void_p(ws_ptr), int(ws_bytes), C.c_void_p(stream))
+                                 C.c_void_p(mean.data_ptr()), C.c_void_p(ws_ptr), int(ws_bytes), state_h,
+                                 C.c_void_p(slots.data_ptr()) if slots is not None else None, C.c_void_p(stream))
         _capi.check(rc, "vv_encode")
-        self._keep = audio                              # alive until the stream has consumed it
+        self._keep = (audio, slots)                     # alive until the stream has consumed them
         return B200TokenizerEncoderOutput(mean=mean if audio.dtype == torch.float32 else mean.to(audio.dtype),
                                           std=self.fix_std)
 
