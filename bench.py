@@ -211,6 +211,34 @@ def streaming_leg(dec, geom, dev, n_streams=256, steps=300, warmup=30):
         del y
     except Exception as e:                                     # report, do not hide
         out["graph_error"] = f"{type(e).__name__}: {e}"[:200]
+    # the semantic tokenizer's streaming encode of the 3200 samples just decoded (same TokenizerEncoder,
+    # vae_dim 128; modeling_vibevoice_inference.py:656-662), audio handed over on the device
+    try:
+        import vvdec
+        from vvdec.synthetic import random_encoder_state_dict
+        sgeom = vvdec.Geometry(vae_dim=128)
+        senc = vvdec.B200AcousticEncoder(sgeom, device=dev.index, fix_std=0.0, std_dist_type="none")
+        senc.load_state_dict(random_encoder_state_dict(sgeom, seed=77))
+        ecache = senc.new_cache(n_streams)
+        chunk = step()                                         # [n_streams, 1, 3200] bf16, stays on the device
+
+        def estep():
+            return senc.encode(chunk, cache=ecache, sample_indices=idx, use_cache=True).mean
+        for _ in range(warmup):
+            estep()
+        torch.cuda.synchronize()
+        senc.take_launch_count()
+        e50, e99 = timed(estep, steps)
+        out["semantic_encode"] = {"eager_p50_ms": e50, "eager_p99_ms": e99,
+                                  "launches_per_step": int(senc.take_launch_count() // steps)}
+
+        def both():
+            return senc.encode(step(), cache=ecache, sample_indices=idx, use_cache=True).mean
+        b50, b99 = timed(both, steps)
+        out["decode_plus_semantic_encode"] = {"eager_p50_ms": b50, "eager_p99_ms": b99}
+        del senc, ecache
+    except Exception as e:
+        out["semantic_encode"] = {"error": f"{type(e).__name__}: {e}"[:200]}
     return out
 
 
