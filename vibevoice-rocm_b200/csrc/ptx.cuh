@@ -52,9 +52,13 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
 }
 // Spin on try_wait (which itself sleeps in hardware).  A protocol bug would otherwise hang the GPU until
 // the watchdog kills the box; trap instead so the launch fails loudly (legit waits are micro- to milliseconds).
+#ifndef VV_WAIT_SLEEP_AFTER
+#define VV_WAIT_SLEEP_AFTER 0      // > 0: polls before a waiting thread starts to nanosleep between polls (experiment)
+#endif
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   uint32_t spins = 0;
   while (!mbar_try_wait(bar, parity)) {
+    if (VV_WAIT_SLEEP_AFTER > 0 && spins >= VV_WAIT_SLEEP_AFTER) __nanosleep(32);
     if (++spins > (1u << 25)) __trap();
   }
 }

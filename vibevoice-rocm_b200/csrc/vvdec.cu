@@ -172,6 +172,7 @@ static int32_t init_core(const vv_config* cfg, vv_decoder* d) {
   }
   cudaDeviceProp prop;
   VV_CUDA(cudaGetDeviceProperties(&prop, cfg->device));
+  d->num_sms = prop.multiProcessorCount;
   if (prop.major != 10) {
     set_error("device %d is sm_%d%d; this library only contains sm_100a code", cfg->device, prop.major, prop.minor);
     return VV_ERR_NO_DEVICE;
@@ -478,16 +479,27 @@ struct EpiOut {
   long long bf16_row0 = 0;
 };
 
+// Opt a kernel into its dynamic shared memory size once per (kernel, device): the attribute is per device and
+// handles on different devices may share this process; calls may come from different host threads.
+template <typename F>
+int ensure_smem(F* func, int bytes, int device) {
+  static std::mutex mu;
+  static std::set<std::pair<const void*, int>> done;
+  std::lock_guard<std::mutex> lk(mu);
+  const auto key = std::make_pair(reinterpret_cast<const void*>(func), device);
+  if (done.count(key)) return VV_OK;
+  VV_CUDA(cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+  done.insert(key);
+  return VV_OK;
+}
+
 template <int BN, int BK>
-int launch_gemm_inst(const CUtensorMap& tmA, const DenseW& w, const GemmArgs& g, dim3 grid, cudaStream_t s) {
-  static bool attr_set = false;
+int launch_gemm_inst(const CUtensorMap& tmA, const DenseW& w, const GemmArgs& g, dim3 grid, int device, cudaStream_t s) {
   const size_t smem = gemm_smem_bytes<BN, BK>(g.stages);
-  if (!attr_set) {
-    constexpr int per_stage = GEMM_BM * BK * 2 + BN * BK * 2;
-    VV_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<BN, BK>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 (int)gemm_smem_bytes<BN, BK>(std::min(GEMM_MAX_STAGES, (96 * 1024) / per_stage))));
-    attr_set = true;
-  }
+  constexpr int per_stage = GEMM_BM * BK * 2 + BN * BK * 2;
+  const int rc = ensure_smem(gemm_tc_kernel<BN, BK>,
+                             (int)gemm_smem_bytes<BN, BK>(std::min(GEMM_MAX_STAGES, (96 * 1024) / per_stage)), device);
+  if (rc != VV_OK) return rc;
   gemm_tc_kernel<BN, BK><<<grid, GEMM_THREADS, smem, s>>>(tmA, w.tm, g);
   return VV_OK;
 }
@@ -555,19 +567,14 @@ int launch_gemm_impl(vv_decoder* d, const __nv_bfloat16* A, long long a_rpb, int
       else tmR = tmO;
     }
     if (rc != VV_OK) return rc;
-    static int num_sms = 0;
-    if (num_sms == 0) VV_CUDA(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, d->cfg.device));
+    const int num_sms = d->num_sms;
     const long long ntiles = best_tiles * (w.N / w.BN);
     const unsigned grid2 = (unsigned)std::min<long long>(ntiles, num_sms);
-    static bool attr_set[3][2] = {{false, false}, {false, false}, {false, false}};
     const bool deep = nk >= 32;   // K >= 2048: mainloop-dominated
 #define VV_G2_LAUNCH(E, D)                                                                                  \
     do {                                                                                                      \
-      if (!attr_set[E][D]) {                                                                                  \
-        VV_CUDA(cudaFuncSetAttribute(gemm_tc2_kernel<E, D>, cudaFuncAttributeMaxDynamicSharedMemorySize,      \
-                                     (int)Gemm2Cfg<E, D>::TOTAL));                                            \
-        attr_set[E][D] = true;                                                                                \
-      }                                                                                                       \
+      rc = ensure_smem(gemm_tc2_kernel<E, D>, (int)Gemm2Cfg<E, D>::TOTAL, d->cfg.device);                     \
+      if (rc != VV_OK) return rc;                                                                             \
       gemm_tc2_kernel<E, D><<<grid2, G2Warps<E>::THREADS, Gemm2Cfg<E, D>::TOTAL, s>>>(tmA, w.tm, tmR, tmO, g);         \
     } while (0)
     if (e.epi == EPI_BIAS_F32) { if (deep) VV_G2_LAUNCH(EPI_BIAS_F32, true); else VV_G2_LAUNCH(EPI_BIAS_F32, false); }
@@ -580,12 +587,12 @@ int launch_gemm_impl(vv_decoder* d, const __nv_bfloat16* A, long long a_rpb, int
   const long long n_cta = best_tiles * (w.N / w.BN);
   if (n_cta > 0x7fffffffLL) { set_error("internal: %lld tiles exceed the launch limit", n_cta); return VV_ERR_WORKSPACE; }
   dim3 grid((unsigned)n_cta);
-  if (w.BN == 128 && w.BK == 64) rc = launch_gemm_inst<128, 64>(tmA, w, g, grid, s);
-  else if (w.BN == 64 && w.BK == 64) rc = launch_gemm_inst<64, 64>(tmA, w, g, grid, s);
-  else if (w.BN == 32 && w.BK == 64) rc = launch_gemm_inst<32, 64>(tmA, w, g, grid, s);
-  else if (w.BN == 128 && w.BK == 32) rc = launch_gemm_inst<128, 32>(tmA, w, g, grid, s);
-  else if (w.BN == 64 && w.BK == 32) rc = launch_gemm_inst<64, 32>(tmA, w, g, grid, s);
-  else if (w.BN == 32 && w.BK == 32) rc = launch_gemm_inst<32, 32>(tmA, w, g, grid, s);
+  if (w.BN == 128 && w.BK == 64) rc = launch_gemm_inst<128, 64>(tmA, w, g, grid, d->cfg.device, s);
+  else if (w.BN == 64 && w.BK == 64) rc = launch_gemm_inst<64, 64>(tmA, w, g, grid, d->cfg.device, s);
+  else if (w.BN == 32 && w.BK == 64) rc = launch_gemm_inst<32, 64>(tmA, w, g, grid, d->cfg.device, s);
+  else if (w.BN == 128 && w.BK == 32) rc = launch_gemm_inst<128, 32>(tmA, w, g, grid, d->cfg.device, s);
+  else if (w.BN == 64 && w.BK == 32) rc = launch_gemm_inst<64, 32>(tmA, w, g, grid, d->cfg.device, s);
+  else if (w.BN == 32 && w.BK == 32) rc = launch_gemm_inst<32, 32>(tmA, w, g, grid, d->cfg.device, s);
   else { set_error("no GEMM instance for BN=%d BK=%d", w.BN, w.BK); return VV_ERR_UNSUPPORTED; }
   if (rc != VV_OK) return rc;
   VV_CUDA(cudaGetLastError());
@@ -596,14 +603,9 @@ int launch_gemm_impl(vv_decoder* d, const __nv_bfloat16* A, long long a_rpb, int
 template <int C>
 int launch_ffn_fused_inst(vv_decoder* d, const CUtensorMap& tmA, const CUtensorMap& tmR, const CUtensorMap& tmO,
                           const BlockW& bw, const FfnFusedArgs& fa, cudaStream_t s) {
-  static bool attr_set = false;
-  if (!attr_set) {
-    VV_CUDA(cudaFuncSetAttribute(ffn_fused_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 (int)FfnFusedSmem<C>::TOTAL));
-    attr_set = true;
-  }
-  static int num_sms = 0;
-  if (num_sms == 0) VV_CUDA(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, d->cfg.device));
+  const int arc = ensure_smem(ffn_fused_kernel<C>, (int)FfnFusedSmem<C>::TOTAL, d->cfg.device);
+  if (arc != VV_OK) return arc;
+  const int num_sms = d->num_sms;
   const long long ntiles = (fa.R + 127) / 128;
   const unsigned grid = (unsigned)std::min<long long>(ntiles, num_sms);
   ffn_fused_kernel<C><<<grid, FF_THREADS, FfnFusedSmem<C>::TOTAL, s>>>(tmA, tmR, tmO, bw.lin1.tm, bw.lin2.tm, fa);
@@ -641,14 +643,9 @@ int launch_ffn_fused(vv_decoder* d, int C, const BlockW& bw, const __nv_bfloat16
   if (C == 32) return launch_ffn_fused_inst<32>(d, tmA, tmR, tmO, bw, fa, s);
   if (C == 64) return launch_ffn_fused_inst<64>(d, tmA, tmR, tmO, bw, fa, s);
   // C = 128: hidden on chip, weights streamed (ffn_stream.cuh); a is read in [128 rows x 64] K blocks
-  static bool attr_set = false;
-  if (!attr_set) {
-    VV_CUDA(cudaFuncSetAttribute(ffn_stream_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 (int)FfnStreamCfg<128>::TOTAL));
-    attr_set = true;
-  }
-  static int num_sms = 0;
-  if (num_sms == 0) VV_CUDA(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, d->cfg.device));
+  rc = ensure_smem(ffn_stream_kernel<128>, (int)FfnStreamCfg<128>::TOTAL, d->cfg.device);
+  if (rc != VV_OK) return rc;
+  const int num_sms = d->num_sms;
   const long long ntiles = (R + 127) / 128;
   const unsigned grid = (unsigned)std::min<long long>(ntiles, num_sms);
   if (R + 256LL * num_sms >= (1LL << 31)) { set_error("ffn_stream: %lld rows exceed the 31-bit row index", R); return VV_ERR_BAD_SHAPE; }
@@ -666,14 +663,9 @@ bool block_fused_supported(const vv_decoder* d, int C) {
 template <int C, bool STATE>
 int launch_block_fused_inst(vv_decoder* d, const CUtensorMap& tmO, const BlockW& bw, const BlockFusedArgs& a,
                             cudaStream_t s) {
-  static bool attr_set = false;
-  if (!attr_set) {
-    VV_CUDA(cudaFuncSetAttribute(block_fused_kernel<C, STATE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 (int)BlockFusedCfg<C>::TOTAL));
-    attr_set = true;
-  }
-  static int num_sms = 0;
-  if (num_sms == 0) VV_CUDA(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, d->cfg.device));
+  const int arc = ensure_smem(block_fused_kernel<C, STATE>, (int)BlockFusedCfg<C>::TOTAL, d->cfg.device);
+  if (arc != VV_OK) return arc;
+  const int num_sms = d->num_sms;
   const long long ntiles = (long long)a.nbatch * a.tiles_pb;
   const unsigned grid = (unsigned)std::min<long long>(ntiles, num_sms);
   block_fused_kernel<C, STATE><<<grid, BlockFusedCfg<C>::THREADS, BlockFusedCfg<C>::TOTAL, s>>>(tmO, bw.lin1.tm, bw.lin2.tm, a);

@@ -5,6 +5,8 @@
 #include <cuda_bf16.h>
 #include <stdint.h>
 #include <map>
+#include <mutex>
+#include <set>
 #include <string>
 #include <vector>
 #include "../../include/vvdec.h"
@@ -51,6 +53,7 @@ struct StageW {
 struct vv_decoder {
   vv_config cfg;
   int hop = 1, halo = 0;
+  int num_sms = 148;                // of cfg.device (persistent kernels launch one CTA per SM)
   bool finalized = false;
   std::map<std::string, std::vector<float>> staged;        // name -> fp32 host copy until finalize
   std::map<std::string, std::vector<int64_t>> staged_shape;

@@ -62,7 +62,8 @@ class Geometry:
         else:
             depths = list(reversed(enc))                                        # :1024-1028
         ratios = getattr(cfg, "decoder_ratios", None) or cfg.encoder_ratios
-        return cls(vae_dim=int(cfg.vae_dim), n_filters=int(cfg.decoder_n_filters), ratios=tuple(int(r) for r in ratios),
+        nf = getattr(cfg, "decoder_n_filters", None) or cfg.encoder_n_filters    # the semantic config has no decoder_*
+        return cls(vae_dim=int(cfg.vae_dim), n_filters=int(nf), ratios=tuple(int(r) for r in ratios),
                    depths=tuple(depths), kernel_size=7, eps=float(cfg.layernorm_eps))
 
 

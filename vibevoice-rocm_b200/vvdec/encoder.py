@@ -106,9 +106,11 @@ class B200AcousticEncoder:
 
     @classmethod
     def from_reference(cls, model, **kw) -> "B200AcousticEncoder":
-        """Build from a reference VibeVoiceAcousticTokenizerModel instance (weights are copied)."""
-        kw.setdefault("fix_std", getattr(model, "fix_std", 0.5))
-        kw.setdefault("std_dist_type", getattr(model, "std_dist_type", "gaussian"))
+        """Build from a reference VibeVoiceAcousticTokenizerModel or VibeVoiceSemanticTokenizerModel instance (weights
+        are copied).  The semantic model returns ``std=None`` (:1168-1169) and samples with 'none' (:1174)."""
+        semantic = not hasattr(model, "fix_std")
+        kw.setdefault("fix_std", None if semantic else getattr(model, "fix_std"))
+        kw.setdefault("std_dist_type", "none" if semantic else getattr(model, "std_dist_type", "gaussian"))
         enc = cls(Geometry.from_config(model.config), **kw)
         return enc.load_state_dict(model.state_dict())
 
@@ -238,6 +240,8 @@ class B200AcousticEncoder:
     @torch.no_grad()
     def sampling(self, encoder_output, dist_type=None):
         """VibeVoiceAcousticTokenizerModel.sampling (:1087-1097)."""
+        if self.std_dist_type == "none":                 # semantic tokenizer (:1172-1174): always the mean
+            return encoder_output.sample(dist_type="none")
         dist_type = dist_type or self.std_dist_type
         if dist_type not in ("fix", "gaussian"):
             raise ValueError(f"Unsupported dist_type: {dist_type}, expected 'fix' or 'gaussian'")
