@@ -9,8 +9,12 @@
 //   * one CTA per SM loops over tiles (N fastest, so CTAs running together share the A tile in L2);
 //     two TMEM accumulators and two staging slots let tile i's epilogue overlap tile i+1's TMA + MMA.
 //   * 8 epilogue warps (two per TMEM lane quarter, splitting the columns) instead of 4.
-// Roles: warp 0 TMA loads (A/B ring + residual tile), warp 1 MMA issue + TMEM owner, warps 2..9 epilogue,
-// warp 10 TMA stores.
+//   * BN = 256 instantiation (N % 256 == 0 and enough tiles): one 128 x 256 accumulator per MMA tile halves the
+//     shared-memory operand traffic per flop (A 16 KB + B 32 KB per 512 MMA clocks = 96 B/clk against 128 B/clk at
+//     BN = 128, which sits exactly on the TMA/smem feed limit); the epilogue walks it as two 128-column sub-tiles
+//     through the same staging slots.
+// Roles: warp 0 TMA loads (A/B ring), warp 1 MMA issue + TMEM owner, warps 2..9 (2..17 for GELU) epilogue, last warp =
+// staging manager: TMA-stores finished sub-tiles and TMA-loads the residual of the sub-tile that takes the slot next.
 #pragma once
 #include <cuda.h>
 #include "ptx.cuh"
@@ -25,23 +29,26 @@ template <int EPI> struct G2Warps {
   static constexpr int EPI_WARPS = (EPI == EPI_GELU_BF16) ? 16 : 8;
   static constexpr int THREADS = (2 + EPI_WARPS + 1) * 32;
 };
-constexpr int G2_BN = 128, G2_BK = 64;
+constexpr int G2_BN = 128, G2_BK = 64;            // G2_BN: the narrow instantiation (and the epilogue sub-tile width)
 constexpr int G2_A_BYTES = GEMM_BM * G2_BK * 2;   // 16 KB
-constexpr int G2_B_BYTES = G2_BN * G2_BK * 2;     // 16 KB
 constexpr int G2_BOX_BYTES = 128 * 128;           // one staged box: 128 rows x 128 bytes
 
 // DEEP = long K loop (>= 32 k-blocks): the mainloop dominates, so shared memory goes to a deeper A/B ring
 // and the epilogue staging is single-buffered; otherwise the epilogue dominates and staging is double-buffered.
-template <int EPI, bool DEEP>
+template <int EPI, bool DEEP, int BN>
 struct Gemm2Cfg {
+  static_assert(BN == 128 || BN == 256, "tile width");
   static constexpr bool OUT_BF16 = (EPI == EPI_GELU_BF16);
   static constexpr int COLS_PER_BOX = OUT_BF16 ? 64 : 32;
-  static constexpr int BOXES = G2_BN / COLS_PER_BOX;                 // 2 or 4
+  static constexpr int NSUB = BN / G2_BN;                            // epilogue sub-tiles (128 columns) per MMA tile
+  static constexpr int BOXES = G2_BN / COLS_PER_BOX;                 // per sub-tile: 2 or 4
   static constexpr int STG_BYTES = BOXES * G2_BOX_BYTES;             // 32 KB or 64 KB
-  static constexpr int NSTG = DEEP ? 1 : 2;
-  static constexpr int STAGES = DEEP ? (OUT_BF16 ? 6 : 5) : (OUT_BF16 ? 5 : 3);   // A/B ring depth
+  static constexpr int B_BYTES = BN * G2_BK * 2;                     // 16 KB or 32 KB
+  static constexpr int NSTG = (BN == 128) ? (DEEP ? 1 : 2) : (OUT_BF16 ? (DEEP ? 1 : 2) : 1);
+  static constexpr int STAGES = (BN == 128) ? (DEEP ? (OUT_BF16 ? 6 : 5) : (OUT_BF16 ? 5 : 3))    // A/B ring depth
+                                            : (OUT_BF16 ? (DEEP ? 4 : 3) : 3);
   static constexpr int OFF_RING = 0;
-  static constexpr int OFF_STG = STAGES * (G2_A_BYTES + G2_B_BYTES);
+  static constexpr int OFF_STG = STAGES * (G2_A_BYTES + B_BYTES);
   static constexpr int OFF_BAR = OFF_STG + NSTG * STG_BYTES;
   static constexpr int TOTAL = OFF_BAR + 512 + 1024;
   static_assert(TOTAL <= 232448, "shared memory budget");
@@ -51,17 +58,18 @@ struct Gemm2Args {
   GemmArgs g;          // shapes, bias / gamma, optional haloed bf16 copy (out_bf16, ob_rpb, ob_off) for EPI_RESID
 };
 
-template <int EPI, bool DEEP>
+template <int EPI, bool DEEP, int BN>
 __global__ void __launch_bounds__(G2Warps<EPI>::THREADS, 1)
 gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                 const __grid_constant__ CUtensorMap tmR, const __grid_constant__ CUtensorMap tmO,
                 const GemmArgs g) {
-  using Cfg = Gemm2Cfg<EPI, DEEP>;
+  using Cfg = Gemm2Cfg<EPI, DEEP, BN>;
   constexpr int S = Cfg::STAGES;
   constexpr int NSTG = Cfg::NSTG;
-  constexpr int BN = G2_BN, BK = G2_BK;
+  constexpr int BK = G2_BK, NSUB = Cfg::NSUB, SUBW = G2_BN;
+  constexpr int G2_B_BYTES = Cfg::B_BYTES;
   constexpr int EW = G2Warps<EPI>::EPI_WARPS;
-  constexpr int CPW = BN / (EW / 4);        // columns per epilogue warp: 64 or 32
+  constexpr int CPW = SUBW / (EW / 4);      // columns per epilogue warp inside a sub-tile: 64 or 32
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   uint8_t* sA = smem + Cfg::OFF_RING;
@@ -128,15 +136,6 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       for (long long it = 0; it < my_tiles; ++it) {
         int tile_n, tile_t, tile_b;
         tile_coords(it, tile_n, tile_t, tile_b);
-        if (EPI == EPI_RESID) {                           // residual tile -> staging slot
-          const int ss = (int)(it % NSTG);
-          mbar_wait(&stg_empty[ss], (uint32_t)(((it / NSTG) & 1) ^ 1));
-          mbar_expect_tx(&stg_full[ss], Cfg::STG_BYTES);
-#pragma unroll
-          for (int c = 0; c < Cfg::BOXES; ++c)
-            tma_load_3d(sStg + ss * Cfg::STG_BYTES + c * G2_BOX_BYTES, &tmR, &stg_full[ss],
-                        tile_n * BN + c * Cfg::COLS_PER_BOX, tile_t * bt, tile_b * bb);
-        }
         for (int kb = 0; kb < nk; ++kb, ++kbg) {
           const int s = (int)(kbg % S);
           mbar_wait(&empty[s], (uint32_t)(((kbg / S) & 1) ^ 1));
@@ -180,20 +179,24 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     for (long long it = 0; it < my_tiles; ++it) {
       int tile_n, tile_t, tile_b;
       tile_coords(it, tile_n, tile_t, tile_b);
-      const int ab = (int)(it & 1), ss = (int)(it % NSTG);
-      const int n0 = tile_n * BN + colgrp * CPW;
+      const int ab = (int)(it & 1);
       mbar_wait(&acc_full[ab], (uint32_t)((it >> 1) & 1));
-      if (EPI == EPI_RESID) mbar_wait(&stg_full[ss], (uint32_t)((it / NSTG) & 1));
-      else mbar_wait(&stg_empty[ss], (uint32_t)(((it / NSTG) & 1) ^ 1));
+#pragma unroll 1
+      for (int h = 0; h < NSUB; ++h) {                    // 128-column sub-tiles of the accumulator
+      const long long e = it * NSUB + h;
+      const int ss = (int)(e % NSTG);
+      const int n0 = tile_n * BN + h * SUBW + colgrp * CPW;
+      if (EPI == EPI_RESID) mbar_wait(&stg_full[ss], (uint32_t)((e / NSTG) & 1));
+      else mbar_wait(&stg_empty[ss], (uint32_t)(((e / NSTG) & 1) ^ 1));
       tc_fence_after();
       uint8_t* stg = sStg + ss * Cfg::STG_BYTES + r * 128;
 #pragma unroll
       for (int c = 0; c < CPW / 32; ++c) {                // 32-column groups
         uint32_t v[32];
-        tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(ab * BN + colgrp * CPW + c * 32), v);
+        tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(ab * BN + h * SUBW + colgrp * CPW + c * 32), v);
         tmem_ld_wait();
         const int n = n0 + c * 32;                        // global column of v[0]
-        const int nl = colgrp * CPW + c * 32;             // column inside the tile
+        const int nl = colgrp * CPW + c * 32;             // column inside the sub-tile
         if (EPI == EPI_GELU_BF16) {
           uint8_t* box = stg + (nl >> 6) * G2_BOX_BYTES;  // 64 bf16 columns per box
 #pragma unroll
@@ -259,25 +262,45 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       fence_proxy_async_smem();
       __syncwarp();
       if (lane == 0) {
-        mbar_arrive(&acc_empty[ab]);
+        if (h == NSUB - 1) mbar_arrive(&acc_empty[ab]);
         mbar_arrive(&stg_ready[ss]);
+      }
       }
     }
   } else {
-    // ===== TMA stores ================================================================================
+    // ===== staging manager: TMA stores + residual TMA loads ===========================================
     if (elect_one()) {
-      for (long long it = 0; it < my_tiles; ++it) {
+      const long long total_e = my_tiles * NSUB;
+      auto sub_coords = [&](long long e, int& col, int& t0, int& b0) {
         int tile_n, tile_t, tile_b;
-        tile_coords(it, tile_n, tile_t, tile_b);
-        const int ss = (int)(it % NSTG);
-        mbar_wait(&stg_ready[ss], (uint32_t)((it / NSTG) & 1));
+        tile_coords(e / NSUB, tile_n, tile_t, tile_b);
+        col = tile_n * BN + (int)(e % NSUB) * SUBW;
+        t0 = tile_t * bt;
+        b0 = tile_b * bb;
+      };
+      auto load_resid = [&](long long e) {                // residual sub-tile -> its staging slot
+        const int ss = (int)(e % NSTG);
+        int col, t0, b0;
+        sub_coords(e, col, t0, b0);
+        mbar_expect_tx(&stg_full[ss], Cfg::STG_BYTES);
 #pragma unroll
         for (int c = 0; c < Cfg::BOXES; ++c)
-          tma_store_3d(&tmO, sStg + ss * Cfg::STG_BYTES + c * G2_BOX_BYTES, tile_n * BN + c * Cfg::COLS_PER_BOX,
-                       tile_t * bt, tile_b * bb);
+          tma_load_3d(sStg + ss * Cfg::STG_BYTES + c * G2_BOX_BYTES, &tmR, &stg_full[ss], col + c * Cfg::COLS_PER_BOX, t0, b0);
+      };
+      if (EPI == EPI_RESID)
+        for (long long e = 0; e < NSTG && e < total_e; ++e) load_resid(e);
+      for (long long e = 0; e < total_e; ++e) {
+        const int ss = (int)(e % NSTG);
+        int col, t0, b0;
+        sub_coords(e, col, t0, b0);
+        mbar_wait(&stg_ready[ss], (uint32_t)((e / NSTG) & 1));
+#pragma unroll
+        for (int c = 0; c < Cfg::BOXES; ++c)
+          tma_store_3d(&tmO, sStg + ss * Cfg::STG_BYTES + c * G2_BOX_BYTES, col + c * Cfg::COLS_PER_BOX, t0, b0);
         tma_store_commit();
         tma_store_wait_read<0>();
-        mbar_arrive(&stg_empty[ss]);
+        if (EPI == EPI_RESID) { if (e + NSTG < total_e) load_resid(e + NSTG); }   // the slot's next tenant
+        else mbar_arrive(&stg_empty[ss]);
       }
       tma_store_wait_all<0>();
     }

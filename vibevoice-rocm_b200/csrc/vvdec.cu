@@ -308,6 +308,11 @@ struct Packer {
     const uint64_t strides[1] = {(uint64_t)w.K * 2};
     const uint32_t box[2] = {(uint32_t)w.BK, (uint32_t)w.BN};
     status = encode_map(&w.tm, w.w, 2, dims, strides, box);
+    if (status == VV_OK && w.BK == 64 && N % 256 == 0) {
+      const uint32_t box256[2] = {64u, 256u};
+      status = encode_map(&w.tm256, w.w, 2, dims, strides, box256);
+      w.has_tm256 = (status == VV_OK);
+    }
   }
   // one Block1D (:915-945) under state-dict prefix p: folded mixer vectors + the two FFN GEMM operands
   bool block(const std::string& p, int C, BlockW& bw);
@@ -568,14 +573,25 @@ int launch_gemm_impl(vv_decoder* d, const __nv_bfloat16* A, long long a_rpb, int
     }
     if (rc != VV_OK) return rc;
     const int num_sms = d->num_sms;
-    const long long ntiles = best_tiles * (w.N / w.BN);
+    // 256-wide MMA tiles when there are enough of them to keep the tail short (>= 3 waves)
+    static int bn256_mode = -1;                            // VV_GEMM_BN256: 0 never, 1 auto (default), 2 whenever N % 256 == 0
+    if (bn256_mode < 0) { const char* ev = getenv("VV_GEMM_BN256"); bn256_mode = ev ? atoi(ev) : 1; }
+    const long long ntiles256 = best_tiles * (w.N / 256);
+    const bool wide = w.has_tm256 && bn256_mode > 0 && (bn256_mode == 2 || ntiles256 >= 3LL * num_sms);
+    const long long ntiles = wide ? ntiles256 : best_tiles * (w.N / w.BN);
     const unsigned grid2 = (unsigned)std::min<long long>(ntiles, num_sms);
     const bool deep = nk >= 32;   // K >= 2048: mainloop-dominated
 #define VV_G2_LAUNCH(E, D)                                                                                  \
     do {                                                                                                      \
-      rc = ensure_smem(gemm_tc2_kernel<E, D>, (int)Gemm2Cfg<E, D>::TOTAL, d->cfg.device);                     \
-      if (rc != VV_OK) return rc;                                                                             \
-      gemm_tc2_kernel<E, D><<<grid2, G2Warps<E>::THREADS, Gemm2Cfg<E, D>::TOTAL, s>>>(tmA, w.tm, tmR, tmO, g);         \
+      if (wide) {                                                                                             \
+        rc = ensure_smem(gemm_tc2_kernel<E, D, 256>, (int)Gemm2Cfg<E, D, 256>::TOTAL, d->cfg.device);         \
+        if (rc != VV_OK) return rc;                                                                           \
+        gemm_tc2_kernel<E, D, 256><<<grid2, G2Warps<E>::THREADS, Gemm2Cfg<E, D, 256>::TOTAL, s>>>(tmA, w.tm256, tmR, tmO, g); \
+      } else {                                                                                                \
+        rc = ensure_smem(gemm_tc2_kernel<E, D, 128>, (int)Gemm2Cfg<E, D, 128>::TOTAL, d->cfg.device);         \
+        if (rc != VV_OK) return rc;                                                                           \
+        gemm_tc2_kernel<E, D, 128><<<grid2, G2Warps<E>::THREADS, Gemm2Cfg<E, D, 128>::TOTAL, s>>>(tmA, w.tm, tmR, tmO, g);  \
+      }                                                                                                       \
     } while (0)
     if (e.epi == EPI_BIAS_F32) { if (deep) VV_G2_LAUNCH(EPI_BIAS_F32, true); else VV_G2_LAUNCH(EPI_BIAS_F32, false); }
     else if (e.epi == EPI_GELU_BF16) { if (deep) VV_G2_LAUNCH(EPI_GELU_BF16, true); else VV_G2_LAUNCH(EPI_GELU_BF16, false); }

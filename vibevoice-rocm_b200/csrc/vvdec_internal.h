@@ -31,6 +31,8 @@ struct DenseW {                 // one packed GEMM weight: bf16 [N, K] K-major +
   int N = 0, K = 0, Ktap = 0, n_taps = 1;
   int BN = 0, BK = 0;
   CUtensorMap tm;
+  bool has_tm256 = false;       // N % 256 == 0 and BK == 64: second map with a [64 x 256] box (gemm_tc2 BN = 256)
+  CUtensorMap tm256;
 };
 
 struct BlockW {
