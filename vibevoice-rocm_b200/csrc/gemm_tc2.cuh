@@ -40,13 +40,16 @@ struct Gemm2Cfg {
   static_assert(BN == 128 || BN == 256, "tile width");
   static constexpr bool OUT_BF16 = (EPI == EPI_GELU_BF16);
   static constexpr int COLS_PER_BOX = OUT_BF16 ? 64 : 32;
-  static constexpr int NSUB = BN / G2_BN;                            // epilogue sub-tiles (128 columns) per MMA tile
-  static constexpr int BOXES = G2_BN / COLS_PER_BOX;                 // per sub-tile: 2 or 4
+  // epilogue sub-tile: 128 columns, or 64 for the fp32 epilogues of the wide tile (32 KB of staging instead of 64 KB
+  // buys a 4th ring stage for long K loops, or a second staging slot for short ones)
+  static constexpr int SUBW = (BN == 256 && !OUT_BF16) ? 64 : 128;
+  static constexpr int NSUB = BN / SUBW;                             // sub-tiles per MMA tile: 1, 2 or 4
+  static constexpr int BOXES = SUBW / COLS_PER_BOX;                  // per sub-tile: 2 or 4
   static constexpr int STG_BYTES = BOXES * G2_BOX_BYTES;             // 32 KB or 64 KB
   static constexpr int B_BYTES = BN * G2_BK * 2;                     // 16 KB or 32 KB
-  static constexpr int NSTG = (BN == 128) ? (DEEP ? 1 : 2) : (OUT_BF16 ? (DEEP ? 1 : 2) : 1);
+  static constexpr int NSTG = (BN == 128) ? (DEEP ? 1 : 2) : (DEEP ? 1 : 2);
   static constexpr int STAGES = (BN == 128) ? (DEEP ? (OUT_BF16 ? 6 : 5) : (OUT_BF16 ? 5 : 3))    // A/B ring depth
-                                            : (OUT_BF16 ? (DEEP ? 4 : 3) : 3);
+                                            : (DEEP ? 4 : 3);
   static constexpr int OFF_RING = 0;
   static constexpr int OFF_STG = STAGES * (G2_A_BYTES + B_BYTES);
   static constexpr int OFF_BAR = OFF_STG + NSTG * STG_BYTES;
@@ -66,7 +69,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   using Cfg = Gemm2Cfg<EPI, DEEP, BN>;
   constexpr int S = Cfg::STAGES;
   constexpr int NSTG = Cfg::NSTG;
-  constexpr int BK = G2_BK, NSUB = Cfg::NSUB, SUBW = G2_BN;
+  constexpr int BK = G2_BK, NSUB = Cfg::NSUB, SUBW = Cfg::SUBW;
   constexpr int G2_B_BYTES = Cfg::B_BYTES;
   constexpr int EW = G2Warps<EPI>::EPI_WARPS;
   constexpr int CPW = SUBW / (EW / 4);      // columns per epilogue warp inside a sub-tile: 64 or 32
