@@ -573,11 +573,13 @@ int launch_gemm_impl(vv_decoder* d, const __nv_bfloat16* A, long long a_rpb, int
     }
     if (rc != VV_OK) return rc;
     const int num_sms = d->num_sms;
-    // 256-wide MMA tiles when there are enough of them to keep the tail short (>= 3 waves)
+    // 256-wide MMA tiles when there are enough of them to keep the tail short (>= 2 waves)
     static int bn256_mode = -1;                            // VV_GEMM_BN256: 0 never, 1 auto (default), 2 whenever N % 256 == 0
     if (bn256_mode < 0) { const char* ev = getenv("VV_GEMM_BN256"); bn256_mode = ev ? atoi(ev) : 1; }
     const long long ntiles256 = best_tiles * (w.N / 256);
-    const bool wide = w.has_tm256 && bn256_mode > 0 && (bn256_mode == 2 || ntiles256 >= 3LL * num_sms);
+    static int bn256_waves = -1;                           // VV_GEMM_BN256_WAVES: minimum waves of wide tiles (default 2: measured on the C = 2048 FFN)
+    if (bn256_waves < 0) { const char* ev = getenv("VV_GEMM_BN256_WAVES"); bn256_waves = ev ? atoi(ev) : 2; }
+    const bool wide = w.has_tm256 && bn256_mode > 0 && (bn256_mode == 2 || ntiles256 >= (long long)bn256_waves * num_sms);
     const long long ntiles = wide ? ntiles256 : best_tiles * (w.N / w.BN);
     const unsigned grid2 = (unsigned)std::min<long long>(ntiles, num_sms);
     const bool deep = nk >= 32;   // K >= 2048: mainloop-dominated
