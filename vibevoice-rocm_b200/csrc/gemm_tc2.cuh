@@ -42,14 +42,17 @@ struct Gemm2Cfg {
   static constexpr int COLS_PER_BOX = OUT_BF16 ? 64 : 32;
   // epilogue sub-tile: 128 columns, or 64 for the fp32 epilogues of the wide tile (32 KB of staging instead of 64 KB
   // buys a 4th ring stage for long K loops, or a second staging slot for short ones)
-  static constexpr int SUBW = (BN == 256 && !OUT_BF16) ? 64 : 128;
+#ifndef VV_G2_SUBW128_NARROW
+#define VV_G2_SUBW128_NARROW 0     // 1: 128-column fp32 sub-tiles on the 128-wide tile (the earlier layout; A/B: the
+#endif                             //    64 -> 128-channel upsampler runs 4.2 ms with it, 3.15 ms without)
+  static constexpr int SUBW = (!OUT_BF16 && (BN == 256 || !VV_G2_SUBW128_NARROW)) ? 64 : 128;
   static constexpr int NSUB = BN / SUBW;                             // sub-tiles per MMA tile: 1, 2 or 4
   static constexpr int BOXES = SUBW / COLS_PER_BOX;                  // per sub-tile: 2 or 4
   static constexpr int STG_BYTES = BOXES * G2_BOX_BYTES;             // 32 KB or 64 KB
   static constexpr int B_BYTES = BN * G2_BK * 2;                     // 16 KB or 32 KB
   static constexpr int NSTG = (BN == 128) ? (DEEP ? 1 : 2) : (DEEP ? 1 : 2);
-  static constexpr int STAGES = (BN == 128) ? (DEEP ? (OUT_BF16 ? 6 : 5) : (OUT_BF16 ? 5 : 3))    // A/B ring depth
-                                            : (DEEP ? 4 : 3);
+  static constexpr int STAGES = (BN == 128) ? (SUBW == 64 ? (DEEP ? 6 : 5) : (DEEP ? (OUT_BF16 ? 6 : 5) : (OUT_BF16 ? 5 : 3)))
+                                            : (DEEP ? 4 : 3);                                        // A/B ring depth
   static constexpr int OFF_RING = 0;
   static constexpr int OFF_STG = STAGES * (G2_A_BYTES + B_BYTES);
   static constexpr int OFF_BAR = OFF_STG + NSTG * STG_BYTES;
