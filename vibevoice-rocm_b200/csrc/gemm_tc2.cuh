@@ -1,5 +1,6 @@
-// gemm_tc2.cuh — persistent version of the tap GEMM (gemm_tc.cuh) for the 128 x 128 x 64 tile, i.e. every
-// hot dense layer with C >= 128: FFN linear1/linear2, the polyphase transposed convs, the stem.
+// gemm_tc2.cuh — persistent version of the tap GEMM (gemm_tc.cuh) for 128 x {128, 256} x 64 tiles, i.e. every hot
+// dense layer with N % 128 == 0: FFN linear1/linear2 at C >= 256, the polyphase transposed convs, the decoder stem, the
+// encoder's strided convs.
 //
 // What changed against gemm_tc_kernel, and why (ncu on the first round-1 build, profiles/):
 //   * row-per-thread global loads/stores in the epilogue cost one L1TEX tag cycle per ROW per instruction;
@@ -11,8 +12,9 @@
 //   * 8 epilogue warps (two per TMEM lane quarter, splitting the columns) instead of 4.
 //   * BN = 256 instantiation (N % 256 == 0 and enough tiles): one 128 x 256 accumulator per MMA tile halves the
 //     shared-memory operand traffic per flop (A 16 KB + B 32 KB per 512 MMA clocks = 96 B/clk against 128 B/clk at
-//     BN = 128, which sits exactly on the TMA/smem feed limit); the epilogue walks it as two 128-column sub-tiles
-//     through the same staging slots.
+//     BN = 128, which sits exactly on the TMA/smem feed limit); the epilogue walks it in 128-column (bf16 out) or
+//     64-column (fp32 out) sub-tiles through the same staging slots, which leaves room for a 4-stage A/B ring.
+//     K2 step: 236 -> 216 ms; FFN GEMMs 650-930 -> 800-1235 TFLOP/s.
 // Roles: warp 0 TMA loads (A/B ring), warp 1 MMA issue + TMEM owner, warps 2..9 (2..17 for GELU) epilogue, last warp =
 // staging manager: TMA-stores finished sub-tiles and TMA-loads the residual of the sub-tile that takes the slot next.
 #pragma once
