@@ -242,6 +242,66 @@ def streaming_leg(dec, geom, dev, n_streams=256, steps=300, warmup=30):
     return out
 
 
+def torch_eager_leg(sd, geom, dev, dec, B=8, T=450, steps=3):
+    """Context number, not an arm: the same decode written with stock PyTorch ops (cuDNN depthwise / transposed conv,
+    cuBLAS linear, F.gelu — the calls the reference module makes, modular_vibevoice_tokenizer.py:914-951) in bf16 eager on
+    the same GPU and weights, on a bounded sample.  Lives in bench.py only; the product path never uses it."""
+    import torch
+    import torch.nn.functional as F
+    w = {k: v.to(dev, torch.bfloat16) for k, v in sd.items()}
+    n = len(geom.depths)
+
+    def rms(x, wt):                                   # ConvRMSNorm :77-91 (fp32 statistics, cast, then * weight)
+        xt = x.transpose(1, 2)
+        xf = xt.float()
+        xn = (xf * torch.rsqrt(xf.pow(2).mean(-1, keepdim=True) + geom.eps)).to(x.dtype) * wt
+        return xn.transpose(1, 2)
+
+    def decode(lat):                                  # [B, T, D] -> [B, 1, T*hop]
+        x = lat.transpose(1, 2)
+        x = F.conv1d(F.pad(x, (6, 0)), w["decoder.upsample_layers.0.0.conv.conv.weight"], w["decoder.upsample_layers.0.0.conv.conv.bias"])
+        for i in range(n):
+            if i > 0:
+                r = geom.ratios[i - 1]
+                p = f"decoder.upsample_layers.{i}.0.convtr.convtr."
+                y = F.conv_transpose1d(x, w[p + "weight"], w[p + "bias"], stride=r)
+                x = y[..., :y.shape[-1] - r]          # causal trim of k - r samples on the right (:563-571)
+            C = x.shape[1]
+            for j in range(geom.depths[i]):
+                p = f"decoder.stages.{i}.{j}."
+                h = rms(x, w[p + "norm.weight"])
+                h = F.conv1d(F.pad(h, (6, 0)), w[p + "mixer.conv.conv.conv.weight"], w[p + "mixer.conv.conv.conv.bias"], groups=C)
+                x = x + h * w[p + "gamma"][None, :, None]
+                h = rms(x, w[p + "ffn_norm.weight"]).transpose(1, 2)
+                h = F.linear(F.gelu(F.linear(h, w[p + "ffn.linear1.weight"], w[p + "ffn.linear1.bias"])),
+                             w[p + "ffn.linear2.weight"], w[p + "ffn.linear2.bias"]).transpose(1, 2)
+                x = x + h * w[p + "ffn_gamma"][None, :, None]
+        return F.conv1d(F.pad(x, (6, 0)), w["decoder.head.conv.conv.weight"], w["decoder.head.conv.conv.bias"])
+
+    gen = torch.Generator().manual_seed(9)
+    lat = torch.randn(B, T, geom.vae_dim, generator=gen).to(torch.bfloat16).to(dev)
+    with torch.no_grad():
+        y = decode(lat[:1, :8])                       # agreement check on a small piece (both bf16 paths vs each other)
+        ours = dec.decode(lat[:1, :8])
+        err = (y.float() - ours.float())
+        snr = float(10 * torch.log10(ours.float().pow(2).sum() / err.pow(2).sum().clamp_min(1e-30)))
+        del y, ours, err
+        decode(lat)                                   # warm-up (cuDNN heuristics, allocator)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            decode(lat)
+        e1.record()
+        torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / steps
+    del w
+    torch.cuda.empty_cache()
+    return {"what": "stock PyTorch ops (cuDNN/cuBLAS), bf16 eager, same GPU and weights; context only",
+            "sample": f"batch {B} x {T} frames", "ms_per_step": ms, "value": B * T / FRAME_RATE / (ms / 1e3), "unit": UNIT,
+            "snr_vs_b200_path_db": snr, "torch": torch.__version__}
+
+
 def longform_leg(dec, geom, dev, world, rank, dist, steps, frames=40_500):
     """BASELINE.json configs[2]: one 90-minute utterance (40,500 latent frames) split into time chunks across the ranks,
     each rank recomputing its causal halo (58 frames); no collective on the data path, one NCCL gather of the finished
@@ -440,6 +500,7 @@ def main():
     ap.add_argument("--no-streaming", action="store_true")
     ap.add_argument("--no-encoder", action="store_true")
     ap.add_argument("--no-longform", action="store_true")
+    ap.add_argument("--no-torch-eager", action="store_true")
     ap.add_argument("--encoder-kernels-out", default="", help="per-kernel table of the encoder leg (JSON)")
     ap.add_argument("--kernels-out", default="", help="write the per-kernel timing table (JSON) here")
     args = ap.parse_args()
@@ -597,6 +658,17 @@ def main():
         except Exception as e:                                  # report, do not hide
             encoder = {"error": f"{type(e).__name__}: {e}"[:300]}
 
+    # ---- stock-PyTorch eager decode on the same GPU (context for the CPU baseline; bounded sample) ----------------
+    eager = None
+    if not args.no_torch_eager:
+        try:
+            dec._ws = None
+            torch.cuda.empty_cache()
+            eager = torch_eager_leg(sd, geom, dev, dec)
+        except Exception as e:                                  # report, do not hide
+            eager = {"error": f"{type(e).__name__}: {e}"[:300]}
+            torch.cuda.empty_cache()
+
     # ---- CPU baseline (reported, not the target): bounded sample on the host cores -----------------
     cpu = None
     if not args.no_cpu_baseline:
@@ -615,6 +687,7 @@ def main():
                    "sharding": "utterances per rank, no data-path collective"},
         "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roof, "cpu_baseline": cpu,
         "streaming": streaming, "encoder": encoder, "longform": longform,
+        "torch_eager_gpu": eager,
     }
     print(json.dumps(line), flush=True)
     if world > 1:
