@@ -193,6 +193,19 @@ int64_t vv_encoder_take_launch_count(vv_encoder* enc);
 int32_t vv_encoder_set_profiling(vv_encoder* enc, int32_t enabled);
 int32_t vv_encoder_read_profile(vv_encoder* enc, vv_profile_record* out, int32_t cap);
 
+/* Encoder per-kernel hooks (offline form; tests):
+ *  stem SConv1d(1 -> 32, k7) (:732-734): audio [B, L] -> x fp32 [B, L, 32];
+ *  strided SConv1d(C/2 -> C, k = 2r, stride r) INTO encoder stage `stage` (1..n_stages-1) (:737-743): xb is the padded bf16
+ *    operand copy [B, (ceil(rows / r) + 1) * r, C/2] whose rows [r, r + rows) hold the input (the call zeroes the r
+ *    context rows and the ragged tail); y fp32 [B, ceil(rows / r), C];
+ *  head SConv1d(C_last -> vae_dim, k7) (:771): xb bf16 [B, rows + 6, C_last], rows [6, 6 + rows) = input; mean fp32
+ *    [B, rows, vae_dim]. */
+int32_t vv_kernel_enc_stem(vv_encoder* enc, const void* audio, int32_t audio_dtype, float* x, int32_t B, int64_t L,
+                           void* cuda_stream);
+int32_t vv_kernel_downsample(vv_encoder* enc, int32_t stage, void* xb, float* y, int32_t B, int32_t rows,
+                             void* cuda_stream);
+int32_t vv_kernel_enc_head(vv_encoder* enc, void* xb, float* mean, int32_t B, int32_t rows, void* cuda_stream);
+
 /* ---- per-kernel entry points (offline form; tests and bench.py's roofline leg time these alone) -- */
 /* Fused Block1D mixer half on a channels-last fp32 activation x [B, rows, C]:
  *   y = x + gamma * (dwconv7(RMSNorm(x) * norm_w) + bias);   a = bf16( RMSNorm(y) * ffn_norm_w )

@@ -338,3 +338,65 @@ extern "C" int32_t vv_encode(vv_encoder* e, const void* audio, int32_t audio_dty
   prof_collect(d, s);
   return rc;
 }
+
+// ---- per-kernel entry points of the encoder path (offline form; tests time / check these alone) ----------------------
+extern "C" int32_t vv_kernel_enc_stem(vv_encoder* e, const void* audio, int32_t audio_dtype, float* x, int32_t B,
+                                      int64_t L, void* cuda_stream) {
+  if (!e || !e->core.finalized) { set_error("encoder not finalized"); return VV_ERR_NOT_FINALIZED; }
+  if (!audio || !x || B < 1 || L < 1 || L >= (1LL << 31)) { set_error("bad argument"); return VV_ERR_INVALID_ARG; }
+  if (audio_dtype != VV_F32 && audio_dtype != VV_BF16) { set_error("audio dtype must be f32 or bf16"); return VV_ERR_BAD_DTYPE; }
+  VV_CUDA(cudaSetDevice(e->core.cfg.device));
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(cuda_stream);
+  EncStemArgs p;
+  p.audio = audio; p.audio_is_bf16 = audio_dtype == VV_BF16; p.audio_bstride = L;
+  p.w = e->stem_w; p.b = e->stem_b; p.x = x; p.nbatch = B; p.L = (int)L;
+  p.st = make_state_ref(nullptr, nullptr, 0);
+  const long long threads = (L + ENC_STEM_ROWS - 1) / ENC_STEM_ROWS * B * 8;
+  enc_stem_kernel<<<(unsigned)std::min<long long>((threads + 255) / 256, 148LL * 64), 256, 0, s>>>(p);
+  e->core.launches++;
+  VV_CUDA(cudaGetLastError());
+  return VV_OK;
+}
+
+extern "C" int32_t vv_kernel_downsample(vv_encoder* e, int32_t stage, void* xb, float* y, int32_t B, int32_t rows,
+                                        void* cuda_stream) {
+  if (!e || !e->core.finalized) { set_error("encoder not finalized"); return VV_ERR_NOT_FINALIZED; }
+  vv_decoder* d = &e->core;
+  if (stage < 1 || stage >= (int)d->stages.size()) { set_error("stage %d has no strided conv", stage); return VV_ERR_INVALID_ARG; }
+  if (!xb || !y || B < 1 || rows < 1) { set_error("bad argument"); return VV_ERR_INVALID_ARG; }
+  VV_CUDA(cudaSetDevice(d->cfg.device));
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(cuda_stream);
+  const StageW& sw = d->stages[stage];
+  const int r = sw.ratio, Cin = sw.C / 2;
+  const int rows_out = (rows + r - 1) / r;
+  EncContextArgs cp;                                   // zero the r context rows and the ragged tail
+  cp.xb = reinterpret_cast<__nv_bfloat16*>(xb); cp.nbatch = B; cp.rows = rows; cp.off = r; cp.C = Cin;
+  cp.rpb = (long long)(rows_out + 1) * r;
+  cp.st = make_state_ref(nullptr, nullptr, 0);
+  const long long cells = (cp.rpb - rows) * B * (Cin / 8);
+  enc_context_kernel<<<(unsigned)std::max<long long>(1, std::min<long long>((cells + 255) / 256, 148LL * 16)), 256, 0, s>>>(cp);
+  d->launches++;
+  VV_CUDA(cudaGetLastError());
+  EpiOut eo;
+  eo.epi = EPI_BIAS_F32; eo.out_f32 = y;
+  return launch_gemm(d, reinterpret_cast<const __nv_bfloat16*>(xb), rows_out + 1, rows_out, B, sw.up, eo, s);
+}
+
+extern "C" int32_t vv_kernel_enc_head(vv_encoder* e, void* xb, float* mean, int32_t B, int32_t rows, void* cuda_stream) {
+  if (!e || !e->core.finalized) { set_error("encoder not finalized"); return VV_ERR_NOT_FINALIZED; }
+  vv_decoder* d = &e->core;
+  if (!xb || !mean || B < 1 || rows < 1) { set_error("bad argument"); return VV_ERR_INVALID_ARG; }
+  VV_CUDA(cudaSetDevice(d->cfg.device));
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(cuda_stream);
+  const int C = d->stages.back().C;
+  EncContextArgs cp;                                   // zero the 6 context rows
+  cp.xb = reinterpret_cast<__nv_bfloat16*>(xb); cp.nbatch = B; cp.rows = rows; cp.off = 6; cp.C = C; cp.rpb = rows + 6;
+  cp.st = make_state_ref(nullptr, nullptr, 0);
+  const long long cells = 6LL * B * (C / 8);
+  enc_context_kernel<<<(unsigned)std::max<long long>(1, std::min<long long>((cells + 255) / 256, 148LL * 16)), 256, 0, s>>>(cp);
+  d->launches++;
+  VV_CUDA(cudaGetLastError());
+  EpiOut eo;
+  eo.epi = EPI_BIAS_F32; eo.out_f32 = mean;
+  return launch_gemm(d, reinterpret_cast<const __nv_bfloat16*>(xb), rows + 6, rows, B, e->head, eo, s);
+}

@@ -81,6 +81,9 @@ SIGNATURES = {
     "vv_encoder_workspace_bytes": (_I64, [_P, _I32, _I64]),
     "vv_encoder_state_create": (_I32, [_P, _I32, C.POINTER(_P)]),
     "vv_encode": (_I32, [_P, _P, _I32, _I32, _I64, _P, _P, _I64, _P, _P, _P]),
+    "vv_kernel_enc_stem": (_I32, [_P, _P, _I32, _P, _I32, _I64, _P]),
+    "vv_kernel_downsample": (_I32, [_P, _I32, _P, _P, _I32, _I32, _P]),
+    "vv_kernel_enc_head": (_I32, [_P, _P, _P, _I32, _I32, _P]),
     "vv_encoder_take_launch_count": (_I64, [_P]),
     "vv_encoder_set_profiling": (_I32, [_P, _I32]),
     "vv_encoder_read_profile": (_I32, [_P, _P, _I32]),
