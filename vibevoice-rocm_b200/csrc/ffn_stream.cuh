@@ -39,6 +39,11 @@ __device__ long long vv_fs_trace[32 * 16];
 #define VV_TR(slot, g) do { } while (0)
 #endif
 
+#ifndef VV_FS_GROUPS
+#define VV_FS_GROUPS 2      // E1 groups taking chunks round-robin: 2 (8 warps each, 32 columns per warp) or 4 (4 warps
+#endif                      // each, the whole 64-column chunk per warp).  Measured at C = 128, 5760 frames: 1.45 ms with 2,
+                            // 1.70 ms with 4 — a warp's own 64-column walk costs more than the extra overlap returns
+constexpr int FS_GROUPS = VV_FS_GROUPS;
 constexpr int FS_E1_WARPS = 16;
 constexpr int FS_E2_WARPS = 4;
 constexpr int FS_THREADS = (4 + FS_E1_WARPS + FS_E2_WARPS) * 32;
@@ -63,11 +68,12 @@ struct FfnStreamCfg {
   static constexpr int OFF_H = OFF_W2 + S2 * W2_BYTES;
   static constexpr int OFF_Y = OFF_H;              // H lives in tensor memory (no shared-memory copy)
   static constexpr int OFF_BAR = OFF_Y + NY * Y_BYTES;
-  static constexpr int NBARS = 2 * NA + 2 * S1 + 2 * S2 + 2 * ND1 + 8 + 2 * NY;
+  static constexpr int NBARS = 2 * NA + 2 * S1 + 2 * S2 + ND1 + 3 * FS_GROUPS + 4 + 2 * NY;
   static constexpr int TOTAL = OFF_BAR + 512 + 1024;   // + alignment slack
   static_assert(NBARS * 8 + 8 <= 512, "barrier block");
   static_assert(TOTAL <= 232448, "exceeds the 227 KB dynamic shared memory limit");
-  static constexpr uint32_t TMEM_COLS = 512;       // D1: 2 x 64 at column 0; H: 2 x 32 at 128; D2: 2 x C at 256
+  static constexpr uint32_t TMEM_COLS = 512;       // D1: 2 x 64 at column 0; H: FS_GROUPS x 32 at 128; D2: 2 x C at 256
+  static_assert(FS_GROUPS == 2 || FS_GROUPS == 4, "E1 groups");
   static constexpr uint32_t H_COL0 = 128;          // H chunk as packed bf16 pairs: 64 hidden units = 32 columns
   static constexpr uint32_t D2_COL0 = 256;
 };
@@ -93,11 +99,13 @@ ffn_stream_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   uint64_t* w1_empty = w1_full + S1;       // [S1]
   uint64_t* w2_full = w1_empty + S1;       // [S2]
   uint64_t* w2_empty = w2_full + S2;       // [S2]
-  uint64_t* d1_full = w2_empty + S2;       // [ND1]
-  uint64_t* d1_empty = d1_full + ND1;      // [ND1]
-  uint64_t* h_full = d1_empty + ND1;       // [2]
-  uint64_t* h_empty = h_full + 2;          // [2]
-  uint64_t* d2_full = h_empty + 2;         // [2]
+  // d1_full is per E1 GROUP, not per accumulator: a waiter must see the phases of its barrier in order, and with more
+  // groups than accumulators a group would otherwise first wait on a later phase of a buffer it never used (parity alias)
+  uint64_t* d1_full = w2_empty + S2;       // [FS_GROUPS]
+  uint64_t* d1_empty = d1_full + FS_GROUPS; // [ND1]
+  uint64_t* h_full = d1_empty + ND1;       // [FS_GROUPS]
+  uint64_t* h_empty = h_full + FS_GROUPS;  // [FS_GROUPS]
+  uint64_t* d2_full = h_empty + FS_GROUPS; // [2]
   uint64_t* d2_empty = d2_full + 2;        // [2]
   uint64_t* y_full = d2_empty + 2;         // [NY] residual box landed
   uint64_t* y_ready = y_full + NY;         // [NY] E2 finished the box: ready to store
@@ -124,10 +132,13 @@ ffn_stream_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     for (int i = 0; i < NA; ++i) { mbar_init(&a_full[i], 1); mbar_init(&a_empty[i], 1); }
     for (int i = 0; i < S1; ++i) { mbar_init(&w1_full[i], 1); mbar_init(&w1_empty[i], 1); }
     for (int i = 0; i < S2; ++i) { mbar_init(&w2_full[i], 1); mbar_init(&w2_empty[i], 1); }
-    for (int i = 0; i < ND1; ++i) { mbar_init(&d1_full[i], 1); mbar_init(&d1_empty[i], FS_E1_WARPS / 2); }
-    for (int i = 0; i < 2; ++i) {
-      mbar_init(&h_full[i], FS_E1_WARPS / 2);
+    for (int i = 0; i < ND1; ++i) mbar_init(&d1_empty[i], FS_E1_WARPS / FS_GROUPS);
+    for (int i = 0; i < FS_GROUPS; ++i) {
+      mbar_init(&d1_full[i], 1);
+      mbar_init(&h_full[i], FS_E1_WARPS / FS_GROUPS);
       mbar_init(&h_empty[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
       mbar_init(&d2_full[i], 1);
       mbar_init(&d2_empty[i], FS_E2_WARPS);
     }
@@ -203,7 +214,7 @@ ffn_stream_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
               umma_bf16(d, da + (uint64_t)(((kb * 128 * 128) >> 4) + kk * 2),
                         dw + (uint64_t)(((kb * L::HC * 128) >> 4) + kk * 2), idesc1, (kb | kk) != 0);
           }
-          umma_commit(&d1_full[db]);
+          umma_commit(&d1_full[g & (FS_GROUPS - 1)]);
           umma_commit(&w1_empty[s1]);
           VV_TR(2, g);
         }
@@ -221,8 +232,8 @@ ffn_stream_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         mbar_wait(&d2_empty[d2b], (uint32_t)(((it >> 1) & 1) ^ 1));
         const uint32_t d = tmem_base + L::D2_COL0 + (uint32_t)(d2b * C);
         for (int j = 0; j < NCH; ++j, ++g) {
-          const int hb = g & 1, s2 = g & (S2 - 1);
-          mbar_wait2(&w2_full[s2], (uint32_t)((g / S2) & 1), &h_full[hb], (uint32_t)((g >> 1) & 1));
+          const int hb = g & (FS_GROUPS - 1), s2 = g & (S2 - 1);
+          mbar_wait2(&w2_full[s2], (uint32_t)((g / S2) & 1), &h_full[hb], (uint32_t)((g / FS_GROUPS) & 1));
           VV_TR(4, g);
           tc_fence_after();
           const uint32_t ah = tmem_base + L::H_COL0 + (uint32_t)(hb * 32);   // A operand from tensor memory
@@ -262,44 +273,54 @@ ffn_stream_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     // Two groups of 8 warps alternate chunks (group G owns H buffer G), so one group's TMEM-load / MUFU /
     // barrier latency overlaps the other's math; within a chunk a warp owns 32 rows x 32 columns.
     const int q = warp & 3;                   // TMEM lane quarter
-    const int grp = (warp - 4) >> 3;          // chunk parity this warp serves
-    const int ch = ((warp - 4) >> 2) & 1;     // 32-column half of the 64-column chunk
-    const uint32_t haddr = tmem_base + ((uint32_t)(q * 32) << 16) + L::H_COL0 + (uint32_t)(grp * 32 + ch * 16);
-    const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(ch * 32);
-    for (int g = grp; g < total_g; g += 2) {
+    constexpr int WPG = FS_E1_WARPS / FS_GROUPS;          // warps per group: 8 (two column halves) or 4
+    constexpr int NHF = 8 / WPG;                          // 32-column halves a warp walks per chunk: 1 or 2
+    const int grp = (warp - 4) / WPG;                     // chunks g = grp (mod FS_GROUPS)
+    const int ch0 = (WPG == 8) ? (((warp - 4) >> 2) & 1) : 0;
+    const uint32_t haddr = tmem_base + ((uint32_t)(q * 32) << 16) + L::H_COL0 + (uint32_t)(grp * 32);
+    const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16);
+    for (int g = grp; g < total_g; g += FS_GROUPS) {
       const int j = g & (NCH - 1), db = g & (ND1 - 1);
-      const float* bp = p.b1 + j * L::HC + ch * 32;
-      if (q == 0 && ch == 0 && lane == 0) VV_TR(6, g);
-      mbar_wait(&d1_full[db], (uint32_t)((g / ND1) & 1));
-      if (q == 0 && ch == 0 && lane == 0) VV_TR(7, g);
+      if (q == 0 && ch0 == 0 && lane == 0) VV_TR(6, g);
+      mbar_wait(&d1_full[grp], (uint32_t)((g / FS_GROUPS) & 1));
+      if (q == 0 && ch0 == 0 && lane == 0) VV_TR(7, g);
       tc_fence_after();
-      uint32_t v[32];
-      tmem_ld_32x32(taddr + (uint32_t)(db * L::HC), v);
-      tmem_ld_wait();
-      if (q == 0 && ch == 0 && lane == 0) VV_TR(8, g);
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&d1_empty[db]);   // accumulator is in registers: a later G1 may overwrite it
-      uint32_t hv[16];
 #pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        const float4 b0 = __ldg(reinterpret_cast<const float4*>(bp + i * 8));
-        const float4 b1v = __ldg(reinterpret_cast<const float4*>(bp + i * 8 + 4));
-        hv[i * 4 + 0] = gelu2_bias_pack(__uint_as_float(v[i * 8 + 0]), __uint_as_float(v[i * 8 + 1]), b0.x, b0.y);
-        hv[i * 4 + 1] = gelu2_bias_pack(__uint_as_float(v[i * 8 + 2]), __uint_as_float(v[i * 8 + 3]), b0.z, b0.w);
-        hv[i * 4 + 2] = gelu2_bias_pack(__uint_as_float(v[i * 8 + 4]), __uint_as_float(v[i * 8 + 5]), b1v.x, b1v.y);
-        hv[i * 4 + 3] = gelu2_bias_pack(__uint_as_float(v[i * 8 + 6]), __uint_as_float(v[i * 8 + 7]), b1v.z, b1v.w);
+      for (int hf = 0; hf < NHF; ++hf) {
+        const int ch = ch0 + hf;                          // 32-column half of the 64-column chunk
+        const float* bp = p.b1 + j * L::HC + ch * 32;
+        uint32_t v[32];
+        tmem_ld_32x32(taddr + (uint32_t)(db * L::HC + ch * 32), v);
+        tmem_ld_wait();
+        if (hf == NHF - 1) {
+          if (q == 0 && ch0 == 0 && lane == 0) VV_TR(8, g);
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&d1_empty[db]);      // accumulator is in registers: a later G1 may overwrite it
+        }
+        uint32_t hv[16];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const float4 b0 = __ldg(reinterpret_cast<const float4*>(bp + i * 8));
+          const float4 b1v = __ldg(reinterpret_cast<const float4*>(bp + i * 8 + 4));
+          hv[i * 4 + 0] = gelu2_bias_pack(__uint_as_float(v[i * 8 + 0]), __uint_as_float(v[i * 8 + 1]), b0.x, b0.y);
+          hv[i * 4 + 1] = gelu2_bias_pack(__uint_as_float(v[i * 8 + 2]), __uint_as_float(v[i * 8 + 3]), b0.z, b0.w);
+          hv[i * 4 + 2] = gelu2_bias_pack(__uint_as_float(v[i * 8 + 4]), __uint_as_float(v[i * 8 + 5]), b1v.x, b1v.y);
+          hv[i * 4 + 3] = gelu2_bias_pack(__uint_as_float(v[i * 8 + 6]), __uint_as_float(v[i * 8 + 7]), b1v.z, b1v.w);
+        }
+        if (hf == 0) {
+          if (q == 0 && ch0 == 0 && lane == 0) VV_TR(9, g);
+          mbar_wait(&h_empty[grp], (uint32_t)(((g / FS_GROUPS) & 1) ^ 1));
+          if (q == 0 && ch0 == 0 && lane == 0) VV_TR(10, g);
+          tc_fence_after();
+        }
+        tmem_st_32x16(haddr + (uint32_t)(ch * 16), hv);   // thread = row: packed pairs (k, k+1) -> one 32-bit column
       }
-      if (q == 0 && ch == 0 && lane == 0) VV_TR(9, g);
-      mbar_wait(&h_empty[grp], (uint32_t)(((g >> 1) & 1) ^ 1));
-      if (q == 0 && ch == 0 && lane == 0) VV_TR(10, g);
-      tc_fence_after();
-      tmem_st_32x16(haddr, hv);                   // thread = row: packed pairs (k, k+1) -> one 32-bit column
       tmem_st_wait();
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&h_full[grp]);
-      if (q == 0 && ch == 0 && lane == 0) VV_TR(11, g);
+      if (q == 0 && ch0 == 0 && lane == 0) VV_TR(11, g);
     }
   } else {
     // ===== E2: D2 -> + b2, * gamma, + residual (TMA-staged box, swizzled) -> in place -> TMA store ===========
