@@ -153,3 +153,39 @@ def test_two_rank_time_chunk_sharding_under_gloo(tmp_path):
     outs = [p.communicate(timeout=600)[0] for p in procs]
     assert all(p.returncode == 0 for p in procs), outs
     assert "SHARD_OK" in outs[0]
+
+
+def test_encoder_output_distribution_semantics():
+    """B200TokenizerEncoderOutput mirrors VibeVoiceTokenizerEncoderOutput (:954-1000): 'fix' adds std * N(0,1), 'gaussian'
+    draws one std per batch item from N(0, (std/0.8)^2), anything else returns the mean; kl = mean^2; mode = mean."""
+    import torch
+    from vvdec.encoder import B200TokenizerEncoderOutput
+    mean = torch.arange(24, dtype=torch.float32).reshape(2, 3, 4)
+    out = B200TokenizerEncoderOutput(mean=mean, std=0.5)
+    torch.manual_seed(3)
+    x, std = out.sample("fix")
+    torch.manual_seed(3)
+    assert std == 0.5 and torch.equal(x, mean + 0.5 * torch.randn_like(mean))
+    torch.manual_seed(4)
+    x, std = out.sample("gaussian")
+    torch.manual_seed(4)
+    s = torch.randn(2) * (0.5 / 0.8)
+    assert std.shape == (2, 1, 1) and torch.equal(std.flatten(), s)
+    assert torch.equal(x, mean + s[:, None, None] * torch.randn_like(mean))
+    x, std = out.sample("none")
+    assert x is mean and std == 0.5
+    assert out.mode() is mean and torch.equal(out.kl(), mean * mean)
+    try:                                                    # same draws as the reference class, when it is importable here
+        from oracle.ref_shim import import_reference, reference_available
+        if reference_available():
+            import_reference()
+            from vibevoice.modular.modular_vibevoice_tokenizer import VibeVoiceTokenizerEncoderOutput as Ref
+            ref = Ref(mean=mean, std=0.5)
+            for kind in ("fix", "gaussian"):
+                torch.manual_seed(11)
+                a = out.sample(kind)[0]
+                torch.manual_seed(11)
+                assert torch.equal(a, ref.sample(kind)[0])
+            assert torch.equal(out.kl(), ref.kl())
+    except ImportError:
+        pass

@@ -254,3 +254,18 @@ class B200AcousticEncoder:
                 self._h = None
         except Exception:
             pass
+
+
+def patch_encoder(tokenizer, **kw) -> B200AcousticEncoder:
+    """Swap ``encode`` of a reference tokenizer that has an ``.encoder`` (VibeVoiceAcousticTokenizerModel or
+    VibeVoiceSemanticTokenizerModel, e.g. ``model.model.semantic_tokenizer``) for the B200 path, in place; the
+    streaming calls of ``generate()`` (modeling_vibevoice_inference.py:656-662) then run unmodified as long as they feed
+    whole hops.  Returns the encoder object (also kept as ``tokenizer._b200_encoder``)."""
+    if not hasattr(tokenizer, "encoder"):
+        raise ValueError("the given tokenizer has no .encoder")
+    dev = next(tokenizer.parameters()).device
+    enc = B200AcousticEncoder.from_reference(tokenizer, device=dev if dev.type == "cuda" else None, **kw)
+    tokenizer._b200_encoder = enc
+    tokenizer.encode = enc.encode
+    return enc
+
