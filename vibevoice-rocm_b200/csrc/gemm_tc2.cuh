@@ -1,5 +1,5 @@
-// gemm_tc2.cuh — persistent version of the tap GEMM (gemm_tc.cuh) for 128 x {128, 256} x 64 tiles, i.e. every hot
-// dense layer with N % 128 == 0: FFN linear1/linear2 at C >= 256, the polyphase transposed convs, the decoder stem, the
+// gemm_tc2.cuh — persistent version of the tap GEMM (gemm_tc.cuh) for 128 x {64, 128, 256} x 64 tiles, i.e. every hot
+// dense layer with N % 64 == 0: FFN linear1/linear2 at C >= 256, the polyphase transposed convs, the decoder stem, the
 // encoder's strided convs.
 //
 // What changed against gemm_tc_kernel, and why (ncu on the first round-1 build, profiles/):
@@ -39,21 +39,25 @@ constexpr int G2_BOX_BYTES = 128 * 128;           // one staged box: 128 rows x 
 // and the epilogue staging is single-buffered; otherwise the epilogue dominates and staging is double-buffered.
 template <int EPI, bool DEEP, int BN>
 struct Gemm2Cfg {
-  static_assert(BN == 128 || BN == 256, "tile width");
+  static_assert(BN == 64 || BN == 128 || BN == 256, "tile width");
   static constexpr bool OUT_BF16 = (EPI == EPI_GELU_BF16);
+  static_assert(BN != 64 || !OUT_BF16, "the 64-wide tile has fp32 epilogues only");
   static constexpr int COLS_PER_BOX = OUT_BF16 ? 64 : 32;
   // epilogue sub-tile: 128 columns, or 64 for the fp32 epilogues of the wide tile (32 KB of staging instead of 64 KB
   // buys a 4th ring stage for long K loops, or a second staging slot for short ones)
 #ifndef VV_G2_SUBW128_NARROW
 #define VV_G2_SUBW128_NARROW 0     // 1: 128-column fp32 sub-tiles on the 128-wide tile (the earlier layout; A/B: the
 #endif                             //    64 -> 128-channel upsampler runs 4.2 ms with it, 3.15 ms without)
-  static constexpr int SUBW = (!OUT_BF16 && (BN == 256 || !VV_G2_SUBW128_NARROW)) ? 64 : 128;
+  static constexpr int SUBW = (!OUT_BF16 && (BN != 128 || !VV_G2_SUBW128_NARROW)) ? 64 : 128;
   static constexpr int NSUB = BN / SUBW;                             // sub-tiles per MMA tile: 1, 2 or 4
   static constexpr int BOXES = SUBW / COLS_PER_BOX;                  // per sub-tile: 2 or 4
   static constexpr int STG_BYTES = BOXES * G2_BOX_BYTES;             // 32 KB or 64 KB
   static constexpr int B_BYTES = BN * G2_BK * 2;                     // 16 KB or 32 KB
-  static constexpr int NSTG = (BN == 128) ? (DEEP ? 1 : 2) : (DEEP ? 1 : 2);
-  static constexpr int STAGES = (BN == 128) ? (SUBW == 64 ? (DEEP ? 6 : 5) : (DEEP ? (OUT_BF16 ? 6 : 5) : (OUT_BF16 ? 5 : 3)))
+  // BN = 64 (the last upsampler, the encoder's first strided conv and its head): a 24 KB ring stage; the short-K
+  // layers are store-bound, so three staging slots keep TMA stores in flight behind the epilogue
+  static constexpr int NSTG = (BN == 64) ? (DEEP ? 2 : 3) : (DEEP ? 1 : 2);
+  static constexpr int STAGES = (BN == 64)  ? (DEEP ? 6 : 4)
+                              : (BN == 128) ? (SUBW == 64 ? (DEEP ? 6 : 5) : (DEEP ? (OUT_BF16 ? 6 : 5) : (OUT_BF16 ? 5 : 3)))
                                             : (DEEP ? 4 : 3);                                        // A/B ring depth
   static constexpr int OFF_RING = 0;
   static constexpr int OFF_STG = STAGES * (G2_A_BYTES + B_BYTES);

@@ -518,6 +518,11 @@ int launch_gemm(vv_decoder* d, const __nv_bfloat16* A, long long a_rpb, int rows
   if (rc == VV_OK && kind != -2) d->mark(kind, stage, s);
   return rc;
 }
+static bool g2_narrow64() {   // VV_GEMM_BN64=0: N = 64 layers back on the one-tile-per-CTA kernel (A/B)
+  static int mode = -1;
+  if (mode < 0) { const char* ev = getenv("VV_GEMM_BN64"); mode = ev ? atoi(ev) : 1; }
+  return mode != 0;
+}
 int launch_gemm_impl(vv_decoder* d, const __nv_bfloat16* A, long long a_rpb, int rows, int nbatch, const DenseW& w,
                      const EpiOut& e, cudaStream_t s) {
   GemmArgs g;
@@ -599,6 +604,28 @@ int launch_gemm_impl(vv_decoder* d, const __nv_bfloat16* A, long long a_rpb, int
     else if (e.epi == EPI_GELU_BF16) { if (deep) VV_G2_LAUNCH(EPI_GELU_BF16, true); else VV_G2_LAUNCH(EPI_GELU_BF16, false); }
     else { if (deep) VV_G2_LAUNCH(EPI_RESID, true); else VV_G2_LAUNCH(EPI_RESID, false); }
 #undef VV_G2_LAUNCH
+    VV_CUDA(cudaGetLastError());
+    return VV_OK;
+  }
+  if (w.BN == 64 && w.BK == G2_BK && e.epi == EPI_BIAS_F32 && d->cfg.gemm_path == 0 && g2_narrow64()) {
+    // N = 64 layers (last upsampler, encoder's first strided conv and head) on the persistent kernel's 64-wide tile
+    CUtensorMap tmO;
+    const uint32_t bt = 1u << best_log2, bb = 128u >> best_log2;
+    const uint64_t odims[3] = {(uint64_t)w.N, (uint64_t)rows, (uint64_t)nbatch};
+    const uint64_t ostr[2] = {(uint64_t)w.N * 4, (uint64_t)rows * w.N * 4};
+    const uint32_t obox[3] = {32u, bt, bb};
+    rc = encode_map(&tmO, e.out_f32, 3, odims, ostr, obox, true);
+    if (rc != VV_OK) return rc;
+    const unsigned grid2 = (unsigned)std::min<long long>(best_tiles * (w.N / 64), d->num_sms);
+    if (nk >= 32) {
+      rc = ensure_smem(gemm_tc2_kernel<EPI_BIAS_F32, true, 64>, (int)Gemm2Cfg<EPI_BIAS_F32, true, 64>::TOTAL, d->cfg.device);
+      if (rc != VV_OK) return rc;
+      gemm_tc2_kernel<EPI_BIAS_F32, true, 64><<<grid2, G2Warps<EPI_BIAS_F32>::THREADS, Gemm2Cfg<EPI_BIAS_F32, true, 64>::TOTAL, s>>>(tmA, w.tm, tmO, tmO, g);
+    } else {
+      rc = ensure_smem(gemm_tc2_kernel<EPI_BIAS_F32, false, 64>, (int)Gemm2Cfg<EPI_BIAS_F32, false, 64>::TOTAL, d->cfg.device);
+      if (rc != VV_OK) return rc;
+      gemm_tc2_kernel<EPI_BIAS_F32, false, 64><<<grid2, G2Warps<EPI_BIAS_F32>::THREADS, Gemm2Cfg<EPI_BIAS_F32, false, 64>::TOTAL, s>>>(tmA, w.tm, tmO, tmO, g);
+    }
     VV_CUDA(cudaGetLastError());
     return VV_OK;
   }
