@@ -239,6 +239,48 @@ def streaming_leg(dec, geom, dev, n_streams=256, steps=300, warmup=30):
         del senc, ecache
     except Exception as e:
         out["semantic_encode"] = {"error": f"{type(e).__name__}: {e}"[:200]}
+    # the PCM16 step + streamer hand-off of the chunk just decoded (main.py:937-951, streamer.py:50-55)
+    try:
+        import time
+        import numpy as np
+        import vvdec
+        chunk = step()
+        for _ in range(5):
+            vvdec.pcm16(chunk)
+        torch.cuda.synchronize()
+        k50, k99 = timed(lambda: vvdec.pcm16(chunk), steps)
+        streamer = vvdec.B200PcmStreamer(batch_size=n_streams)
+        host_idx = list(range(n_streams))
+
+        def wall(fn, n):
+            ts = []
+            for _ in range(n):
+                torch.cuda.synchronize()
+                t0 = time.perf_counter()
+                fn()
+                ts.append((time.perf_counter() - t0) * 1e3)
+            ts.sort()
+            return ts[len(ts) // 2]
+
+        def put_ours():
+            streamer.put(chunk, host_idx)
+            for q in streamer.audio_queues:                    # drain, as the consumer thread would
+                q.get_nowait()
+
+        def put_reference_pattern():                           # streamer.py:50-55 + main.py:937-951, per sample
+            for i in range(n_streams):
+                a = chunk[i].detach().cpu().float().numpy().astype(np.float32).squeeze()
+                if np.max(np.abs(a)) > 1.0:
+                    a = a / np.max(np.abs(a))
+                (a * 32767).astype(np.int16)
+        wall(put_ours, 5)
+        out["pcm16"] = {"kernel_p50_ms": k50, "kernel_p99_ms": k99, "launches_per_step": 1,
+                        "bytes_per_step": int(chunk.numel() * (chunk.element_size() + 2)),
+                        "streamer_put_wall_p50_ms": wall(put_ours, 50),
+                        "reference_pattern_wall_p50_ms": wall(put_reference_pattern, 10),
+                        "d2h_bytes_per_step": int(chunk.numel() * 2)}
+    except Exception as e:
+        out["pcm16"] = {"error": f"{type(e).__name__}: {e}"[:200]}
     return out
 
 

@@ -229,6 +229,19 @@ int32_t vv_kernel_upsample(vv_decoder* dec, int32_t stage, void* xb, float* y, i
 int32_t vv_kernel_head(vv_decoder* dec, const float* x, void* out, int32_t out_dtype, int32_t B,
                        int32_t rows, void* cuda_stream);
 
+/* ---- PCM16 output step ------------------------------------------------------------------------------
+ * Replaces convert_to_16_bit_wav (reference main.py:2956-2979; same function at demo/gradio_demo.py:1205), run by the
+ * Gradio path on every streamed chunk (main.py:937-951) and on the final waveform:
+ *     per row of wave [B, L]:  peak = max|x|;  if peak > 1: x = x / peak;  pcm = (int16) trunc(x * 32767)
+ * in fp32 with IEEE division / multiplication and truncation, i.e. bit-exact with the numpy original.  A row is one
+ * chunk / utterance (the reference converts each sample's chunk separately).
+ *   wave: device [B, L] f32 | bf16, rows row_stride elements apart (decode() output [B, 1, L] has row_stride = L);
+ *   pcm:  device int16 [B, L] contiguous;   peak: device fp32 [B], receives max|x| per row -- may be NULL when
+ *   L <= 8192 (one launch, row kept in registers); required for longer rows (peak pass + convert pass).
+ * Stateless; runs on the calling thread's current device. */
+int32_t vv_pcm16(const void* wave, int32_t wave_dtype, int32_t B, int64_t L, int64_t row_stride, int16_t* pcm,
+                 float* peak, void* cuda_stream);
+
 /* The GELU of the FFN epilogue (:589, :594), alone: y[i] = gelu(x[i]); device pointers.  Accuracy test hook. */
 int32_t vv_test_gelu(const float* x, float* y, int32_t n, void* cuda_stream);
 

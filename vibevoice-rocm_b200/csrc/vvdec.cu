@@ -14,6 +14,7 @@
 #include "block_fused.cuh"
 #include "gemm_tc2.cuh"
 #include "encoder.cuh"
+#include "pcm16.cuh"
 
 namespace vv {
 
@@ -1245,6 +1246,32 @@ namespace { __global__ void gelu_test_kernel(const float* x, float* y, int n) {
 extern "C" int32_t vv_test_gelu(const float* x, float* y, int32_t n, void* cuda_stream) {
   if (!x || !y || n < 1) { set_error("bad argument"); return VV_ERR_INVALID_ARG; }
   gelu_test_kernel<<<(n + 255) / 256, 256, 0, reinterpret_cast<cudaStream_t>(cuda_stream)>>>(x, y, n);
+  VV_CUDA(cudaGetLastError());
+  return VV_OK;
+}
+
+// PCM16 output step (reference convert_to_16_bit_wav, main.py:2956-2979): see pcm16.cuh.
+extern "C" int32_t vv_pcm16(const void* wave, int32_t wave_dtype, int32_t B, int64_t L, int64_t row_stride, int16_t* pcm,
+                            float* peak, void* cuda_stream) {
+  if (!wave || !pcm || B < 1 || L < 1 || row_stride < L) { set_error("bad argument"); return VV_ERR_INVALID_ARG; }
+  if (wave_dtype != VV_F32 && wave_dtype != VV_BF16) { set_error("wave must be f32 or bf16"); return VV_ERR_BAD_DTYPE; }
+  if (B > 65535) { set_error("at most 65535 rows per call"); return VV_ERR_BAD_SHAPE; }
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(cuda_stream);
+  Pcm16Args p;
+  p.wave = wave; p.wave_is_bf16 = (wave_dtype == VV_BF16); p.B = B; p.L = L; p.row_stride = row_stride;
+  p.pcm = pcm; p.peak = peak;
+  p.vec_ok = ((reinterpret_cast<uintptr_t>(wave) | reinterpret_cast<uintptr_t>(pcm)) % 16 == 0) && row_stride % 8 == 0 &&
+             (B == 1 || L % 8 == 0);
+  if (L <= PCM_ROW_MAX) {
+    pcm16_row_kernel<<<(unsigned)B, PCM_THREADS, 0, s>>>(p);
+  } else {
+    if (!peak) { set_error("rows longer than %d samples need the peak buffer", PCM_ROW_MAX); return VV_ERR_INVALID_ARG; }
+    const long long chunks = (L + PCM_CHUNK - 1) / PCM_CHUNK;
+    if (chunks > 0x7fffffffLL) { set_error("row too long"); return VV_ERR_BAD_SHAPE; }
+    VV_CUDA(cudaMemsetAsync(peak, 0, sizeof(float) * (size_t)B, s));
+    pcm16_peak_kernel<<<dim3((unsigned)chunks, (unsigned)B), PCM_THREADS, 0, s>>>(p);
+    pcm16_convert_kernel<<<dim3((unsigned)chunks, (unsigned)B), PCM_THREADS, 0, s>>>(p);
+  }
   VV_CUDA(cudaGetLastError());
   return VV_OK;
 }
