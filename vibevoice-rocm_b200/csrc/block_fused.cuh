@@ -177,19 +177,23 @@ block_fused_kernel(const __grid_constant__ CUtensorMap tmO, const __grid_constan
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_launch();
+  // ===== weights: loaded once, resident for the whole launch.  They are constants (written at finalize), so under
+  // programmatic dependent launch their TMA loads go out BEFORE this CTA waits for the previous kernel to drain. =====
+  if (warp == BF_E1_WARPS + BF_E2_WARPS + MXW && elect_one()) {
+    mbar_expect_tx(w_full, L::W1_BYTES + L::W2_BYTES);
+#pragma unroll
+    for (int j = 0; j < 4 * C / 128; ++j) tma_load_2d(sW1 + j * 128 * L::ROWB, &tmW1, w_full, 0, j * 128);
+#pragma unroll
+    for (int kb = 0; kb < NCH; ++kb) tma_load_2d(sW2 + kb * (C * 128), &tmW2, w_full, kb * 64, 0);
+  }
+  pdl_wait();
 
   if (warp >= WARP_CTRL) {
     reg_dec<L::REG_CTRL>();
     const int role = warp - WARP_CTRL;
     if (role == 0) {
-      // ===== weights: loaded once, resident for the whole launch ==========================================
-      if (elect_one()) {
-        mbar_expect_tx(w_full, L::W1_BYTES + L::W2_BYTES);
-#pragma unroll
-        for (int j = 0; j < 4 * C / 128; ++j) tma_load_2d(sW1 + j * 128 * L::ROWB, &tmW1, w_full, 0, j * 128);
-#pragma unroll
-        for (int kb = 0; kb < NCH; ++kb) tma_load_2d(sW2 + kb * (C * 128), &tmW2, w_full, kb * 64, 0);
-      }
+      // (weights loader: its TMA loads were issued above, before pdl_wait)
     } else if (role == 1) {
       // ===== GEMM 1 issuer: D1[g & 1] = a * W1_chunk^T =====================================================
       if (elect_one()) {

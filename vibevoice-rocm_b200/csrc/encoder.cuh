@@ -38,6 +38,8 @@ struct EncStemArgs {
 constexpr int ENC_STEM_ROWS = 4;   // rows per thread (the 10-sample window is shared between them)
 
 __global__ void __launch_bounds__(256) enc_stem_kernel(const EncStemArgs p) {
+  pdl_launch();
+  pdl_wait();
   constexpr int C = 32, Q = C / 4, RT = ENC_STEM_ROWS;
   const int quad = threadIdx.x % Q;                 // 4 channels of a row
   float4 w[7];
@@ -119,6 +121,8 @@ struct EncContextArgs {
 };
 
 __global__ void __launch_bounds__(256) enc_context_kernel(const EncContextArgs p) {
+  pdl_launch();
+  pdl_wait();
   const int c8 = p.C / 8;                                   // 16-byte cells per row
   const long long pad_rows = p.rpb - p.rows;                // per item: off context rows + tail rows
   const long long total = pad_rows * p.nbatch * c8;

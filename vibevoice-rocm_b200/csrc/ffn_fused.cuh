@@ -136,6 +136,8 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_launch();
+  pdl_wait();
 
   if (warp == 0) {
     // ===== TMA producer ==========================================================================

@@ -131,6 +131,8 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_launch();
+  pdl_wait();
 
   // tile index -> (n, t, b) coordinates
   auto tile_coords = [&](long long it, int& tile_n, int& tile_t, int& tile_b) {

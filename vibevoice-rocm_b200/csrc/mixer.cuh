@@ -19,6 +19,7 @@
 #include <cuda_runtime.h>
 #include <cuda_bf16.h>
 #include "epilogue.cuh"
+#include "ptx.cuh"
 
 namespace vv {
 
@@ -97,6 +98,8 @@ __device__ __forceinline__ void reduce7(float (&s)[7], float* xchg, int buf) {
 template <int LPR>
 __global__ void __launch_bounds__((LPR <= 32) ? 128 : LPR, (LPR <= 32) ? VV_MIXER_MINBLOCKS : 1)
 mixer_kernel(const MixerArgs p) {
+  pdl_launch();
+  pdl_wait();
   __shared__ float xchg[(LPR <= 32) ? 1 : 4 * (LPR / 32) * 8];
   int group, lane_in_group;
   if constexpr (LPR <= 32) {

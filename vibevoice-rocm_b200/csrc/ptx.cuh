@@ -22,6 +22,15 @@ __device__ __forceinline__ bool elect_one() {
   return pred != 0;
 }
 
+// ---- programmatic dependent launch -------------------------------------------------------------
+// Every kernel of the pass runs  [prologue: barrier init, TMEM alloc]  ->  pdl_launch(); pdl_wait();  ->  body.
+// With the launch attribute set (host: launch_k, VV_PDL=1) the NEXT kernel's CTAs are scheduled once every CTA of this
+// one has passed pdl_launch() -- i.e. holds all its resources, TMEM included -- run their own prologue and then block
+// in pdl_wait() until this grid has completed and its writes are visible; nothing before pdl_wait() may touch memory a
+// predecessor writes.  Without the attribute both instructions are no-ops.
+__device__ __forceinline__ void pdl_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 // ---- mbarrier ---------------------------------------------------------------------------------
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");

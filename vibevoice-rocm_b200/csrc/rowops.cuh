@@ -21,6 +21,8 @@ struct PrepArgs {
 };
 
 __global__ void prep_latents_kernel(const PrepArgs p) {
+  pdl_launch();
+  pdl_wait();
   const long long per_b = (long long)(p.T + 6) * p.D;
   const long long total = per_b * p.nbatch;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
@@ -57,6 +59,8 @@ struct HaloArgs {
 };
 
 __global__ void upsample_halo_kernel(const HaloArgs p) {
+  pdl_launch();
+  pdl_wait();
   const int total = p.nbatch * p.C;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
     const int b = i / p.C, c = i - b * p.C;
@@ -85,6 +89,8 @@ struct HeadArgs {
 };
 
 __global__ void __launch_bounds__(128) head_kernel(const HeadArgs p) {
+  pdl_launch();
+  pdl_wait();
   constexpr int C = 32, LPR = 8;
   const int gtid = blockIdx.x * blockDim.x + threadIdx.x;
   const int group = gtid / LPR, lig = gtid % LPR;
@@ -166,6 +172,8 @@ __global__ void __launch_bounds__(128) head_kernel(const HeadArgs p) {
 // ---- streaming-state bookkeeping -----------------------------------------------------------------------
 // After every stateful layer of a pass has written the inactive bank, the pass flips its slots' parity.
 __global__ void state_flip_kernel(const int* slot_ids, int n, int* parity) {
+  pdl_launch();
+  pdl_wait();
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) parity[slot_ids[i]] ^= 1;
 }

@@ -5,7 +5,9 @@
 #include <stdarg.h>
 #include <stdio.h>
 #include <string.h>
+#include <stdlib.h>
 #include <algorithm>
+#include <utility>
 #include <cmath>
 #include "vvdec_internal.h"
 #include "rowops.cuh"
@@ -26,6 +28,33 @@ void set_error(const char* fmt, ...) {
   va_end(ap);
 }
 const char* get_error() { return g_err; }
+
+// ---- kernel launch -------------------------------------------------------------------------------------
+// Every kernel of a decode / encode pass goes through launch_k.  With VV_PDL=1 the launch carries the programmatic
+// stream-serialization attribute: the kernel's CTAs may be scheduled while the previous kernel of the stream drains,
+// run their prologue (mbarrier init, TMEM allocation, descriptor prefetch) and block in griddepcontrol.wait until the
+// predecessor has completed (ptx.cuh: pdl_launch / pdl_wait; every kernel launched here executes both).  Default off:
+// the attribute list is empty and this is a plain launch.
+static bool pdl_enabled() {
+  static int mode = -1;
+  if (mode < 0) { const char* ev = getenv("VV_PDL"); mode = ev ? atoi(ev) : 0; }
+  return mode != 0;
+}
+template <typename... KArgs, typename... Args>
+static inline void launch_k(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, Args&&... args) {
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = s;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  (void)cudaLaunchKernelEx(&cfg, kern, std::forward<Args>(args)...);   // a failure stays in cudaGetLastError()
+}
 
 // ---- TMA tensor maps (driver entry point fetched through the runtime: no link against libcuda) ---------
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
@@ -506,7 +535,7 @@ int launch_gemm_inst(const CUtensorMap& tmA, const DenseW& w, const GemmArgs& g,
   const int rc = ensure_smem(gemm_tc_kernel<BN, BK>,
                              (int)gemm_smem_bytes<BN, BK>(std::min(GEMM_MAX_STAGES, (96 * 1024) / per_stage)), device);
   if (rc != VV_OK) return rc;
-  gemm_tc_kernel<BN, BK><<<grid, GEMM_THREADS, smem, s>>>(tmA, w.tm, g);
+  launch_k(gemm_tc_kernel<BN, BK>, dim3(grid), dim3(GEMM_THREADS), smem, s, tmA, w.tm, g);
   return VV_OK;
 }
 
@@ -594,11 +623,11 @@ int launch_gemm_impl(vv_decoder* d, const __nv_bfloat16* A, long long a_rpb, int
       if (wide) {                                                                                             \
         rc = ensure_smem(gemm_tc2_kernel<E, D, 256>, (int)Gemm2Cfg<E, D, 256>::TOTAL, d->cfg.device);         \
         if (rc != VV_OK) return rc;                                                                           \
-        gemm_tc2_kernel<E, D, 256><<<grid2, G2Warps<E>::THREADS, Gemm2Cfg<E, D, 256>::TOTAL, s>>>(tmA, w.tm256, tmR, tmO, g); \
+        launch_k(gemm_tc2_kernel<E, D, 256>, dim3(grid2), dim3(G2Warps<E>::THREADS), Gemm2Cfg<E, D, 256>::TOTAL, s, tmA, w.tm256, tmR, tmO, g); \
       } else {                                                                                                \
         rc = ensure_smem(gemm_tc2_kernel<E, D, 128>, (int)Gemm2Cfg<E, D, 128>::TOTAL, d->cfg.device);         \
         if (rc != VV_OK) return rc;                                                                           \
-        gemm_tc2_kernel<E, D, 128><<<grid2, G2Warps<E>::THREADS, Gemm2Cfg<E, D, 128>::TOTAL, s>>>(tmA, w.tm, tmR, tmO, g);  \
+        launch_k(gemm_tc2_kernel<E, D, 128>, dim3(grid2), dim3(G2Warps<E>::THREADS), Gemm2Cfg<E, D, 128>::TOTAL, s, tmA, w.tm, tmR, tmO, g);  \
       }                                                                                                       \
     } while (0)
     if (e.epi == EPI_BIAS_F32) { if (deep) VV_G2_LAUNCH(EPI_BIAS_F32, true); else VV_G2_LAUNCH(EPI_BIAS_F32, false); }
@@ -621,11 +650,11 @@ int launch_gemm_impl(vv_decoder* d, const __nv_bfloat16* A, long long a_rpb, int
     if (nk >= 32) {
       rc = ensure_smem(gemm_tc2_kernel<EPI_BIAS_F32, true, 64>, (int)Gemm2Cfg<EPI_BIAS_F32, true, 64>::TOTAL, d->cfg.device);
       if (rc != VV_OK) return rc;
-      gemm_tc2_kernel<EPI_BIAS_F32, true, 64><<<grid2, G2Warps<EPI_BIAS_F32>::THREADS, Gemm2Cfg<EPI_BIAS_F32, true, 64>::TOTAL, s>>>(tmA, w.tm, tmO, tmO, g);
+      launch_k(gemm_tc2_kernel<EPI_BIAS_F32, true, 64>, dim3(grid2), dim3(G2Warps<EPI_BIAS_F32>::THREADS), Gemm2Cfg<EPI_BIAS_F32, true, 64>::TOTAL, s, tmA, w.tm, tmO, tmO, g);
     } else {
       rc = ensure_smem(gemm_tc2_kernel<EPI_BIAS_F32, false, 64>, (int)Gemm2Cfg<EPI_BIAS_F32, false, 64>::TOTAL, d->cfg.device);
       if (rc != VV_OK) return rc;
-      gemm_tc2_kernel<EPI_BIAS_F32, false, 64><<<grid2, G2Warps<EPI_BIAS_F32>::THREADS, Gemm2Cfg<EPI_BIAS_F32, false, 64>::TOTAL, s>>>(tmA, w.tm, tmO, tmO, g);
+      launch_k(gemm_tc2_kernel<EPI_BIAS_F32, false, 64>, dim3(grid2), dim3(G2Warps<EPI_BIAS_F32>::THREADS), Gemm2Cfg<EPI_BIAS_F32, false, 64>::TOTAL, s, tmA, w.tm, tmO, tmO, g);
     }
     VV_CUDA(cudaGetLastError());
     return VV_OK;
@@ -654,7 +683,7 @@ int launch_ffn_fused_inst(vv_decoder* d, const CUtensorMap& tmA, const CUtensorM
   const int num_sms = d->num_sms;
   const long long ntiles = (fa.R + 127) / 128;
   const unsigned grid = (unsigned)std::min<long long>(ntiles, num_sms);
-  ffn_fused_kernel<C><<<grid, FF_THREADS, FfnFusedSmem<C>::TOTAL, s>>>(tmA, tmR, tmO, bw.lin1.tm, bw.lin2.tm, fa);
+  launch_k(ffn_fused_kernel<C>, dim3(grid), dim3(FF_THREADS), FfnFusedSmem<C>::TOTAL, s, tmA, tmR, tmO, bw.lin1.tm, bw.lin2.tm, fa);
   VV_CUDA(cudaGetLastError());
   return VV_OK;
 }
@@ -695,7 +724,7 @@ int launch_ffn_fused(vv_decoder* d, int C, const BlockW& bw, const __nv_bfloat16
   const long long ntiles = (R + 127) / 128;
   const unsigned grid = (unsigned)std::min<long long>(ntiles, num_sms);
   if (R + 256LL * num_sms >= (1LL << 31)) { set_error("ffn_stream: %lld rows exceed the 31-bit row index", R); return VV_ERR_BAD_SHAPE; }
-  ffn_stream_kernel<128><<<grid, FS_THREADS, FfnStreamCfg<128>::TOTAL, s>>>(tmA, tmR, tmO, bw.tm_w1s, bw.lin2.tm, fa);
+  launch_k(ffn_stream_kernel<128>, dim3(grid), dim3(FS_THREADS), FfnStreamCfg<128>::TOTAL, s, tmA, tmR, tmO, bw.tm_w1s, bw.lin2.tm, fa);
   VV_CUDA(cudaGetLastError());
   return VV_OK;
 }
@@ -714,7 +743,7 @@ int launch_block_fused_inst(vv_decoder* d, const CUtensorMap& tmO, const BlockW&
   const int num_sms = d->num_sms;
   const long long ntiles = (long long)a.nbatch * a.tiles_pb;
   const unsigned grid = (unsigned)std::min<long long>(ntiles, num_sms);
-  block_fused_kernel<C, STATE><<<grid, BlockFusedCfg<C>::THREADS, BlockFusedCfg<C>::TOTAL, s>>>(tmO, bw.lin1.tm, bw.lin2.tm, a);
+  launch_k(block_fused_kernel<C, STATE>, dim3(grid), dim3(BlockFusedCfg<C>::THREADS), BlockFusedCfg<C>::TOTAL, s, tmO, bw.lin1.tm, bw.lin2.tm, a);
   VV_CUDA(cudaGetLastError());
   return VV_OK;
 }
@@ -818,8 +847,8 @@ int launch_mixer(vv_decoder* d, const BlockW& bw, int C, const float* x, float* 
   d->launches++;
 #define VV_MIXER_CASE(L)                                                                         \
   case L:                                                                                        \
-    if (L <= 32) mixer_kernel<L><<<(unsigned)((groups * L + 127) / 128), 128, 0, s>>>(p);        \
-    else mixer_kernel<L><<<(unsigned)groups, L, 0, s>>>(p);                                      \
+    if (L <= 32) launch_k(mixer_kernel<L>, dim3((unsigned)((groups * L + 127) / 128)), dim3(128), 0, s, p);        \
+    else launch_k(mixer_kernel<L>, dim3((unsigned)groups), dim3(L), 0, s, p);                                      \
     break;
   switch (lpr) {
     VV_MIXER_CASE(8) VV_MIXER_CASE(16) VV_MIXER_CASE(32) VV_MIXER_CASE(64) VV_MIXER_CASE(128)
@@ -881,7 +910,7 @@ int run_pass(vv_decoder* d, const LatView& lat, int nb, int T, void* audio, int 
     p.out = LB; p.nbatch = nb; p.T = T; p.D = D;
     p.st_ref = make_state_ref(st, slots, d->stages[0].up_state_off);
     const long long total = (long long)nb * (T + 6) * D;
-    prep_latents_kernel<<<(unsigned)std::min<long long>((total + 255) / 256, 148 * 16), 256, 0, s>>>(p);
+    launch_k(prep_latents_kernel, dim3((unsigned)std::min<long long>((total + 255) / 256, 148 * 16)), dim3(256), 0, s, p);
     d->launches++;
     VV_CUDA(cudaGetLastError());
     d->mark(VV_K_PREP, 0, s);
@@ -912,7 +941,7 @@ int run_pass(vv_decoder* d, const LatView& lat, int nb, int T, void* audio, int 
       HaloArgs hp;
       hp.xb = PXB; hp.nbatch = nb; hp.rows = prow; hp.C = pw.C;
       hp.st_ref = make_state_ref(st, slots, sw.up_state_off);
-      upsample_halo_kernel<<<(unsigned)std::min((nb * pw.C + 255) / 256, 148 * 8), 256, 0, s>>>(hp);
+      launch_k(upsample_halo_kernel, dim3((unsigned)std::min((nb * pw.C + 255) / 256, 148 * 8)), dim3(256), 0, s, hp);
       d->launches++;
       VV_CUDA(cudaGetLastError());
       d->mark(VV_K_HALO, i, s);
@@ -955,14 +984,14 @@ int run_pass(vv_decoder* d, const LatView& lat, int nb, int T, void* audio, int 
       hp.strips_per_batch = (rows_pb + hp.strip - 1) / hp.strip;
       hp.st = make_state_ref(st, slots, d->head_state_off);
       const long long groups = (long long)nb * hp.strips_per_batch;
-      head_kernel<<<(unsigned)((groups * 8 + 127) / 128), 128, 0, s>>>(hp);
+      launch_k(head_kernel, dim3((unsigned)((groups * 8 + 127) / 128)), dim3(128), 0, s, hp);
       d->launches++;
       VV_CUDA(cudaGetLastError());
       d->mark(VV_K_HEAD, i, s);
     }
   }
   if (st != nullptr) {
-    state_flip_kernel<<<(nb + 127) / 128, 128, 0, s>>>(slots, nb, st->parity);
+    launch_k(state_flip_kernel, dim3((nb + 127) / 128), dim3(128), 0, s, slots, nb, st->parity);
     d->launches++;
     VV_CUDA(cudaGetLastError());
     d->mark(VV_K_STATE, 0, s);
@@ -1212,7 +1241,7 @@ extern "C" int32_t vv_kernel_upsample(vv_decoder* d, int32_t stage, void* xb, fl
   HaloArgs hp;
   hp.xb = reinterpret_cast<__nv_bfloat16*>(xb); hp.nbatch = B; hp.rows = rows; hp.C = sw.up.Ktap;
   hp.st_ref = make_state_ref(nullptr, nullptr, 0);
-  upsample_halo_kernel<<<(unsigned)std::min((B * hp.C + 255) / 256, 148 * 8), 256, 0, s>>>(hp);
+  launch_k(upsample_halo_kernel, dim3((unsigned)std::min((B * hp.C + 255) / 256, 148 * 8)), dim3(256), 0, s, hp);
   d->launches++;
   VV_CUDA(cudaGetLastError());
   EpiOut e;
@@ -1232,7 +1261,7 @@ extern "C" int32_t vv_kernel_head(vv_decoder* d, const float* x, void* out, int3
   hp.strips_per_batch = (rows + hp.strip - 1) / hp.strip;
   hp.st = make_state_ref(nullptr, nullptr, 0);
   const long long groups = (long long)B * hp.strips_per_batch;
-  head_kernel<<<(unsigned)((groups * 8 + 127) / 128), 128, 0, reinterpret_cast<cudaStream_t>(cuda_stream)>>>(hp);
+  launch_k(head_kernel, dim3((unsigned)((groups * 8 + 127) / 128)), dim3(128), 0, reinterpret_cast<cudaStream_t>(cuda_stream), hp);
   d->launches++;
   VV_CUDA(cudaGetLastError());
   return VV_OK;

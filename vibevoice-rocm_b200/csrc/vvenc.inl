@@ -96,7 +96,7 @@ int enc_run_pass(vv_encoder* e, const void* audio, int audio_is_bf16, long long 
       p.w = e->stem_w; p.b = e->stem_b; p.x = X; p.nbatch = nb; p.L = rows_pb;
       p.st = make_state_ref(st, slots, e->stem_state_off);
       const long long threads = ((long long)rows_pb + ENC_STEM_ROWS - 1) / ENC_STEM_ROWS * nb * 8;
-      enc_stem_kernel<<<(unsigned)std::min<long long>((threads + 255) / 256, 148LL * 64), 256, 0, s>>>(p);
+      launch_k(enc_stem_kernel, dim3((unsigned)std::min<long long>((threads + 255) / 256, 148LL * 64)), dim3(256), 0, s, p);
       d->launches++;
       VV_CUDA(cudaGetLastError());
       d->mark(VV_K_ENC_STEM, 0, s);
@@ -141,7 +141,7 @@ int enc_run_pass(vv_encoder* e, const void* audio, int audio_is_bf16, long long 
       cp.xb = XB; cp.nbatch = nb; cp.rows = rows_pb; cp.off = bo.xb_off; cp.C = C; cp.rpb = bo.xb_rpb;
       cp.st = make_state_ref(st, slots, i + 1 < S ? d->stages[i + 1].up_state_off : e->head_state_off);
       const long long cells = (bo.xb_rpb - rows_pb) * nb * (C / 8);
-      enc_context_kernel<<<(unsigned)std::max<long long>(1, std::min<long long>((cells + 255) / 256, 148LL * 16)), 256, 0, s>>>(cp);
+      launch_k(enc_context_kernel, dim3((unsigned)std::max<long long>(1, std::min<long long>((cells + 255) / 256, 148LL * 16))), dim3(256), 0, s, cp);
       d->launches++;
       VV_CUDA(cudaGetLastError());
       d->mark(VV_K_PAD, i, s);
@@ -154,7 +154,7 @@ int enc_run_pass(vv_encoder* e, const void* audio, int audio_is_bf16, long long 
     }
   }
   if (st != nullptr) {
-    state_flip_kernel<<<(nb + 127) / 128, 128, 0, s>>>(slots, nb, st->parity);
+    launch_k(state_flip_kernel, dim3((nb + 127) / 128), dim3(128), 0, s, slots, nb, st->parity);
     d->launches++;
     VV_CUDA(cudaGetLastError());
     d->mark(VV_K_STATE, 0, s);
@@ -352,7 +352,7 @@ extern "C" int32_t vv_kernel_enc_stem(vv_encoder* e, const void* audio, int32_t 
   p.w = e->stem_w; p.b = e->stem_b; p.x = x; p.nbatch = B; p.L = (int)L;
   p.st = make_state_ref(nullptr, nullptr, 0);
   const long long threads = (L + ENC_STEM_ROWS - 1) / ENC_STEM_ROWS * B * 8;
-  enc_stem_kernel<<<(unsigned)std::min<long long>((threads + 255) / 256, 148LL * 64), 256, 0, s>>>(p);
+  launch_k(enc_stem_kernel, dim3((unsigned)std::min<long long>((threads + 255) / 256, 148LL * 64)), dim3(256), 0, s, p);
   e->core.launches++;
   VV_CUDA(cudaGetLastError());
   return VV_OK;
@@ -374,7 +374,7 @@ extern "C" int32_t vv_kernel_downsample(vv_encoder* e, int32_t stage, void* xb, 
   cp.rpb = (long long)(rows_out + 1) * r;
   cp.st = make_state_ref(nullptr, nullptr, 0);
   const long long cells = (cp.rpb - rows) * B * (Cin / 8);
-  enc_context_kernel<<<(unsigned)std::max<long long>(1, std::min<long long>((cells + 255) / 256, 148LL * 16)), 256, 0, s>>>(cp);
+  launch_k(enc_context_kernel, dim3((unsigned)std::max<long long>(1, std::min<long long>((cells + 255) / 256, 148LL * 16))), dim3(256), 0, s, cp);
   d->launches++;
   VV_CUDA(cudaGetLastError());
   EpiOut eo;
@@ -393,7 +393,7 @@ extern "C" int32_t vv_kernel_enc_head(vv_encoder* e, void* xb, float* mean, int3
   cp.xb = reinterpret_cast<__nv_bfloat16*>(xb); cp.nbatch = B; cp.rows = rows; cp.off = 6; cp.C = C; cp.rpb = rows + 6;
   cp.st = make_state_ref(nullptr, nullptr, 0);
   const long long cells = 6LL * B * (C / 8);
-  enc_context_kernel<<<(unsigned)std::max<long long>(1, std::min<long long>((cells + 255) / 256, 148LL * 16)), 256, 0, s>>>(cp);
+  launch_k(enc_context_kernel, dim3((unsigned)std::max<long long>(1, std::min<long long>((cells + 255) / 256, 148LL * 16))), dim3(256), 0, s, cp);
   d->launches++;
   VV_CUDA(cudaGetLastError());
   EpiOut eo;
