@@ -9,7 +9,7 @@ step() { local name=$1 lim=$2; shift 2; local t0=$(date +%s); timeout $lim "$@" 
          echo "$name rc=$rc $(( $(date +%s) - t0 ))s" | tee -a $O/steps.txt; }
 : > $O/steps.txt
 nvidia-smi --query-gpu=name,clocks.max.sm,power.limit --format=csv > $O/gpu.txt 2>&1
-step tests_gpu 420 python -m pytest tests -m gpu -x -q
+step tests_gpu 420 python -m pytest tests -m gpu -q
 step smoke 240 python -c "import __graft_entry__ as g; g.smoke()"
 step bench 540 python bench.py --kernels-out $O/kernels.json --encoder-kernels-out $O/kernels_encoder.json
 BARGS="--steps 1 --warmup 3 --no-cpu-baseline --no-streaming --no-encoder --no-longform --no-torch-eager"
@@ -21,5 +21,5 @@ step ncu_pcm16 240 ncu --set full --clock-control none --import-source on -k reg
 import sys; sys.path.insert(0, 'vibevoice-rocm_b200'); import torch, vvdec
 x = (torch.randn(64, 1, 1440000, device='cuda') * 3).to(torch.bfloat16)
 vvdec.pcm16(x); vvdec.pcm16(x[:, :, :3200].contiguous()); torch.cuda.synchronize()"
-step tests_gpu_pdl 420 env VV_PDL=1 python -m pytest tests -m gpu -x -q
+step tests_gpu_pdl 420 env VV_PDL=1 python -m pytest tests -m gpu -q
 cat $O/steps.txt
