@@ -189,3 +189,29 @@ def test_encoder_output_distribution_semantics():
             assert torch.equal(out.kl(), ref.kl())
     except ImportError:
         pass
+
+
+def test_pcm16_has_no_cpu_path_and_streamer_queue_contract():
+    """vv_pcm16: a CPU tensor is refused (nothing routes to numpy); the streamer's end / get_stream /
+    iteration contract (streamer.py:57-101) holds without any chunk having been put."""
+    import torch
+    import vvdec
+    with pytest.raises(RuntimeError, match="no CPU path"):
+        vvdec.pcm16(torch.zeros(2, 3200))
+    with pytest.raises(ValueError):
+        vvdec.pcm16([0.0, 1.0])
+    st = vvdec.B200PcmStreamer(batch_size=2, stop_signal=None, timeout=1.0)
+    with pytest.raises(RuntimeError, match="no CPU path"):
+        st.put(torch.zeros(2, 3200), [0, 1])
+    with pytest.raises(AssertionError):
+        st.put(torch.zeros(2, 3200), [0])
+    st.end([1])
+    assert st.finished_flags == [False, True]
+    assert list(st.get_stream(1)) == []
+    st.end()
+    assert list(st.get_stream(0)) == []
+    st2 = vvdec.B200PcmStreamer(batch_size=2, timeout=1.0)
+    st2.end()
+    assert list(st2) == []                                # batch iteration consumes the stop signals itself
+    with pytest.raises(ValueError):
+        st.get_stream(2)
