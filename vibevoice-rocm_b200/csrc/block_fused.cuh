@@ -46,13 +46,25 @@ struct BlockFusedArgs {
   StateRef st;               // mixer context: fp32 [6][C] raw rows per stream (null base = offline)
 };
 
+// VV_BF_MXSETS32 = 2: at C = 32 two sets of mixer warps work on alternate tiles (set s takes this CTA's tiles s, s + 2,
+// ...).  ncu (profiles/block_fused_s6_r01.txt + source page): the 4 mixer warps -- one per scheduler -- are never idle
+// and issue at ~0.2 IPC (dependency, shuffle and load latency), everything downstream waits for them; a second set doubles
+// the latency-bound work in flight without adding warm-up rows.  All slots and barriers stay per tile.
+// MEASURED SLOWER on B200 (tools/kbench.py --kind block --stage 6, 5760 frames): 1.72 ms -> 2.06 ms with 2 sets (parity
+// tests green); the 8 mixer warps get 128 registers instead of 168 (256 B of spills) and share the issue slots and the
+// L1 with E1 / E2 -- so the default stays 1 and the finding stands next to DESIGN.md section 4 (5).
+#ifndef VV_BF_MXSETS32
+#define VV_BF_MXSETS32 1
+#endif
 constexpr int BF_E1_WARPS = 8;
 constexpr int BF_E2_WARPS = 4;
 
 template <int C>
 struct BlockFusedCfg {
   static_assert(C == 32 || C == 64, "block_fused_kernel is laid out for C = 32 / 64");
-  static constexpr int MXW = C / 8;                 // mixer warps
+  static constexpr int MXW_TILE = C / 8;            // mixer warps that build one tile
+  static constexpr int MXSETS = (C == 32) ? VV_BF_MXSETS32 : 1;   // sets of them, working on alternate tiles
+  static constexpr int MXW = MXW_TILE * MXSETS;     // mixer warps in the CTA
   static constexpr int LPR = C / 4;                 // lanes per row
   static constexpr int WARPS = BF_E1_WARPS + BF_E2_WARPS + MXW + 4;
   static constexpr int THREADS = WARPS * 32;
@@ -81,7 +93,7 @@ struct BlockFusedCfg {
   // with (threads x launch registers), not the whole register file: with 768 threads x 80 registers a 144-register
   // mixer (total 65536) hung on B200, 128 (total 61440) runs.
   static constexpr int REG_LAUNCH = (65536 / THREADS) / 8 * 8;      // what __launch_bounds__(THREADS, 1) yields
-  static constexpr int REG_E = 64, REG_E2 = 64, REG_CTRL = 32, REG_MX = (C == 64) ? 128 : 168;   // (136 / 56 / 24 at C = 64: spill-free mixer, not faster)
+  static constexpr int REG_E = 64, REG_E2 = 64, REG_CTRL = 32, REG_MX = (C == 64 || MXSETS > 1) ? 128 : 168;   // (136 / 56 / 24 at C = 64: spill-free mixer, not faster)
   static_assert(32 * (BF_E1_WARPS * REG_E + BF_E2_WARPS * REG_E2 + 4 * REG_CTRL + MXW * REG_MX) <= THREADS * REG_LAUNCH,
                 "setmaxnreg budget exceeds the CTA's launch allocation");
 };
@@ -153,9 +165,9 @@ block_fused_kernel(const __grid_constant__ CUtensorMap tmO, const __grid_constan
     tma_prefetch_desc(&tmW1);
     tma_prefetch_desc(&tmW2);
     mbar_init(w_full, 1);
-    for (int i = 0; i < NA; ++i) { mbar_init(&a_full[i], MXW); mbar_init(&a_empty[i], 1); }
+    for (int i = 0; i < NA; ++i) { mbar_init(&a_full[i], L::MXW_TILE); mbar_init(&a_empty[i], 1); }
     for (int i = 0; i < NY; ++i) {
-      mbar_init(&y_full[i], MXW);
+      mbar_init(&y_full[i], L::MXW_TILE);
       mbar_init(&y_ready[i], BF_E2_WARPS);
       mbar_init(&y_empty[i], 1);
     }
@@ -370,7 +382,9 @@ block_fused_kernel(const __grid_constant__ CUtensorMap tmO, const __grid_constan
     // ===== mixer: x (global) -> y (staging slot) + a (GEMM 1 operand tile) ====================================
     reg_inc<L::REG_MX>();
     struct P4 { f32x2 lo, hi; };               // 4 adjacent channels as two packed fp32 pairs (FFMA2)
-    const int gi = (warp - WARP_MX) * (32 / LPR) + lane / LPR;      // strip 0..15: tile rows [8 gi, 8 gi + 8)
+    constexpr int MXSETS = L::MXSETS;
+    const int mset = (warp - WARP_MX) / L::MXW_TILE;                 // this warp's set: tiles mset, mset + MXSETS, ...
+    const int gi = ((warp - WARP_MX) % L::MXW_TILE) * (32 / LPR) + lane / LPR;   // strip 0..15: tile rows [8 gi, 8 gi + 8)
     const int c0 = (lane % LPR) * 4;
     const float inv_c = 1.0f / (float)C;
     // folded taps: y = x + gb + sum_j wq[j] * n[t-6+j],  n = x * rstd,  wq = gamma * w * norm_w,  gb = gamma * conv_bias
@@ -475,12 +489,12 @@ block_fused_kernel(const __grid_constant__ CUtensorMap tmO, const __grid_constan
     //  C = 64; the next-tile prefetch staged through shared memory with cp.async instead of registers, 1.87 -> 2.03 ms)
     float4 bufA[7], bufB[7];
     int b, t0, nb = 0, nt0 = 0;
-    tile_of(0, b, t0);
-    load_rows(0, b, t0, 0, bufA);
-    for (int it = 0; it < my_tiles; ++it) {
+    tile_of(mset, b, t0);
+    load_rows(mset, b, t0, 0, bufA);
+    for (int it = mset; it < my_tiles; it += MXSETS) {
       const int sa = it % NA, sy = it % NY;
-      if (it > 0) { b = nb; t0 = nt0; }
-      tile_of(it + 1, nb, nt0);
+      if (it > mset) { b = nb; t0 = nt0; }
+      tile_of(it + MXSETS, nb, nt0);
       if (STATE && p.st.base != nullptr) {
         const uint8_t* rd8;
         uint8_t* wr8;
@@ -523,7 +537,7 @@ block_fused_kernel(const __grid_constant__ CUtensorMap tmO, const __grid_constan
         mbar_wait(&y_empty[sy], (uint32_t)(((it / NY) & 1) ^ 1));
         store_row(0, rows[6], rstd_of(s2, inv_c, p.eps), fw, ys, as);
       }
-      load_rows(it + 1, nb, nt0, 0, bufA);                 // first batch of the next tile: in flight during batch 1
+      load_rows(it + MXSETS, nb, nt0, 0, bufA);            // first batch of this set's next tile: in flight during batch 1
 
       // ---- batch 1: output rows k = 1..7 ------------------------------------------------------------------------
       {

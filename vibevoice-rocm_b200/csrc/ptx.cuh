@@ -48,8 +48,27 @@ __device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
+// VV_TRYWAIT_HINT_NS > 0 passes try_wait's optional suspend-time hint: the thread sleeps IN HARDWARE until the phase
+// completes or the time is up, instead of coming back after the (short) default limit to execute the poll loop again.
+// ncu on block_fused (profiles/block_fused_s6_r01.txt, source page): 47 % of all warp instructions executed were poll
+// loops of the E1 / E2 / control warps, taking issue slots from the mixer warps on the critical path.
+// Measured (same box, back to back, tools/ab_libs.sh): hint 0 / 2000 / 10^7 ns -> K2 step 218.4 / 218.7 / 217.2 ms (noise),
+// K4 streaming step 3.00 / 2.95 / 2.95 ms, semantic streaming encode 3.15 / 3.09 / 3.09 ms: the polls were not what
+// held the mixer warps back, but half the executed instructions are gone for free.  SASS: TRYWAIT; @!P0 NANOSLEEP.SYNCS.
+#ifndef VV_TRYWAIT_HINT_NS
+#define VV_TRYWAIT_HINT_NS 2000
+#endif
 __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
   uint32_t ok;
+#if VV_TRYWAIT_HINT_NS > 0
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}\n"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity), "r"((uint32_t)VV_TRYWAIT_HINT_NS)
+      : "memory");
+#else
   asm volatile(
       "{\n\t.reg .pred p;\n\t"
       "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
@@ -57,6 +76,7 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
       : "=r"(ok)
       : "r"(smem_u32(bar)), "r"(parity)
       : "memory");
+#endif
   return ok != 0;
 }
 // Spin on try_wait (which itself sleeps in hardware).  A protocol bug would otherwise hang the GPU until
