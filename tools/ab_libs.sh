@@ -1,3 +1,8 @@
+#!/bin/bash
+# A/B of library builds on one box, back to back: K2 headline (3 steps), K4 streaming and the per-kernel table for each
+# lib listed below.  Variant libs are built next to the product one with extra -D flags, e.g.
+#   nvcc <flags of __graft_entry__.NVCC_FLAGS> -DVV_TRYWAIT_HINT_NS=0 -o vibevoice-rocm_b200/vvdec/libvvdec_b200_hint0.so vibevoice-rocm_b200/csrc/vvdec.cu
+# and selected through VVDEC_LIB (vvdec/_capi.py).  Usage: gpurun -- 'bash tools/ab_libs.sh'  (edit the list).
 mkdir -p gpurun_out
 BARGS="--steps 3 --warmup 3 --no-cpu-baseline --no-encoder --no-longform --no-torch-eager"
 for L in libvvdec_b200 libvvdec_b200_hint2000 libvvdec_b200_hint10000000; do

@@ -1,3 +1,6 @@
+#!/bin/bash
+# Final verification of HEAD on the GPU box: every GPU test, smoke(), the bench line, the ncu launch list of the
+# same command (after it ran alone) and the reference arm.  Outputs under gpurun_out/f_*.
 set +e
 O=gpurun_out; mkdir -p $O
 step() { local name=$1 lim=$2; shift 2; local t0=$(date +%s); timeout $lim "$@" > $O/$name.log 2> $O/$name.err; echo "$name rc=$? $(( $(date +%s) - t0 ))s" | tee -a $O/steps2.txt; }
