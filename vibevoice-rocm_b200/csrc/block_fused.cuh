@@ -383,8 +383,11 @@ block_fused_kernel(const __grid_constant__ CUtensorMap tmO, const __grid_constan
     reg_inc<L::REG_MX>();
     struct P4 { f32x2 lo, hi; };               // 4 adjacent channels as two packed fp32 pairs (FFMA2)
     constexpr int MXSETS = L::MXSETS;
-    const int mset = (warp - WARP_MX) / L::MXW_TILE;                 // this warp's set: tiles mset, mset + MXSETS, ...
-    const int gi = ((warp - WARP_MX) % L::MXW_TILE) * (32 / LPR) + lane / LPR;   // strip 0..15: tile rows [8 gi, 8 gi + 8)
+    // this warp's set: tiles mset, mset + MXSETS, ...  (a compile-time 0 with one set: at C = 64 the mixer sits on its
+    // register limit, and a run-time mset cost one more live register = 20 % on the kernel, measured)
+    const int mset = (MXSETS > 1) ? (warp - WARP_MX) / L::MXW_TILE : 0;
+    const int mwarp = (MXSETS > 1) ? (warp - WARP_MX) % L::MXW_TILE : (warp - WARP_MX);
+    const int gi = mwarp * (32 / LPR) + lane / LPR;                  // strip 0..15: tile rows [8 gi, 8 gi + 8)
     const int c0 = (lane % LPR) * 4;
     const float inv_c = 1.0f / (float)C;
     // folded taps: y = x + gb + sum_j wq[j] * n[t-6+j],  n = x * rstd,  wq = gamma * w * norm_w,  gb = gamma * conv_bias
