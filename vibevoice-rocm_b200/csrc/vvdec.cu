@@ -33,12 +33,19 @@ const char* get_error() { return g_err; }
 // Every kernel of a decode / encode pass goes through launch_k.  With VV_PDL=1 the launch carries the programmatic
 // stream-serialization attribute: the kernel's CTAs may be scheduled while the previous kernel of the stream drains,
 // run their prologue (mbarrier init, TMEM allocation, descriptor prefetch) and block in griddepcontrol.wait until the
-// predecessor has completed (ptx.cuh: pdl_launch / pdl_wait; every kernel launched here executes both).  Default off:
-// the attribute list is empty and this is a plain launch.
+// predecessor has completed (ptx.cuh: pdl_launch / pdl_wait; every kernel launched here executes both).
+// VV_PDL unset: on for small streaming calls only (a state is given and the call holds <= 2048 frames: the K4 step
+// drops 2.95 -> 2.83 ms; every launch of such a call is 5-140 us long), off for offline passes (K2 measured 5 % SLOWER
+// with it).  VV_PDL=0: never; VV_PDL=1: every launch (the whole GPU suite passes under it).
+static thread_local bool g_pdl_small_stream = false;
+struct PdlScope {                        // marks the calling thread's current vv_decode / vv_encode call
+  explicit PdlScope(bool small_stream) { g_pdl_small_stream = small_stream; }
+  ~PdlScope() { g_pdl_small_stream = false; }
+};
 static bool pdl_enabled() {
-  static int mode = -1;
-  if (mode < 0) { const char* ev = getenv("VV_PDL"); mode = ev ? atoi(ev) : 0; }
-  return mode != 0;
+  static int mode = -2;
+  if (mode == -2) { const char* ev = getenv("VV_PDL"); mode = ev ? (atoi(ev) != 0 ? 1 : 0) : -1; }
+  return mode == 1 || (mode == -1 && g_pdl_small_stream);
 }
 template <typename... KArgs, typename... Args>
 static inline void launch_k(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, Args&&... args) {
@@ -1096,6 +1103,7 @@ static int32_t decode_impl(vv_decoder* d, const void* latents, int32_t lat_dtype
 extern "C" int32_t vv_decode(vv_decoder* d, const void* latents, int32_t lat_dtype, int32_t layout, int32_t B,
                              int32_t T, void* audio, int32_t out_dtype, void* workspace, int64_t workspace_bytes,
                              vv_state* state, const int32_t* slot_ids, void* cuda_stream) {
+  PdlScope pdl(state != nullptr && (long long)B * T <= 2048);
   const int32_t rc = decode_impl(d, latents, lat_dtype, layout, B, T, audio, out_dtype, workspace, workspace_bytes,
                                  state, slot_ids, cuda_stream);
   if (d != nullptr) prof_collect(d, reinterpret_cast<cudaStream_t>(cuda_stream));

@@ -310,6 +310,7 @@ extern "C" int32_t vv_encode(vv_encoder* e, const void* audio, int32_t audio_dty
   if (((uintptr_t)workspace & 1023) != 0) { set_error("workspace must be 1 KB aligned"); return VV_ERR_INVALID_ARG; }
   if (state != nullptr && slot_ids == nullptr) { set_error("state given without slot_ids"); return VV_ERR_INVALID_ARG; }
   if (state != nullptr && state->dec != d) { set_error("state belongs to another encoder / decoder"); return VV_ERR_INVALID_ARG; }
+  PdlScope pdl(state != nullptr && (long long)B * (L / d->hop) <= 2048);
   if (state != nullptr && L % d->hop != 0) {
     // a ragged chunk would be right-padded by every strided conv in mid-stream (:127-133): not the same signal
     set_error("streaming encode takes whole hops: L=%lld is not a multiple of %d", (long long)L, d->hop);
