@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define VVDEC_ABI_VERSION 1
+#define VVDEC_ABI_VERSION 2
 #define VV_MAX_STAGES 8
 
 typedef enum vv_status {
@@ -99,6 +99,16 @@ int32_t vv_decoder_load_tensor(vv_decoder* dec, const char* name, const void* da
  * convs).  Fails with VV_ERR_NOT_FINALIZED and names the first missing tensor in vv_last_error(). */
 int32_t vv_decoder_finalize(vv_decoder* dec);
 int64_t vv_decoder_param_count(const vv_decoder* dec);
+/*
+ * Run-time options of one decoder (tests and A/B runs; the defaults are the product routing).  Keys:
+ *   "gemm_bn256"       0 = never use the 128x256 GEMM tile, 1 = automatic (default: when the launch has at least
+ *                      gemm_bn256_waves waves of wide tiles), 2 = whenever N % 256 == 0
+ *   "gemm_bn256_waves" threshold of the automatic mode, in waves of one tile per SM (default 2)
+ *   "gemm_bn64"        1 (default) = N = 64 layers on the persistent kernel's 64-wide tile, 0 = one-tile-per-CTA kernel
+ * Unknown keys / values out of range: VV_ERR_INVALID_ARG.  The environment variables VV_GEMM_BN256,
+ * VV_GEMM_BN256_WAVES, VV_GEMM_BN64 set the defaults a decoder is created with.
+ */
+int32_t vv_decoder_set_option(vv_decoder* dec, const char* key, int64_t value);
 /* samples produced per latent frame (prod(ratios) = 3200) and causal receptive field in frames (58) */
 int32_t vv_decoder_hop(const vv_decoder* dec);
 int32_t vv_decoder_halo_frames(const vv_decoder* dec);
@@ -152,6 +162,15 @@ int32_t vv_state_create(const vv_decoder* dec, int32_t n_slots, vv_state** out);
 int32_t vv_state_destroy(vv_state* st);
 int32_t vv_state_n_slots(const vv_state* st);
 int64_t vv_state_bytes_per_slot(const vv_state* st);
+/*
+ * Slot ids are consumed on the device (no host sync, unlike the reference's sample_indices.tolist(), :204,230,238), so a
+ * bad id cannot fail the call that carries it.  Kernels never index the state with an id outside [0, n_slots): such a row
+ * is decoded with a zero context and saves nothing, the id is recorded, and the NEXT vv_decode / vv_encode /
+ * vv_state_zero / vv_state_export on the state -- or vv_state_check, which does nothing else -- returns VV_ERR_SLOT once
+ * (the record is host-mapped memory: no synchronisation; to observe an error of a call still in flight, synchronise the
+ * stream first).
+ */
+int32_t vv_state_check(vv_state* st);
 /* set_to_zero(sample_indices) (:234-241): slot_ids is a device int32 [n] array; n<0 zeroes all. */
 int32_t vv_state_zero(vv_state* st, const int32_t* slot_ids, int32_t n, void* cuda_stream);
 /* checkpoint one slot to / from host memory (vv_state_bytes_per_slot bytes); synchronises. */
@@ -168,6 +187,7 @@ int32_t vv_encoder_destroy(vv_encoder* enc);
 int32_t vv_encoder_load_tensor(vv_encoder* enc, const char* name, const void* data, int32_t dtype,
                                const int64_t* shape, int32_t ndim, int32_t is_device);
 int32_t vv_encoder_finalize(vv_encoder* enc);
+int32_t vv_encoder_set_option(vv_encoder* enc, const char* key, int64_t value);   /* same keys as vv_decoder_set_option */
 int64_t vv_encoder_param_count(const vv_encoder* enc);
 int32_t vv_encoder_hop(const vv_encoder* enc);
 /* latent frames for L samples: ceil(L / hop) (each strided conv pads its input up to a whole stride, :127-133) */

@@ -433,7 +433,7 @@ block_fused_kernel(const __grid_constant__ CUtensorMap tmO, const __grid_constan
         const uint8_t* rd8;
         uint8_t* wr8;
         p.st.resolve(b, rd8, wr8);
-        srd = reinterpret_cast<const float*>(rd8) + c0;
+        srd = rd8 ? reinterpret_cast<const float*>(rd8) + c0 : nullptr;
       }
 #pragma unroll
       for (int i = 0; i < 7; ++i) {
@@ -503,7 +503,7 @@ block_fused_kernel(const __grid_constant__ CUtensorMap tmO, const __grid_constan
         uint8_t* wr8;
         p.st.resolve(b, rd8, wr8);
         st_rd = reinterpret_cast<const float*>(rd8);
-        st_wr = reinterpret_cast<float*>(wr8) + c0;
+        st_wr = wr8 ? reinterpret_cast<float*>(wr8) + c0 : nullptr;
       }
       uint8_t* ys = sY + sy * L::Y_BYTES;
       uint8_t* as = sA + sa * L::A_BYTES;

@@ -95,6 +95,7 @@ __global__ void __launch_bounds__(256) enc_stem_kernel(const EncStemArgs p) {
       const uint8_t* rd8;
       uint8_t* wr8;
       p.st.resolve(b, rd8, wr8);
+      if (wr8 == nullptr) continue;                    // slot id out of range: reported by state_flip_kernel
       const long long t = (long long)p.L - 6 + j;
       float v;
       if (t >= 0) {

@@ -30,9 +30,13 @@ struct StateRef {          // how a kernel finds a stream's cached context for o
   long long bank_bytes;    // distance between the two banks
   long long slot_bytes;    // distance between slots inside a bank
   long long layer_off;     // this layer's offset inside a slot
+  int n_slots;             // slot ids outside [0, n_slots) never touch the arena: the row decodes with a zero context,
+                           // saves nothing, and the pass's state_flip_kernel reports it (vv_state::err -> VV_ERR_SLOT)
   __device__ __forceinline__ void resolve(int b, const uint8_t*& rd, uint8_t*& wr) const {
-    if (base == nullptr) { rd = nullptr; wr = nullptr; return; }
+    rd = nullptr; wr = nullptr;
+    if (base == nullptr) return;
     const int slot = slot_ids[b];
+    if ((unsigned)slot >= (unsigned)n_slots) return;
     const int par = parity[slot] & 1;
     rd = base + (long long)par * bank_bytes + (long long)slot * slot_bytes + layer_off;
     wr = base + (long long)(par ^ 1) * bank_bytes + (long long)slot * slot_bytes + layer_off;

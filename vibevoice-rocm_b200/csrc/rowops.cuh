@@ -171,16 +171,25 @@ __global__ void __launch_bounds__(128) head_kernel(const HeadArgs p) {
 
 // ---- streaming-state bookkeeping -----------------------------------------------------------------------
 // After every stateful layer of a pass has written the inactive bank, the pass flips its slots' parity.
-__global__ void state_flip_kernel(const int* slot_ids, int n, int* parity) {
+// A slot id outside [0, n_slots) was treated as "no state" by every layer (StateRef::resolve); here it is reported
+// through the state's error word (host-mapped: the next vv_* call on the state returns VV_ERR_SLOT).
+__global__ void state_flip_kernel(const int* slot_ids, int n, int* parity, int n_slots, int* err) {
   pdl_launch();
   pdl_wait();
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n) parity[slot_ids[i]] ^= 1;
+  if (i >= n) return;
+  const int slot = slot_ids[i];
+  if ((unsigned)slot < (unsigned)n_slots) parity[slot] ^= 1;
+  else if (err != nullptr) *err = (slot < 0) ? slot : slot + 1;       // nonzero either way
 }
 // set_to_zero (reference :234-241): clear the CURRENT bank of the listed slots (n < 0: every slot).
 __global__ void state_zero_kernel(uint8_t* base, long long bank_bytes, long long slot_bytes, const int* slot_ids,
-                                  int n, const int* parity) {
+                                  int n, const int* parity, int n_slots, int* err) {
   const int slot = (slot_ids != nullptr) ? slot_ids[blockIdx.y] : blockIdx.y;
+  if ((unsigned)slot >= (unsigned)n_slots) {
+    if (err != nullptr && blockIdx.x == 0 && threadIdx.x == 0) *err = (slot < 0) ? slot : slot + 1;
+    return;
+  }
   uint4* p = reinterpret_cast<uint4*>(base + (long long)(parity[slot] & 1) * bank_bytes +
                                       (long long)slot * slot_bytes);
   const long long n16 = slot_bytes / 16;

@@ -47,6 +47,14 @@ static bool pdl_enabled() {
   if (mode == -2) { const char* ev = getenv("VV_PDL"); mode = ev ? (atoi(ev) != 0 ? 1 : 0) : -1; }
   return mode == 1 || (mode == -1 && g_pdl_small_stream);
 }
+static thread_local bool g_launch_failed = false;
+// after a launch_k: the launch's own return code first (cudaGetLastError can be cleared by an unrelated call), then the
+// sticky / asynchronous error state
+#define VV_LAUNCH_OK()                                                     \
+  do {                                                                     \
+    if (vv::g_launch_failed) { vv::g_launch_failed = false; (void)cudaGetLastError(); return VV_ERR_CUDA; } \
+    VV_CUDA(cudaGetLastError());                                           \
+  } while (0)
 template <typename... KArgs, typename... Args>
 static inline void launch_k(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, Args&&... args) {
   cudaLaunchConfig_t cfg;
@@ -60,7 +68,11 @@ static inline void launch_k(void (*kern)(KArgs...), dim3 grid, dim3 block, size_
   at[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = at;
   cfg.numAttrs = pdl_enabled() ? 1 : 0;
-  (void)cudaLaunchKernelEx(&cfg, kern, std::forward<Args>(args)...);   // a failure stays in cudaGetLastError()
+  const cudaError_t e = cudaLaunchKernelEx(&cfg, kern, std::forward<Args>(args)...);
+  if (e != cudaSuccess) {            // callers test g_launch_failed through VV_LAUNCH_OK() right after every launch
+    g_launch_failed = true;
+    set_error("kernel launch failed: %s", cudaGetErrorString(e));
+  }
 }
 
 // ---- TMA tensor maps (driver entry point fetched through the runtime: no link against libcuda) ---------
@@ -215,6 +227,9 @@ static int32_t init_core(const vv_config* cfg, vv_decoder* d) {
     return VV_ERR_NO_DEVICE;
   }
   d->cfg = *cfg;
+  if (const char* ev = getenv("VV_GEMM_BN256")) d->opt_bn256 = atoi(ev);            // defaults; vv_decoder_set_option overrides
+  if (const char* ev = getenv("VV_GEMM_BN256_WAVES")) d->opt_bn256_waves = atoi(ev);
+  if (const char* ev = getenv("VV_GEMM_BN64")) d->opt_bn64 = atoi(ev);
   d->hop = 1;
   for (int i = 0; i + 1 < cfg->n_stages; ++i) d->hop *= cfg->ratios[i];
   // causal receptive field in latent frames: sum of left taps / layer input rate
@@ -246,6 +261,16 @@ extern "C" int32_t vv_decoder_destroy(vv_decoder* d) {
   for (void* p : d->allocs) cudaFree(p);
   delete d;
   return VV_OK;
+}
+
+// run-time options (tests force kernel instantiations the automatic routing would only pick at benchmark sizes)
+extern "C" int32_t vv_decoder_set_option(vv_decoder* d, const char* key, int64_t value) {
+  if (!d || !key) { set_error("null argument"); return VV_ERR_INVALID_ARG; }
+  if (strcmp(key, "gemm_bn256") == 0 && value >= 0 && value <= 2) { d->opt_bn256 = (int)value; return VV_OK; }
+  if (strcmp(key, "gemm_bn256_waves") == 0 && value >= 0) { d->opt_bn256_waves = (int)value; return VV_OK; }
+  if (strcmp(key, "gemm_bn64") == 0 && value >= 0 && value <= 1) { d->opt_bn64 = (int)value; return VV_OK; }
+  set_error("unknown option '%s' or value %lld out of range", key, (long long)value);
+  return VV_ERR_INVALID_ARG;
 }
 
 extern "C" int64_t vv_decoder_param_count(const vv_decoder* d) { return d ? d->param_count : 0; }
@@ -506,6 +531,7 @@ StateRef make_state_ref(vv_state* st, const int32_t* slot_ids, long long layer_o
   r.bank_bytes = st ? st->bank_bytes : 0;
   r.slot_bytes = st ? st->slot_bytes : 0;
   r.layer_off = layer_off;
+  r.n_slots = st ? st->n_slots : 0;
   return r;
 }
 
@@ -555,11 +581,6 @@ int launch_gemm(vv_decoder* d, const __nv_bfloat16* A, long long a_rpb, int rows
   if (rc == VV_OK && kind != -2) d->mark(kind, stage, s);
   return rc;
 }
-static bool g2_narrow64() {   // VV_GEMM_BN64=0: N = 64 layers back on the one-tile-per-CTA kernel (A/B)
-  static int mode = -1;
-  if (mode < 0) { const char* ev = getenv("VV_GEMM_BN64"); mode = ev ? atoi(ev) : 1; }
-  return mode != 0;
-}
 int launch_gemm_impl(vv_decoder* d, const __nv_bfloat16* A, long long a_rpb, int rows, int nbatch, const DenseW& w,
                      const EpiOut& e, cudaStream_t s) {
   GemmArgs g;
@@ -587,7 +608,7 @@ int launch_gemm_impl(vv_decoder* d, const __nv_bfloat16* A, long long a_rpb, int
     r.A = A; r.a_rpb = a_rpb; r.W = w.w; r.Ktap = w.Ktap; r.g = g;
     const long long work = (long long)nbatch * rows * (w.N / 32);
     gemm_ref_kernel<<<(unsigned)((work + 127) / 128), 128, 0, s>>>(r);
-    VV_CUDA(cudaGetLastError());
+    VV_LAUNCH_OK();
     return VV_OK;
   }
   CUtensorMap tmA;
@@ -615,13 +636,11 @@ int launch_gemm_impl(vv_decoder* d, const __nv_bfloat16* A, long long a_rpb, int
     }
     if (rc != VV_OK) return rc;
     const int num_sms = d->num_sms;
-    // 256-wide MMA tiles when there are enough of them to keep the tail short (>= 2 waves)
-    static int bn256_mode = -1;                            // VV_GEMM_BN256: 0 never, 1 auto (default), 2 whenever N % 256 == 0
-    if (bn256_mode < 0) { const char* ev = getenv("VV_GEMM_BN256"); bn256_mode = ev ? atoi(ev) : 1; }
+    // 256-wide MMA tiles when there are enough of them to keep the tail short (>= 2 waves: measured on the C = 2048
+    // FFN); vv_decoder_set_option("gemm_bn256" / "gemm_bn256_waves") overrides (tests force every instantiation)
     const long long ntiles256 = best_tiles * (w.N / 256);
-    static int bn256_waves = -1;                           // VV_GEMM_BN256_WAVES: minimum waves of wide tiles (default 2: measured on the C = 2048 FFN)
-    if (bn256_waves < 0) { const char* ev = getenv("VV_GEMM_BN256_WAVES"); bn256_waves = ev ? atoi(ev) : 2; }
-    const bool wide = w.has_tm256 && bn256_mode > 0 && (bn256_mode == 2 || ntiles256 >= (long long)bn256_waves * num_sms);
+    const bool wide = w.has_tm256 && d->opt_bn256 > 0 &&
+                      (d->opt_bn256 == 2 || ntiles256 >= (long long)d->opt_bn256_waves * num_sms);
     const long long ntiles = wide ? ntiles256 : best_tiles * (w.N / w.BN);
     const unsigned grid2 = (unsigned)std::min<long long>(ntiles, num_sms);
     const bool deep = nk >= 32;   // K >= 2048: mainloop-dominated
@@ -641,10 +660,10 @@ int launch_gemm_impl(vv_decoder* d, const __nv_bfloat16* A, long long a_rpb, int
     else if (e.epi == EPI_GELU_BF16) { if (deep) VV_G2_LAUNCH(EPI_GELU_BF16, true); else VV_G2_LAUNCH(EPI_GELU_BF16, false); }
     else { if (deep) VV_G2_LAUNCH(EPI_RESID, true); else VV_G2_LAUNCH(EPI_RESID, false); }
 #undef VV_G2_LAUNCH
-    VV_CUDA(cudaGetLastError());
+    VV_LAUNCH_OK();
     return VV_OK;
   }
-  if (w.BN == 64 && w.BK == G2_BK && e.epi == EPI_BIAS_F32 && d->cfg.gemm_path == 0 && g2_narrow64()) {
+  if (w.BN == 64 && w.BK == G2_BK && e.epi == EPI_BIAS_F32 && d->cfg.gemm_path == 0 && d->opt_bn64 != 0) {
     // N = 64 layers (last upsampler, encoder's first strided conv and head) on the persistent kernel's 64-wide tile
     CUtensorMap tmO;
     const uint32_t bt = 1u << best_log2, bb = 128u >> best_log2;
@@ -663,7 +682,7 @@ int launch_gemm_impl(vv_decoder* d, const __nv_bfloat16* A, long long a_rpb, int
       if (rc != VV_OK) return rc;
       launch_k(gemm_tc2_kernel<EPI_BIAS_F32, false, 64>, dim3(grid2), dim3(G2Warps<EPI_BIAS_F32>::THREADS), Gemm2Cfg<EPI_BIAS_F32, false, 64>::TOTAL, s, tmA, w.tm, tmO, tmO, g);
     }
-    VV_CUDA(cudaGetLastError());
+    VV_LAUNCH_OK();
     return VV_OK;
   }
   const long long n_cta = best_tiles * (w.N / w.BN);
@@ -677,7 +696,7 @@ int launch_gemm_impl(vv_decoder* d, const __nv_bfloat16* A, long long a_rpb, int
   else if (w.BN == 32 && w.BK == 32) rc = launch_gemm_inst<32, 32>(tmA, w, g, grid, d->cfg.device, s);
   else { set_error("no GEMM instance for BN=%d BK=%d", w.BN, w.BK); return VV_ERR_UNSUPPORTED; }
   if (rc != VV_OK) return rc;
-  VV_CUDA(cudaGetLastError());
+  VV_LAUNCH_OK();
   return VV_OK;
 }
 
@@ -691,7 +710,7 @@ int launch_ffn_fused_inst(vv_decoder* d, const CUtensorMap& tmA, const CUtensorM
   const long long ntiles = (fa.R + 127) / 128;
   const unsigned grid = (unsigned)std::min<long long>(ntiles, num_sms);
   launch_k(ffn_fused_kernel<C>, dim3(grid), dim3(FF_THREADS), FfnFusedSmem<C>::TOTAL, s, tmA, tmR, tmO, bw.lin1.tm, bw.lin2.tm, fa);
-  VV_CUDA(cudaGetLastError());
+  VV_LAUNCH_OK();
   return VV_OK;
 }
 
@@ -732,7 +751,7 @@ int launch_ffn_fused(vv_decoder* d, int C, const BlockW& bw, const __nv_bfloat16
   const unsigned grid = (unsigned)std::min<long long>(ntiles, num_sms);
   if (R + 256LL * num_sms >= (1LL << 31)) { set_error("ffn_stream: %lld rows exceed the 31-bit row index", R); return VV_ERR_BAD_SHAPE; }
   launch_k(ffn_stream_kernel<128>, dim3(grid), dim3(FS_THREADS), FfnStreamCfg<128>::TOTAL, s, tmA, tmR, tmO, bw.tm_w1s, bw.lin2.tm, fa);
-  VV_CUDA(cudaGetLastError());
+  VV_LAUNCH_OK();
   return VV_OK;
 }
 
@@ -751,7 +770,7 @@ int launch_block_fused_inst(vv_decoder* d, const CUtensorMap& tmO, const BlockW&
   const long long ntiles = (long long)a.nbatch * a.tiles_pb;
   const unsigned grid = (unsigned)std::min<long long>(ntiles, num_sms);
   launch_k(block_fused_kernel<C, STATE>, dim3(grid), dim3(BlockFusedCfg<C>::THREADS), BlockFusedCfg<C>::TOTAL, s, tmO, bw.lin1.tm, bw.lin2.tm, a);
-  VV_CUDA(cudaGetLastError());
+  VV_LAUNCH_OK();
   return VV_OK;
 }
 
@@ -863,7 +882,7 @@ int launch_mixer(vv_decoder* d, const BlockW& bw, int C, const float* x, float* 
     default: set_error("no mixer kernel for C=%d", C); return VV_ERR_UNSUPPORTED;
   }
 #undef VV_MIXER_CASE
-  VV_CUDA(cudaGetLastError());
+  VV_LAUNCH_OK();
   return VV_OK;
 }
 
@@ -919,7 +938,7 @@ int run_pass(vv_decoder* d, const LatView& lat, int nb, int T, void* audio, int 
     const long long total = (long long)nb * (T + 6) * D;
     launch_k(prep_latents_kernel, dim3((unsigned)std::min<long long>((total + 255) / 256, 148 * 16)), dim3(256), 0, s, p);
     d->launches++;
-    VV_CUDA(cudaGetLastError());
+    VV_LAUNCH_OK();
     d->mark(VV_K_PREP, 0, s);
   }
   int rc;
@@ -950,7 +969,7 @@ int run_pass(vv_decoder* d, const LatView& lat, int nb, int T, void* audio, int 
       hp.st_ref = make_state_ref(st, slots, sw.up_state_off);
       launch_k(upsample_halo_kernel, dim3((unsigned)std::min((nb * pw.C + 255) / 256, 148 * 8)), dim3(256), 0, s, hp);
       d->launches++;
-      VV_CUDA(cudaGetLastError());
+      VV_LAUNCH_OK();
       d->mark(VV_K_HALO, i, s);
       EpiOut e;
       e.epi = EPI_BIAS_F32; e.out_f32 = X;
@@ -993,14 +1012,14 @@ int run_pass(vv_decoder* d, const LatView& lat, int nb, int T, void* audio, int 
       const long long groups = (long long)nb * hp.strips_per_batch;
       launch_k(head_kernel, dim3((unsigned)((groups * 8 + 127) / 128)), dim3(128), 0, s, hp);
       d->launches++;
-      VV_CUDA(cudaGetLastError());
+      VV_LAUNCH_OK();
       d->mark(VV_K_HEAD, i, s);
     }
   }
   if (st != nullptr) {
-    launch_k(state_flip_kernel, dim3((nb + 127) / 128), dim3(128), 0, s, slots, nb, st->parity);
+    launch_k(state_flip_kernel, dim3((nb + 127) / 128), dim3(128), 0, s, slots, nb, st->parity, st->n_slots, st->err_dev);
     d->launches++;
-    VV_CUDA(cudaGetLastError());
+    VV_LAUNCH_OK();
     d->mark(VV_K_STATE, 0, s);
   }
   return VV_OK;
@@ -1016,6 +1035,7 @@ extern "C" int64_t vv_decoder_workspace_bytes(const vv_decoder* d, int32_t B, in
   return pass_bytes(d, B, T);
 }
 
+static int32_t state_take_error(vv_state* st);
 static int32_t decode_impl(vv_decoder* d, const void* latents, int32_t lat_dtype, int32_t layout, int32_t B,
                              int32_t T, void* audio, int32_t out_dtype, void* workspace, int64_t workspace_bytes,
                              vv_state* state, const int32_t* slot_ids, void* cuda_stream) {
@@ -1029,6 +1049,7 @@ static int32_t decode_impl(vv_decoder* d, const void* latents, int32_t lat_dtype
   if (layout != VV_LAYOUT_BTD && layout != VV_LAYOUT_BDT) { set_error("layout %d", layout); return VV_ERR_INVALID_ARG; }
   if (state != nullptr && slot_ids == nullptr) { set_error("state given without slot_ids"); return VV_ERR_INVALID_ARG; }
   if (state != nullptr && state->dec != d) { set_error("state belongs to another decoder"); return VV_ERR_INVALID_ARG; }
+  if (state != nullptr) { const int32_t prev = state_take_error(state); if (prev != VV_OK) return prev; }
   if (((uintptr_t)workspace & 1023) != 0) { set_error("workspace must be 1 KB aligned"); return VV_ERR_INVALID_ARG; }
   VV_CUDA(cudaSetDevice(d->cfg.device));
   cudaStream_t s = reinterpret_cast<cudaStream_t>(cuda_stream);
@@ -1113,21 +1134,40 @@ extern "C" int32_t vv_decode(vv_decoder* d, const void* latents, int32_t lat_dty
 // =====================================================================================================
 // streaming state
 // =====================================================================================================
+// A slot id outside [0, n_slots) reached a kernel in an earlier call on this state: report it once (VV_ERR_SLOT).
+static int32_t state_take_error(vv_state* st) {
+  if (st == nullptr || st->err_host == nullptr) return VV_OK;
+  const int e = *reinterpret_cast<volatile int*>(st->err_host);
+  if (e == 0) return VV_OK;
+  *reinterpret_cast<volatile int*>(st->err_host) = 0;
+  set_error("an earlier call on this state used slot id %d, outside [0, %d): that row was decoded with a zero context "
+            "and its state was not saved (create the cache with more slots)", e < 0 ? e : e - 1, st->n_slots);
+  return VV_ERR_SLOT;
+}
+
 extern "C" int32_t vv_state_create(const vv_decoder* d, int32_t n_slots, vv_state** out) {
   if (!d || !out || n_slots < 1) { set_error("bad argument"); return VV_ERR_INVALID_ARG; }
   if (!d->finalized) { set_error("decoder not finalized"); return VV_ERR_NOT_FINALIZED; }
   VV_CUDA(cudaSetDevice(d->cfg.device));
   vv_state* st = new vv_state();
-  st->dec = d; st->n_slots = n_slots; st->slot_bytes = d->state_slot_bytes;
+  st->dec = d; st->n_slots = n_slots; st->slot_bytes = d->state_slot_bytes; st->device = d->cfg.device;
   st->bank_bytes = st->slot_bytes * n_slots;
   void* p = nullptr;
   cudaError_t e = cudaMalloc(&p, (size_t)(2 * st->bank_bytes));
   if (e == cudaSuccess) { st->base = (uint8_t*)p; e = cudaMalloc(&p, sizeof(int) * n_slots); }
   if (e == cudaSuccess) { st->parity = (int*)p; e = cudaMemset(st->base, 0, (size_t)(2 * st->bank_bytes)); }
   if (e == cudaSuccess) e = cudaMemset(st->parity, 0, sizeof(int) * n_slots);
+  if (e == cudaSuccess) e = cudaHostAlloc(&p, sizeof(int), cudaHostAllocMapped);
+  if (e == cudaSuccess) {
+    st->err_host = (int*)p;
+    *st->err_host = 0;
+    e = cudaHostGetDevicePointer(&p, st->err_host, 0);
+    if (e == cudaSuccess) st->err_dev = (int*)p;
+  }
   if (e != cudaSuccess) {
     set_error("state allocation failed: %s", cudaGetErrorString(e));
     cudaFree(st->base); cudaFree(st->parity);
+    if (st->err_host) cudaFreeHost(st->err_host);
     delete st;
     return VV_ERR_CUDA;
   }
@@ -1136,30 +1176,42 @@ extern "C" int32_t vv_state_create(const vv_decoder* d, int32_t n_slots, vv_stat
 }
 extern "C" int32_t vv_state_destroy(vv_state* st) {
   if (!st) return VV_OK;
+  cudaSetDevice(st->device);
   cudaFree(st->base);
   cudaFree(st->parity);
+  if (st->err_host) cudaFreeHost(st->err_host);
   delete st;
   return VV_OK;
 }
 extern "C" int32_t vv_state_n_slots(const vv_state* st) { return st ? st->n_slots : 0; }
 extern "C" int64_t vv_state_bytes_per_slot(const vv_state* st) { return st ? st->slot_bytes : 0; }
+extern "C" int32_t vv_state_check(vv_state* st) {
+  if (!st) { set_error("null state"); return VV_ERR_INVALID_ARG; }
+  return state_take_error(st);
+}
 
 extern "C" int32_t vv_state_zero(vv_state* st, const int32_t* slot_ids, int32_t n, void* cuda_stream) {
   if (!st) { set_error("null state"); return VV_ERR_INVALID_ARG; }
   if (n == 0) return VV_OK;
   if (n > 0 && !slot_ids) { set_error("slot_ids is null"); return VV_ERR_INVALID_ARG; }
+  const int32_t prev = state_take_error(st);
+  if (prev != VV_OK) return prev;
+  VV_CUDA(cudaSetDevice(st->device));
   cudaStream_t s = reinterpret_cast<cudaStream_t>(cuda_stream);
   const int ny = n < 0 ? st->n_slots : n;
   dim3 grid(8, (unsigned)ny);
   state_zero_kernel<<<grid, 256, 0, s>>>(st->base, st->bank_bytes, st->slot_bytes, n < 0 ? nullptr : slot_ids, ny,
-                                         st->parity);
+                                         st->parity, st->n_slots, st->err_dev);
   VV_CUDA(cudaGetLastError());
   return VV_OK;
 }
 
+// checkpoint helpers: select the state's device and wait for ITS work (all streams of that device: the caller does not
+// pass the stream the decode ran on), then locate the slot's current bank
 static int state_slot_ptr(const vv_state* st, int slot, uint8_t** p) {
   if (!st || slot < 0 || slot >= st->n_slots) { set_error("slot %d out of range", slot); return VV_ERR_SLOT; }
   int par = 0;
+  VV_CUDA(cudaSetDevice(st->device));
   VV_CUDA(cudaDeviceSynchronize());
   VV_CUDA(cudaMemcpy(&par, st->parity + slot, sizeof(int), cudaMemcpyDeviceToHost));
   *p = st->base + (long long)(par & 1) * st->bank_bytes + (long long)slot * st->slot_bytes;
@@ -1168,6 +1220,8 @@ static int state_slot_ptr(const vv_state* st, int slot, uint8_t** p) {
 extern "C" int32_t vv_state_export(const vv_state* st, int32_t slot, void* host_dst, int64_t bytes) {
   uint8_t* p;
   int rc = state_slot_ptr(st, slot, &p);
+  if (rc != VV_OK) return rc;
+  rc = state_take_error(const_cast<vv_state*>(st));
   if (rc != VV_OK) return rc;
   if (!host_dst || bytes != st->slot_bytes) { set_error("export needs %lld bytes", (long long)st->slot_bytes); return VV_ERR_INVALID_ARG; }
   VV_CUDA(cudaMemcpy(host_dst, p, (size_t)bytes, cudaMemcpyDeviceToHost));
@@ -1251,7 +1305,7 @@ extern "C" int32_t vv_kernel_upsample(vv_decoder* d, int32_t stage, void* xb, fl
   hp.st_ref = make_state_ref(nullptr, nullptr, 0);
   launch_k(upsample_halo_kernel, dim3((unsigned)std::min((B * hp.C + 255) / 256, 148 * 8)), dim3(256), 0, s, hp);
   d->launches++;
-  VV_CUDA(cudaGetLastError());
+  VV_LAUNCH_OK();
   EpiOut e;
   e.epi = EPI_BIAS_F32; e.out_f32 = y;
   return launch_gemm(d, reinterpret_cast<const __nv_bfloat16*>(xb), rows + 1, rows, B, sw.up, e, s);
@@ -1271,7 +1325,7 @@ extern "C" int32_t vv_kernel_head(vv_decoder* d, const float* x, void* out, int3
   const long long groups = (long long)B * hp.strips_per_batch;
   launch_k(head_kernel, dim3((unsigned)((groups * 8 + 127) / 128)), dim3(128), 0, reinterpret_cast<cudaStream_t>(cuda_stream), hp);
   d->launches++;
-  VV_CUDA(cudaGetLastError());
+  VV_LAUNCH_OK();
   return VV_OK;
 }
 
@@ -1283,7 +1337,7 @@ namespace { __global__ void gelu_test_kernel(const float* x, float* y, int n) {
 extern "C" int32_t vv_test_gelu(const float* x, float* y, int32_t n, void* cuda_stream) {
   if (!x || !y || n < 1) { set_error("bad argument"); return VV_ERR_INVALID_ARG; }
   gelu_test_kernel<<<(n + 255) / 256, 256, 0, reinterpret_cast<cudaStream_t>(cuda_stream)>>>(x, y, n);
-  VV_CUDA(cudaGetLastError());
+  VV_LAUNCH_OK();
   return VV_OK;
 }
 
@@ -1309,7 +1363,7 @@ extern "C" int32_t vv_pcm16(const void* wave, int32_t wave_dtype, int32_t B, int
     pcm16_peak_kernel<<<dim3((unsigned)chunks, (unsigned)B), PCM_THREADS, 0, s>>>(p);
     pcm16_convert_kernel<<<dim3((unsigned)chunks, (unsigned)B), PCM_THREADS, 0, s>>>(p);
   }
-  VV_CUDA(cudaGetLastError());
+  VV_LAUNCH_OK();
   return VV_OK;
 }
 

@@ -67,6 +67,10 @@ struct vv_decoder {
   std::vector<void*> allocs;
   int64_t param_count = 0;
   int64_t launches = 0;
+  // run-time options (vv_decoder_set_option); defaults come from the environment once, at create
+  int opt_bn256 = 1;                // gemm_tc2 tile width: 0 never 256, 1 auto (>= opt_bn256_waves waves of wide tiles), 2 whenever N % 256 == 0
+  int opt_bn256_waves = 2;
+  int opt_bn64 = 1;                 // N = 64 layers on the persistent kernel's 64-wide tile (0: one-tile-per-CTA kernel)
   // optional per-launch timing (vv_decoder_set_profiling): CUDA events recorded on the decode stream
   bool prof_on = false;
   struct ProfMark { cudaEvent_t ev; int kind; int stage; };
@@ -82,4 +86,10 @@ struct vv_state {
   long long slot_bytes = 0, bank_bytes = 0;
   uint8_t* base = nullptr;          // 2 banks
   int* parity = nullptr;            // [n_slots]
+  int device = 0;                   // the decoder's / encoder's device: every vv_state_* entry point selects it
+  // out-of-range slot ids: kernels never index the arena with them (StateRef::resolve) and state_flip / state_zero
+  // write the offending id here.  Host-mapped pinned word, so the NEXT call on this state can report VV_ERR_SLOT
+  // without synchronising the stream.
+  int* err_host = nullptr;
+  int* err_dev = nullptr;
 };

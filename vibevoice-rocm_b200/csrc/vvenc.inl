@@ -98,7 +98,7 @@ int enc_run_pass(vv_encoder* e, const void* audio, int audio_is_bf16, long long 
       const long long threads = ((long long)rows_pb + ENC_STEM_ROWS - 1) / ENC_STEM_ROWS * nb * 8;
       launch_k(enc_stem_kernel, dim3((unsigned)std::min<long long>((threads + 255) / 256, 148LL * 64)), dim3(256), 0, s, p);
       d->launches++;
-      VV_CUDA(cudaGetLastError());
+      VV_LAUNCH_OK();
       d->mark(VV_K_ENC_STEM, 0, s);
     } else {
       // strided conv from the previous stage's padded bf16 copy: 2 taps of K_tap = r * C/2 (encoder.cuh)
@@ -143,7 +143,7 @@ int enc_run_pass(vv_encoder* e, const void* audio, int audio_is_bf16, long long 
       const long long cells = (bo.xb_rpb - rows_pb) * nb * (C / 8);
       launch_k(enc_context_kernel, dim3((unsigned)std::max<long long>(1, std::min<long long>((cells + 255) / 256, 148LL * 16))), dim3(256), 0, s, cp);
       d->launches++;
-      VV_CUDA(cudaGetLastError());
+      VV_LAUNCH_OK();
       d->mark(VV_K_PAD, i, s);
     }
     if (i == S - 1) {   // self.norm is Identity (disable_last_norm, :767-770); head k7 -> mean [nb, T, vae_dim]
@@ -154,9 +154,9 @@ int enc_run_pass(vv_encoder* e, const void* audio, int audio_is_bf16, long long 
     }
   }
   if (st != nullptr) {
-    launch_k(state_flip_kernel, dim3((nb + 127) / 128), dim3(128), 0, s, slots, nb, st->parity);
+    launch_k(state_flip_kernel, dim3((nb + 127) / 128), dim3(128), 0, s, slots, nb, st->parity, st->n_slots, st->err_dev);
     d->launches++;
-    VV_CUDA(cudaGetLastError());
+    VV_LAUNCH_OK();
     d->mark(VV_K_STATE, 0, s);
   }
   return VV_OK;
@@ -271,6 +271,10 @@ extern "C" int32_t vv_encoder_finalize(vv_encoder* e) {
   return VV_OK;
 }
 
+extern "C" int32_t vv_encoder_set_option(vv_encoder* e, const char* key, int64_t value) {
+  if (!e) { set_error("null encoder"); return VV_ERR_INVALID_ARG; }
+  return vv_decoder_set_option(&e->core, key, value);
+}
 extern "C" int64_t vv_encoder_param_count(const vv_encoder* e) { return e ? e->core.param_count : 0; }
 extern "C" int32_t vv_encoder_hop(const vv_encoder* e) { return e ? e->core.hop : 0; }
 extern "C" int64_t vv_encoder_frames(const vv_encoder* e, int64_t L) {
@@ -310,6 +314,7 @@ extern "C" int32_t vv_encode(vv_encoder* e, const void* audio, int32_t audio_dty
   if (((uintptr_t)workspace & 1023) != 0) { set_error("workspace must be 1 KB aligned"); return VV_ERR_INVALID_ARG; }
   if (state != nullptr && slot_ids == nullptr) { set_error("state given without slot_ids"); return VV_ERR_INVALID_ARG; }
   if (state != nullptr && state->dec != d) { set_error("state belongs to another encoder / decoder"); return VV_ERR_INVALID_ARG; }
+  if (state != nullptr) { const int32_t prev = state_take_error(state); if (prev != VV_OK) return prev; }
   PdlScope pdl(state != nullptr && (long long)B * (L / d->hop) <= 2048);
   if (state != nullptr && L % d->hop != 0) {
     // a ragged chunk would be right-padded by every strided conv in mid-stream (:127-133): not the same signal
@@ -355,7 +360,7 @@ extern "C" int32_t vv_kernel_enc_stem(vv_encoder* e, const void* audio, int32_t 
   const long long threads = (L + ENC_STEM_ROWS - 1) / ENC_STEM_ROWS * B * 8;
   launch_k(enc_stem_kernel, dim3((unsigned)std::min<long long>((threads + 255) / 256, 148LL * 64)), dim3(256), 0, s, p);
   e->core.launches++;
-  VV_CUDA(cudaGetLastError());
+  VV_LAUNCH_OK();
   return VV_OK;
 }
 
@@ -377,7 +382,7 @@ extern "C" int32_t vv_kernel_downsample(vv_encoder* e, int32_t stage, void* xb, 
   const long long cells = (cp.rpb - rows) * B * (Cin / 8);
   launch_k(enc_context_kernel, dim3((unsigned)std::max<long long>(1, std::min<long long>((cells + 255) / 256, 148LL * 16))), dim3(256), 0, s, cp);
   d->launches++;
-  VV_CUDA(cudaGetLastError());
+  VV_LAUNCH_OK();
   EpiOut eo;
   eo.epi = EPI_BIAS_F32; eo.out_f32 = y;
   return launch_gemm(d, reinterpret_cast<const __nv_bfloat16*>(xb), rows_out + 1, rows_out, B, sw.up, eo, s);
@@ -396,7 +401,7 @@ extern "C" int32_t vv_kernel_enc_head(vv_encoder* e, void* xb, float* mean, int3
   const long long cells = 6LL * B * (C / 8);
   launch_k(enc_context_kernel, dim3((unsigned)std::max<long long>(1, std::min<long long>((cells + 255) / 256, 148LL * 16))), dim3(256), 0, s, cp);
   d->launches++;
-  VV_CUDA(cudaGetLastError());
+  VV_LAUNCH_OK();
   EpiOut eo;
   eo.epi = EPI_BIAS_F32; eo.out_f32 = mean;
   return launch_gemm(d, reinterpret_cast<const __nv_bfloat16*>(xb), rows + 6, rows, B, e->head, eo, s);

@@ -16,7 +16,7 @@ VV_MAX_STAGES = 8
 VV_F32, VV_BF16 = 0, 1
 VV_LAYOUT_BTD, VV_LAYOUT_BDT = 0, 1
 VV_OK = 0
-ABI_VERSION = 1
+ABI_VERSION = 2
 
 
 class VvConfig(C.Structure):
@@ -51,6 +51,9 @@ SIGNATURES = {
     "vv_decoder_load_tensor": (_I32, [_P, C.c_char_p, _P, _I32, C.POINTER(_I64), _I32, _I32]),
     "vv_decoder_finalize": (_I32, [_P]),
     "vv_decoder_param_count": (_I64, [_P]),
+    "vv_decoder_set_option": (_I32, [_P, C.c_char_p, _I64]),
+    "vv_encoder_set_option": (_I32, [_P, C.c_char_p, _I64]),
+    "vv_state_check": (_I32, [_P]),
     "vv_decoder_hop": (_I32, [_P]),
     "vv_decoder_halo_frames": (_I32, [_P]),
     "vv_decoder_workspace_bytes": (_I64, [_P, _I32, _I32]),
@@ -127,4 +130,6 @@ def check(status: int, what: str):
         err = VvError(status, what, detail)
         if status in (-1, -2, -3, -4):           # invalid arg / shape / dtype / unsupported
             raise ValueError(str(err))
+        if status == -7:                         # VV_ERR_SLOT: the reference's dict cache would raise KeyError/IndexError
+            raise IndexError(str(err))
         raise err

@@ -38,10 +38,10 @@ class Geometry:
     def stage_channels(self, i: int) -> int:
         return self.n_filters * (2 ** (len(self.depths) - 1 - i))
 
-    @classmethod
-    def from_config(cls, cfg) -> "Geometry":
-        """Accepts the reference's VibeVoiceAcousticTokenizerConfig; rejects every variant outside the path
-         with ValueError, like the reference's own constructors do (:649, :728)."""
+    @staticmethod
+    def _check_supported(cfg) -> None:
+        """Reject every config variant outside the path with ValueError, like the reference's own
+        constructors do (:649, :728).  A missing attribute means the reference default, which is the supported value."""
         def want(name, ok):
             v = getattr(cfg, name, ok[0])
             if v not in ok:
@@ -54,17 +54,38 @@ class Geometry:
         want("conv_bias", (True,))
         want("disable_last_norm", (True,))
         want("channels", (1,))
-        enc = cfg.encoder_depths
-        enc = [int(d) for d in enc.split("-")] if isinstance(enc, str) else list(enc)
+        # Block1D builds its norms affine whatever this says (:629-630), the encoder / decoder final norm is Identity
+        # (disable_last_norm): the flag has no effect on the path, but a config that sets it False announces weights
+        # without norm scales, which the packer would then miss -- reject early with the reason
+        want("layernorm_elementwise_affine", (True,))
+
+    @staticmethod
+    def _ints(v):
+        return [int(d) for d in v.split("-")] if isinstance(v, str) else [int(d) for d in v]
+
+    @classmethod
+    def from_config(cls, cfg) -> "Geometry":
+        """DECODER geometry from the reference's VibeVoiceAcousticTokenizerConfig (configuration_vibevoice.py:16-44),
+        the way VibeVoiceAcousticTokenizerModel.__init__ derives it (:1019-1045): decoder depths = the encoder's
+        reversed unless decoder_depths is given; ratios / n_filters from the decoder_* fields."""
+        cls._check_supported(cfg)
         dd = getattr(cfg, "decoder_depths", None)
-        if dd is not None and isinstance(dd, str):
-            depths = [int(d) for d in dd.split("-")]
-        else:
-            depths = list(reversed(enc))                                        # :1024-1028
+        depths = cls._ints(dd) if dd is not None else list(reversed(cls._ints(cfg.encoder_depths)))   # :1024-1028
         ratios = getattr(cfg, "decoder_ratios", None) or cfg.encoder_ratios
-        nf = getattr(cfg, "decoder_n_filters", None) or cfg.encoder_n_filters    # the semantic config has no decoder_*
+        nf = getattr(cfg, "decoder_n_filters", None) or cfg.encoder_n_filters
         return cls(vae_dim=int(cfg.vae_dim), n_filters=int(nf), ratios=tuple(int(r) for r in ratios),
                    depths=tuple(depths), kernel_size=7, eps=float(cfg.layernorm_eps))
+
+    @classmethod
+    def from_encoder_config(cls, cfg) -> "Geometry":
+        """ENCODER geometry (acoustic or semantic tokenizer config), from the encoder_* fields only (:1030-1037,
+        :1130-1150), expressed in the decoder order this struct uses: TokenizerEncoder reverses encoder_ratios (:701) and
+        walks encoder_depths as given (:702), so the mirror decoder has ratios = encoder_ratios and depths = reversed."""
+        cls._check_supported(cfg)
+        depths = list(reversed(cls._ints(cfg.encoder_depths)))
+        return cls(vae_dim=int(cfg.vae_dim), n_filters=int(cfg.encoder_n_filters),
+                   ratios=tuple(int(r) for r in cfg.encoder_ratios), depths=tuple(depths), kernel_size=7,
+                   eps=float(cfg.layernorm_eps))
 
 
 def _dtype_code(dt: torch.dtype) -> int:
@@ -109,12 +130,19 @@ class B200StreamingCache:
         clears the listed (or all) streams entirely, which is what every reference caller does."""
         if sample_indices is None:
             _capi.check(self._lib.vv_state_zero(self._h, None, -1,
-                                                C.c_void_p(torch.cuda.current_stream().cuda_stream)), "vv_state_zero")
+                                                C.c_void_p(torch.cuda.current_stream(self._dec.device).cuda_stream)),
+                        "vv_state_zero")
             self.seen.clear()
         else:
             self.set_to_zero(sample_indices)
             for i in self._dec._indices_list(sample_indices):
                 self.seen.discard(i)
+
+    def check(self) -> None:
+        """Raise IndexError if an earlier call used a sample index outside [0, n_slots) (indices given as CUDA tensors are
+        consumed on the device without a host sync, so the call that carried the bad index could not fail itself; that
+        row was decoded with a zero context and saved no state).  Synchronise first to cover calls still in flight."""
+        _capi.check(self._lib.vv_state_check(self._h), "vv_state_check")
 
     # -- checkpoint --------------------------------------------------------------------------------
     def export_state(self, sample_idx: int) -> bytes:
@@ -221,6 +249,10 @@ class B200AcousticDecoder:
     def take_launch_count(self) -> int:
         return int(self._lib.vv_decoder_take_launch_count(self._h))
 
+    def set_option(self, key: str, value: int) -> None:
+        """vv_decoder_set_option: "gemm_bn256" (0 never / 1 auto / 2 always), "gemm_bn256_waves", "gemm_bn64"."""
+        _capi.check(self._lib.vv_decoder_set_option(self._h, key.encode(), int(value)), f"vv_decoder_set_option({key})")
+
     # -- helpers -----------------------------------------------------------------------------------
     def _indices_list(self, sample_indices) -> Sequence[int]:
         if isinstance(sample_indices, torch.Tensor):
@@ -246,7 +278,7 @@ class B200AcousticDecoder:
     def new_cache(self, n_slots: Optional[int] = None) -> B200StreamingCache:
         return B200StreamingCache(self, n_slots or self.default_slots)
 
-    def _state_for(self, cache) -> B200StreamingCache:
+    def _state_for(self, cache, batch: int = 0) -> B200StreamingCache:
         """Accept our cache, or ANY object the caller uses as the reference cache (e.g. a genuine
         VibeVoiceTokenizerStreamingCache built at modeling_vibevoice_inference.py:386): the device state hangs
         off it and its set_to_zero / clear are forwarded, so generate() runs unmodified."""
@@ -254,7 +286,9 @@ class B200AcousticDecoder:
             return cache
         st = getattr(cache, "_b200_state", None)
         if st is None or st._dec is not self:
-            st = self.new_cache()
+            # generate() passes batch positions as sample_indices (:571), at most the generation batch; the first
+            # streaming call may carry only a subset of it, so keep the default as the floor
+            st = self.new_cache(max(self.default_slots, int(batch)))
             cache._b200_state = st
             for name in ("set_to_zero", "clear"):
                 orig = getattr(cache, name, None)
@@ -294,7 +328,7 @@ class B200AcousticDecoder:
         if use_cache and cache is not None:             # :317, :469
             if sample_indices is None:
                 raise AssertionError("sample_indices must be provided for streaming mode")       # :321
-            st = self._state_for(cache)
+            st = self._state_for(cache, B)
             slots = self._indices_tensor(sample_indices)
             if slots.numel() != B:
                 raise AssertionError("len(sample_indices) must match batch size")                 # :322-323

@@ -111,7 +111,7 @@ class B200AcousticEncoder:
         semantic = not hasattr(model, "fix_std")
         kw.setdefault("fix_std", None if semantic else getattr(model, "fix_std"))
         kw.setdefault("std_dist_type", "none" if semantic else getattr(model, "std_dist_type", "gaussian"))
-        enc = cls(Geometry.from_config(model.config), **kw)
+        enc = cls(Geometry.from_encoder_config(model.config), **kw)
         return enc.load_state_dict(model.state_dict())
 
     @property
@@ -137,6 +137,10 @@ class B200AcousticEncoder:
     def take_launch_count(self) -> int:
         return int(self._lib.vv_encoder_take_launch_count(self._h))
 
+    def set_option(self, key: str, value: int) -> None:
+        """vv_encoder_set_option (same keys as the decoder's)."""
+        _capi.check(self._lib.vv_encoder_set_option(self._h, key.encode(), int(value)), f"vv_encoder_set_option({key})")
+
     # -- streaming state ------------------------------------------------------------------------------
     def _indices_list(self, sample_indices):
         if isinstance(sample_indices, torch.Tensor):
@@ -151,7 +155,7 @@ class B200AcousticEncoder:
     def new_cache(self, n_slots: Optional[int] = None) -> B200StreamingCache:
         return B200StreamingCache(self, n_slots or self.default_slots)
 
-    def _state_for(self, cache) -> B200StreamingCache:
+    def _state_for(self, cache, batch: int = 0) -> B200StreamingCache:
         """Our cache, or any object the caller uses as the reference cache (a genuine VibeVoiceTokenizerStreamingCache):
         the encoder's device state hangs off it and its set_to_zero / clear are forwarded (same as the decoder)."""
         if isinstance(cache, B200StreamingCache):
@@ -160,7 +164,7 @@ class B200AcousticEncoder:
             return cache
         st = getattr(cache, "_b200_enc_state", None)
         if st is None or st._dec is not self:
-            st = self.new_cache()
+            st = self.new_cache(max(self.default_slots, int(batch)))
             cache._b200_enc_state = st
             for name in ("set_to_zero", "clear"):
                 orig = getattr(cache, name, None)
@@ -207,7 +211,7 @@ class B200AcousticEncoder:
         if use_cache and cache is not None:             # :317
             if sample_indices is None:
                 raise AssertionError("sample_indices must be provided for streaming mode")       # :321
-            st = self._state_for(cache)
+            st = self._state_for(cache, B)
             slots = self._indices_tensor(sample_indices)
             if slots.numel() != B:
                 raise AssertionError("len(sample_indices) must match batch size")                 # :322-323
