@@ -47,6 +47,29 @@ def test_offline_stress_T6_matches_reference(weight_cache, gemm_path):
     assert dec.param_count == 343_695_969
 
 
+@pytest.mark.parametrize("bn256", [0, 2])
+def test_offline_forced_tile_widths_match_reference(full_decoder, bn256):
+    """The whole path with the 128 x 256 GEMM tile forced everywhere it exists (what the K2 headline routes to at its
+    row counts: stem, every upsampler into stages 1-4, every FFN GEMM at C >= 256) and with it disabled."""
+    dec, _ = full_decoder
+    z, meta = load_golden("full_stress_T6")
+    lat = make_latents(meta["B"], meta["T"], FULL.vae_dim, meta["lseed"])
+    dec.set_option("gemm_bn256", bn256)
+    try:
+        y = dec.decode(torch.from_numpy(lat).cuda())
+    finally:
+        dec.set_option("gemm_bn256", 1)
+    print(bn256, _assert_parity(y.cpu().numpy(), z["audio"], f"bn256={bn256}"))
+    z2, meta2 = load_golden("full_stress_K1_T75")
+    lat2 = make_latents(meta2["B"], meta2["T"], FULL.vae_dim, meta2["lseed"])
+    dec.set_option("gemm_bn256", bn256)
+    try:
+        y2 = dec.decode(torch.from_numpy(lat2).cuda())
+    finally:
+        dec.set_option("gemm_bn256", 1)
+    print(bn256, _assert_parity(y2.cpu().numpy(), z2["audio"], f"K1 bn256={bn256}"))
+
+
 def test_offline_K1_T75_matches_reference(full_decoder):
     """BASELINE.json configs[0]: batch 1, 10 s (75 frames)."""
     dec, _ = full_decoder
