@@ -168,7 +168,8 @@ int64_t vv_state_bytes_per_slot(const vv_state* st);
  * is decoded with a zero context and saves nothing, the id is recorded, and the NEXT vv_decode / vv_encode /
  * vv_state_zero / vv_state_export on the state -- or vv_state_check, which does nothing else -- returns VV_ERR_SLOT once
  * (the record is host-mapped memory: no synchronisation; to observe an error of a call still in flight, synchronise the
- * stream first).
+ * stream first).  Slot id -1 is a PADDING ROW: decoded with a zero context, nothing saved, no error -- it lets a caller
+ * pad a step to a fixed row count (one CUDA graph per bucket of stream counts, vvdec.FrameStep).
  */
 int32_t vv_state_check(vv_state* st);
 /* set_to_zero(sample_indices) (:234-241): slot_ids is a device int32 [n] array; n<0 zeroes all. */
@@ -190,6 +191,9 @@ int32_t vv_encoder_finalize(vv_encoder* enc);
 int32_t vv_encoder_set_option(vv_encoder* enc, const char* key, int64_t value);   /* same keys as vv_decoder_set_option */
 int64_t vv_encoder_param_count(const vv_encoder* enc);
 int32_t vv_encoder_hop(const vv_encoder* enc);
+/* left context, in latent frames, that makes a time chunk starting on a hop boundary reproduce the monolithic encode
+ * (time-chunk sharding across GPUs, SURVEY.md 8e last row): 58 for the shipped geometry, like the decoder's */
+int32_t vv_encoder_halo_frames(const vv_encoder* enc);
 /* latent frames for L samples: ceil(L / hop) (each strided conv pads its input up to a whole stride, :127-133) */
 int64_t vv_encoder_frames(const vv_encoder* enc, int64_t L);
 int64_t vv_encoder_workspace_bytes(const vv_encoder* enc, int32_t B, int64_t L);

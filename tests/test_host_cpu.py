@@ -155,6 +155,59 @@ def test_two_rank_time_chunk_sharding_under_gloo(tmp_path):
     assert "SHARD_OK" in outs[0]
 
 
+WORKER_API = r'''
+import os, sys
+sys.path.insert(0, os.environ["VV_ROOT"]); sys.path.insert(0, os.path.join(os.environ["VV_ROOT"], "vibevoice-rocm_b200"))
+import numpy as np, torch, torch.distributed as dist
+import vvdec
+from oracle.geometry import TINY
+from oracle.vv_oracle import OracleDecoder, OracleEncoder
+from oracle.weights import make_weights, make_encoder_weights, make_latents, make_audio
+dist.init_process_group("gloo", rank=int(os.environ["RANK"]), world_size=int(os.environ["WORLD_SIZE"]))
+rank = dist.get_rank()
+H, hop, D = TINY.receptive_field_frames(), TINY.hop, TINY.vae_dim
+dec = OracleDecoder(make_weights(TINY, "stress", 5), TINY)      # stand-in decode function (CPU, gloo): the product's
+enc = OracleEncoder(make_encoder_weights(TINY, "stress", 6), TINY)   # plan + point-to-point gather are what is tested
+T = 3 * H + 11
+lat = torch.from_numpy(make_latents(2, T, D, 81))
+y = vvdec.decode_sharded(None, lat, min_chunk=H, decode_fn=lambda x: torch.from_numpy(dec.decode(x.numpy())), halo=H, hop=hop,
+                         device="cpu")
+L = (2 * H + 7) * hop + 123                                      # ragged tail: only the last chunk is right-padded
+audio = torch.from_numpy(make_audio(2, L, 82))
+m = vvdec.encode_sharded(None, audio, min_chunk=H, encode_fn=lambda a: torch.from_numpy(enc.encode(a.numpy())), halo=H, hop=hop,
+                         device="cpu", vae_dim=D)
+if rank == 0:
+    ref = dec.decode(lat.numpy())
+    assert y.shape == ref.shape, (y.shape, ref.shape)
+    err = float(np.abs(y.numpy() - ref).max() / np.abs(ref).max())
+    assert err < 1e-4, err
+    mref = enc.encode(audio.numpy())
+    assert m.shape == mref.shape, (m.shape, mref.shape)
+    merr = float(np.abs(m.numpy() - mref).max() / np.abs(mref).max())
+    assert merr < 1e-4, merr
+    from vvdec.sharded import plan_for
+    assert len({s.rank for s in plan_for([T, T], 2, H, H)}) == 2
+    print("API_OK", err, merr)
+else:
+    assert y is None and m is None
+dist.destroy_process_group()
+'''
+
+
+def test_decode_and_encode_sharded_api_under_gloo(tmp_path):
+    """vvdec.decode_sharded / encode_sharded (plan -> per-rank chunks with recomputed halo -> batched point-to-point
+    gather into the final tensor) with world_size 2 over gloo; the per-chunk function is the CPU oracle."""
+    script = tmp_path / "worker_api.py"
+    script.write_text(WORKER_API)
+    env = dict(os.environ, VV_ROOT=ROOT, MASTER_ADDR="127.0.0.1", MASTER_PORT="29519", WORLD_SIZE="2",
+               OMP_NUM_THREADS="2")
+    procs = [subprocess.Popen([sys.executable, str(script)], env=dict(env, RANK=str(r)), stdout=subprocess.PIPE,
+                              stderr=subprocess.STDOUT, text=True) for r in range(2)]
+    outs = [p.communicate(timeout=600)[0] for p in procs]
+    assert all(p.returncode == 0 for p in procs), outs
+    assert "API_OK" in outs[0]
+
+
 def test_encoder_output_distribution_semantics():
     """B200TokenizerEncoderOutput mirrors VibeVoiceTokenizerEncoderOutput (:954-1000): 'fix' adds std * N(0,1), 'gaussian'
     draws one std per batch item from N(0, (std/0.8)^2), anything else returns the mean; kl = mean^2; mode = mean."""

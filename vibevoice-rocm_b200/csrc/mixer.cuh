@@ -31,7 +31,8 @@ struct StateRef {          // how a kernel finds a stream's cached context for o
   long long slot_bytes;    // distance between slots inside a bank
   long long layer_off;     // this layer's offset inside a slot
   int n_slots;             // slot ids outside [0, n_slots) never touch the arena: the row decodes with a zero context,
-                           // saves nothing, and the pass's state_flip_kernel reports it (vv_state::err -> VV_ERR_SLOT)
+                           // saves nothing, and the pass's state_flip_kernel reports it (vv_state::err -> VV_ERR_SLOT);
+                           // id -1 is the documented "padding row" (same treatment, no report)
   __device__ __forceinline__ void resolve(int b, const uint8_t*& rd, uint8_t*& wr) const {
     rd = nullptr; wr = nullptr;
     if (base == nullptr) return;

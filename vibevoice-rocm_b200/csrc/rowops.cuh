@@ -180,14 +180,14 @@ __global__ void state_flip_kernel(const int* slot_ids, int n, int* parity, int n
   if (i >= n) return;
   const int slot = slot_ids[i];
   if ((unsigned)slot < (unsigned)n_slots) parity[slot] ^= 1;
-  else if (err != nullptr) *err = (slot < 0) ? slot : slot + 1;       // nonzero either way
+  else if (slot != -1 && err != nullptr) *err = (slot < 0) ? slot : slot + 1;   // nonzero either way; -1 = padding row
 }
 // set_to_zero (reference :234-241): clear the CURRENT bank of the listed slots (n < 0: every slot).
 __global__ void state_zero_kernel(uint8_t* base, long long bank_bytes, long long slot_bytes, const int* slot_ids,
                                   int n, const int* parity, int n_slots, int* err) {
   const int slot = (slot_ids != nullptr) ? slot_ids[blockIdx.y] : blockIdx.y;
   if ((unsigned)slot >= (unsigned)n_slots) {
-    if (err != nullptr && blockIdx.x == 0 && threadIdx.x == 0) *err = (slot < 0) ? slot : slot + 1;
+    if (slot != -1 && err != nullptr && blockIdx.x == 0 && threadIdx.x == 0) *err = (slot < 0) ? slot : slot + 1;
     return;
   }
   uint4* p = reinterpret_cast<uint4*>(base + (long long)(parity[slot] & 1) * bank_bytes +

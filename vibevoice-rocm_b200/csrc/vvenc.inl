@@ -277,6 +277,10 @@ extern "C" int32_t vv_encoder_set_option(vv_encoder* e, const char* key, int64_t
 }
 extern "C" int64_t vv_encoder_param_count(const vv_encoder* e) { return e ? e->core.param_count : 0; }
 extern "C" int32_t vv_encoder_hop(const vv_encoder* e) { return e ? e->core.hop : 0; }
+// Causal receptive field in latent frames beyond a frame's own hop of samples.  The encoder is the decoder's mirror: a
+// stride-1 k7 layer adds 6 rows of left context at its rate, a strided conv (k = 2r) adds r input rows = 1 output row,
+// which is term by term the sum init_core evaluates for the decoder (58 frames for the shipped geometry).
+extern "C" int32_t vv_encoder_halo_frames(const vv_encoder* e) { return e ? e->core.halo : 0; }
 extern "C" int64_t vv_encoder_frames(const vv_encoder* e, int64_t L) {
   if (!e || L < 1) return 0;
   long long rows[VV_MAX_STAGES];

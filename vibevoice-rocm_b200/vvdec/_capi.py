@@ -81,6 +81,7 @@ SIGNATURES = {
     "vv_encoder_finalize": (_I32, [_P]),
     "vv_encoder_param_count": (_I64, [_P]),
     "vv_encoder_hop": (_I32, [_P]),
+    "vv_encoder_halo_frames": (_I32, [_P]),
     "vv_encoder_frames": (_I64, [_P, _I64]),
     "vv_encoder_workspace_bytes": (_I64, [_P, _I32, _I64]),
     "vv_encoder_state_create": (_I32, [_P, _I32, C.POINTER(_P)]),

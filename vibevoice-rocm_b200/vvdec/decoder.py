@@ -301,8 +301,10 @@ class B200AcousticDecoder:
 
     # -- the reference entry point --------------------------------------------------------------------
     @torch.no_grad()
-    def decode(self, latents, cache=None, sample_indices=None, use_cache=False, debug=False):
+    def decode(self, latents, cache=None, sample_indices=None, use_cache=False, debug=False, *, workspace=None):
         """Same contract as VibeVoiceAcousticTokenizerModel.decode (:1099-1108).
+        ``workspace`` (keyword only, not in the reference): a caller-owned uint8 CUDA tensor used instead of the decoder's
+        own scratch -- a CUDA graph that captured this call keeps reading it on every replay (vvdec.FrameStep).
 
         latents: [B, T, vae_dim] or [B, vae_dim, T] (shape[1] == vae_dim means the latter, :1102-1105),
         float32 or bfloat16, on this decoder's device.  Returns audio [B, 1, T*hop] in the latents' dtype.
@@ -342,7 +344,7 @@ class B200AcousticDecoder:
                 st.seen.update(idx)
             state_h = st._h
         out = torch.empty((B, 1, T * self.hop), dtype=latents.dtype, device=self.device)
-        ws = self._workspace(B, T)
+        ws = workspace if workspace is not None else self._workspace(B, T)
         ws_ptr = (ws.data_ptr() + 1023) & ~1023
         ws_bytes = ws.numel() - (ws_ptr - ws.data_ptr())
         stream = torch.cuda.current_stream(self.device).cuda_stream

@@ -118,6 +118,10 @@ class B200AcousticEncoder:
     def param_count(self) -> int:
         return int(self._lib.vv_encoder_param_count(self._h))
 
+    @property
+    def halo_frames(self) -> int:
+        return int(self._lib.vv_encoder_halo_frames(self._h))
+
     def frames(self, L: int) -> int:
         return int(self._lib.vv_encoder_frames(self._h, int(L)))
 
@@ -184,8 +188,9 @@ class B200AcousticEncoder:
 
     # -- the reference entry points -------------------------------------------------------------------
     @torch.no_grad()
-    def encode(self, audio, cache=None, sample_indices=None, use_cache=False, debug=False):
+    def encode(self, audio, cache=None, sample_indices=None, use_cache=False, debug=False, *, workspace=None):
         """Same contract as VibeVoiceAcousticTokenizerModel.encode (:1081-1085).
+        ``workspace`` (keyword only): caller-owned uint8 CUDA scratch instead of the encoder's own (CUDA-graph capture).
 
         audio: [B, 1, L] (or [B, L]) float32 / bfloat16 on this encoder's device.  Returns
         B200TokenizerEncoderOutput(mean [B, ceil(L / hop), vae_dim] in the audio's dtype, std=fix_std).
@@ -227,7 +232,7 @@ class B200AcousticEncoder:
                 st.seen.update(idx)
             state_h = st._h
         mean = torch.empty((B, T, self.vae_dim), dtype=torch.float32, device=self.device)
-        ws = self._workspace(B, L)
+        ws = workspace if workspace is not None else self._workspace(B, L)
         ws_ptr = (ws.data_ptr() + 1023) & ~1023
         ws_bytes = ws.numel() - (ws_ptr - ws.data_ptr())
         stream = torch.cuda.current_stream(self.device).cuda_stream
