@@ -41,24 +41,39 @@ def peaks():
 
 
 # --------------------------------------------------------------------------------------------------
-# CPU arm: the oracle port, timed on the host cores (checker code used as the reported CPU baseline)
+# CPU arm: the reference's own CPU path = its ATen call sequence (oracle/torch_ref.py: F.conv1d / conv_transpose1d /
+# linear / gelu, fp32, pinned to the reference's outputs by tests/test_oracle_torch_ref.py), on all host threads.
+# /root/reference cannot travel to the GPU box, so the modules are restated call for call: kind = "port".
 # --------------------------------------------------------------------------------------------------
-def cpu_port_audio_s_per_s(sd, steps: int, warmup: int):
-    import numpy as np
+def workload_config(B, T):
+    return {"workload": f"acoustic decoder bf16, batch {B} x {T / FRAME_RATE:.0f} s ({T} latent frames) synthetic "
+                        f"latents per GPU, random-init (stress) weights",
+            "l2": "inputs >> L2 (each pass streams >700 MB of activations per utterance group)",
+            "sharding": "utterances per rank, no data-path collective"}
+
+
+def cpu_reference_audio_s_per_s(sd, steps: int, warmup: int):
+    """-> (audio-s/s, seconds per decode, threads used): configs[0] (batch 1 x 75 frames = 10 s) per step."""
+    import torch
+    from oracle import torch_ref
     from oracle.geometry import FULL
-    from oracle.vv_oracle import OracleDecoder
-    from oracle.weights import make_latents
-    dec = OracleDecoder({k: v.numpy() for k, v in sd.items()}, FULL)
-    lat = make_latents(CPU_SAMPLE_B, CPU_SAMPLE_T, FULL.vae_dim, 1)
+    threads = torch_ref.use_all_host_threads()
+    w = torch_ref.to_weights(sd)
+    gen = torch.Generator().manual_seed(1)
+    lat = torch.randn(CPU_SAMPLE_B, CPU_SAMPLE_T, FULL.vae_dim, generator=gen).to(torch.bfloat16).float()
     for _ in range(warmup):
-        dec.decode(lat)
+        torch_ref.decode(w, FULL, lat)
     ts = []
     for _ in range(steps):
         t0 = time.perf_counter()
-        dec.decode(lat)
+        torch_ref.decode(w, FULL, lat)
         ts.append(time.perf_counter() - t0)
     sec = sum(ts) / len(ts)
-    return CPU_SAMPLE_B * CPU_SAMPLE_T / FRAME_RATE / sec, sec
+    return CPU_SAMPLE_B * CPU_SAMPLE_T / FRAME_RATE / sec, sec, threads
+
+
+CPU_SAMPLE = (f"batch {CPU_SAMPLE_B} x {CPU_SAMPLE_T} frames (10 s = BASELINE.json configs[0]) per step; the reference's "
+              f"ATen call sequence (torch CPU fp32: conv1d / conv_transpose1d / linear / erf-GELU), all host threads")
 
 
 def run_reference_arm(args):
@@ -67,21 +82,49 @@ def run_reference_arm(args):
         return
     import torch
     from vvdec.synthetic import random_state_dict
-    torch.set_num_threads(os.cpu_count() or 1)
     sd = random_state_dict()
-    v, sec = cpu_port_audio_s_per_s(sd, max(1, args.steps), max(0, args.warmup))
-    sample = f"batch {CPU_SAMPLE_B} x {CPU_SAMPLE_T} frames (10 s) per step, numpy fp32 port of the reference path"
+    v, sec, threads = cpu_reference_audio_s_per_s(sd, max(1, args.steps), max(0, args.warmup))
     line = {
         "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"acoustic decoder, batch {K2_B} x 60 s ({K2_T} latent frames) per GPU; CPU arm "
-                               f"times a bounded sample: {sample}"},
-        "cpu_baseline": {"value": v, "unit": UNIT, "cores": os.cpu_count(), "kind": "port", "sample": sample},
+        "config": workload_config(args.batch, args.frames),
+        "cpu_baseline": {"value": v, "unit": UNIT, "cores": threads, "kind": "port", "sample": CPU_SAMPLE,
+                         "torch": torch.__version__},
         "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
     print(json.dumps(line), flush=True)
+
+
+# --------------------------------------------------------------------------------------------------
+# parity samples at the benchmark's own sizes: the CPU reference (oracle/torch_ref.py, fp32) on ONE utterance / row /
+# window of the tensors the timed legs just produced.  Tolerance = BASELINE.json: SNR >= 40 dB, max-abs <= 2e-2 of peak.
+# --------------------------------------------------------------------------------------------------
+def _metrics(test, ref):
+    import torch
+    t, r = test.double().flatten().cpu(), ref.double().flatten().cpu()
+    d = t - r
+    peak = float(r.abs().max()) or 1.0
+    den = float((d * d).sum())
+    snr = float("inf") if den == 0 else float(10 * torch.log10((r * r).sum().clamp_min(1e-300) / den))
+    return {"snr_db": snr, "rel_max": float(d.abs().max()) / peak}
+
+
+def _verdict(m):
+    m["ok"] = bool(m["snr_db"] >= 40.0 and m["rel_max"] <= 2e-2)
+    return m
+
+
+def parity_decode_sample(sd, geom, lat_cpu_f32, y_dev, what):
+    """lat_cpu_f32 [1, T, D] (the bf16-representable latents of one utterance), y_dev the path's output for it."""
+    from oracle import torch_ref
+    torch_ref.use_all_host_threads()
+    t0 = time.perf_counter()
+    ref = torch_ref.decode(torch_ref.to_weights(sd), geom, lat_cpu_f32)
+    m = _verdict(_metrics(y_dev.float().cpu(), ref))
+    m.update({"what": what, "cpu_seconds": time.perf_counter() - t0})
+    return m
 
 
 # --------------------------------------------------------------------------------------------------
@@ -160,7 +203,7 @@ def kernel_work(geom, kind: str, stage: int):
     return "hbm", 0, 0, 0
 
 
-def streaming_leg(dec, geom, dev, n_streams=256, steps=300, warmup=30):
+def streaming_leg(dec, geom, dev, sd, n_streams=256, steps=300, warmup=30):
     """BASELINE.json configs[3]: frame-by-frame decode of `n_streams` concurrent streams with the device-resident
     conv state; per-step latency from CUDA events, eager launches and one CUDA graph per step."""
     import torch
@@ -281,59 +324,126 @@ def streaming_leg(dec, geom, dev, n_streams=256, steps=300, warmup=30):
                         "d2h_bytes_per_step": int(chunk.numel() * 2)}
     except Exception as e:
         out["pcm16"] = {"error": f"{type(e).__name__}: {e}"[:200]}
+    # SURVEY 8d K4 schedule through the product's frame step: random active subsets, set_to_zero events
+    try:
+        out["schedule"] = streaming_schedule_leg(dec, geom, dev, sd, n_streams=n_streams)
+    except Exception as e:
+        out["schedule"] = {"error": f"{type(e).__name__}: {e}"[:300]}
     return out
 
 
-def torch_eager_leg(sd, geom, dev, dec, B=8, T=450, steps=3):
-    """Context number, not an arm: the same decode written with stock PyTorch ops (cuDNN depthwise / transposed conv,
-    cuBLAS linear, F.gelu — the calls the reference module makes, modular_vibevoice_tokenizer.py:914-951) in bf16 eager on
-    the same GPU and weights, on a bounded sample.  Lives in bench.py only; the product path never uses it."""
+def streaming_schedule_leg(dec, geom, dev, sd, n_streams=256, steps=320, p_active=0.8, zero_every=300, track=(3, 200)):
+    """SURVEY 8d's K4 schedule: every step a random subset of the streams (p = 0.8) decodes one frame, every stream ends a
+    speech segment (set_to_zero on both caches) about once per `zero_every` steps -- driven through vvdec.FrameStep
+    (decode -> semantic streaming encode -> PCM16 as one CUDA graph per stream-count bucket, indices on the device, no
+    host sync inside the loop).  Per-step device time from CUDA events read after the loop.  Two tracked streams are then
+    checked against the CPU reference: their longest segment's chunks (streaming) vs the reference's OFFLINE decode of the
+    same latents (the reference's streaming form equals its offline form), and the semantic means vs the
+    reference's encode of the audio that was handed over."""
+    import numpy as np
     import torch
-    import torch.nn.functional as F
-    w = {k: v.to(dev, torch.bfloat16) for k, v in sd.items()}
-    n = len(geom.depths)
+    import vvdec
+    from vvdec.synthetic import random_encoder_state_dict
+    sgeom = vvdec.Geometry(vae_dim=128)
+    senc = vvdec.B200AcousticEncoder(sgeom, device=dev.index, fix_std=None, std_dist_type="none")
+    sd_sem = random_encoder_state_dict(sgeom, seed=77)
+    senc.load_state_dict(sd_sem)
+    fs = vvdec.FrameStep(dec, senc, pcm=True, n_slots=n_streams, bucket=32)
+    rng = np.random.Generator(np.random.Philox(key=[4, 4]))
+    gen = torch.Generator().manual_seed(4)
+    lat_all = torch.randn(steps, n_streams, 1, geom.vae_dim, generator=gen).to(torch.bfloat16)
+    lat_dev = lat_all.to(dev)
+    act = [np.nonzero(rng.random(n_streams) < p_active)[0] for _ in range(steps)]
+    zero = [np.nonzero(rng.random(n_streams) < 1.0 / zero_every)[0] for _ in range(steps)]
+    idx_dev = [torch.from_numpy(a.astype(np.int64)).to(dev) for a in act]
+    zero_dev = [torch.from_numpy(z.astype(np.int64)).to(dev) if z.size else None for z in zero]
+    for nb in sorted({-(-len(a) // 32) * 32 for a in act}):         # build every bucket's graph before timing
+        fs(lat_dev[0, :nb], torch.arange(nb, device=dev))
+    fs.set_to_zero(torch.arange(n_streams, device=dev))
+    torch.cuda.synchronize()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+    seg = {k: {"lat": [], "audio": [], "sem": []} for k in track}
+    best = {k: None for k in track}
 
-    def rms(x, wt):                                   # ConvRMSNorm :77-91 (fp32 statistics, cast, then * weight)
-        xt = x.transpose(1, 2)
-        xf = xt.float()
-        xn = (xf * torch.rsqrt(xf.pow(2).mean(-1, keepdim=True) + geom.eps)).to(x.dtype) * wt
-        return xn.transpose(1, 2)
+    def close(k):
+        if best[k] is None or len(seg[k]["lat"]) > len(best[k]["lat"]):
+            best[k] = seg[k]
+        seg[k] = {"lat": [], "audio": [], "sem": []}
+    torch.cuda.set_sync_debug_mode("error")                         # a host synchronisation inside the loop raises
+    try:
+        t_wall = time.perf_counter()
+        for t in range(steps):
+            ev[t][0].record()
+            o = fs(lat_dev[t].index_select(0, idx_dev[t]), idx_dev[t])
+            ev[t][1].record()
+            for k in track:
+                pos = np.nonzero(act[t] == k)[0]
+                if pos.size:
+                    seg[k]["lat"].append(lat_all[t, k]); seg[k]["audio"].append(o.audio[int(pos[0])]); seg[k]["sem"].append(o.semantic[int(pos[0])])
+            if zero_dev[t] is not None:
+                fs.set_to_zero(zero_dev[t])
+                for k in track:
+                    if k in zero[t]:
+                        close(k)
+    finally:
+        torch.cuda.set_sync_debug_mode("default")
+    torch.cuda.synchronize()
+    wall_ms = (time.perf_counter() - t_wall) * 1e3 / steps
+    fs.check()
+    for k in track:
+        close(k)
+    ts = sorted(a.elapsed_time(b) for a, b in ev)
+    res = {"what": f"{steps} steps, {n_streams} streams, each active with p = {p_active} per step, a set_to_zero per stream "
+                   f"about every {zero_every} steps; vvdec.FrameStep = decode + semantic encode + PCM16 in one CUDA graph",
+           "active_mean": float(np.mean([len(a) for a in act])), "zero_events": int(sum(z.size for z in zero)),
+           "step_p50_ms": ts[len(ts) // 2], "step_p99_ms": ts[min(len(ts) - 1, int(len(ts) * 0.99))],
+           "host_wall_ms_per_step": wall_ms, "graphs": len(fs._plans), "graph_launches": fs.graph_launches}
+    # parity of the tracked streams (CPU reference, fp32)
+    from oracle import torch_ref
+    torch_ref.use_all_host_threads()
+    wd, ws = torch_ref.to_weights(sd), torch_ref.to_weights(sd_sem)
+    checks = []
+    for k in track:
+        b = best[k]
+        n = min(len(b["lat"]), 40)
+        if n < 4:
+            continue
+        lat = torch.stack(b["lat"][:n], 0).reshape(1, n, geom.vae_dim).float()
+        audio = torch.cat([a.reshape(-1) for a in b["audio"][:n]]).float().cpu()
+        sem = torch.cat([x.reshape(1, -1) for x in b["sem"][:n]], 0).float().cpu()
+        t0 = time.perf_counter()
+        ref_a = torch_ref.decode(wd, geom, lat).reshape(-1)
+        ref_s = torch_ref.encode(ws, sgeom, audio.reshape(1, 1, -1))[0]
+        m = {"stream": int(k), "frames": n, "decode": _verdict(_metrics(audio, ref_a)), "semantic": _verdict(_metrics(sem, ref_s)),
+             "cpu_seconds": time.perf_counter() - t0}
+        checks.append(m)
+    res["parity"] = checks
+    res["parity_ok"] = bool(checks) and all(c["decode"]["ok"] and c["semantic"]["ok"] for c in checks)
+    del senc, fs
+    return res
 
-    def decode(lat):                                  # [B, T, D] -> [B, 1, T*hop]
-        x = lat.transpose(1, 2)
-        x = F.conv1d(F.pad(x, (6, 0)), w["decoder.upsample_layers.0.0.conv.conv.weight"], w["decoder.upsample_layers.0.0.conv.conv.bias"])
-        for i in range(n):
-            if i > 0:
-                r = geom.ratios[i - 1]
-                p = f"decoder.upsample_layers.{i}.0.convtr.convtr."
-                y = F.conv_transpose1d(x, w[p + "weight"], w[p + "bias"], stride=r)
-                x = y[..., :y.shape[-1] - r]          # causal trim of k - r samples on the right (:563-571)
-            C = x.shape[1]
-            for j in range(geom.depths[i]):
-                p = f"decoder.stages.{i}.{j}."
-                h = rms(x, w[p + "norm.weight"])
-                h = F.conv1d(F.pad(h, (6, 0)), w[p + "mixer.conv.conv.conv.weight"], w[p + "mixer.conv.conv.conv.bias"], groups=C)
-                x = x + h * w[p + "gamma"][None, :, None]
-                h = rms(x, w[p + "ffn_norm.weight"]).transpose(1, 2)
-                h = F.linear(F.gelu(F.linear(h, w[p + "ffn.linear1.weight"], w[p + "ffn.linear1.bias"])),
-                             w[p + "ffn.linear2.weight"], w[p + "ffn.linear2.bias"]).transpose(1, 2)
-                x = x + h * w[p + "ffn_gamma"][None, :, None]
-        return F.conv1d(F.pad(x, (6, 0)), w["decoder.head.conv.conv.weight"], w["decoder.head.conv.conv.bias"])
 
+def torch_eager_leg(sd, geom, dev, dec, B=8, T=450, steps=3):
+    """Context number, not an arm: the reference's call sequence (oracle/torch_ref.py: the ATen calls the reference module
+    makes -- cuDNN depthwise / transposed conv, cuBLAS linear, F.gelu) in bf16 eager on the same GPU and weights, on a
+    bounded sample.  Lives in bench.py only; the product path never uses it."""
+    import torch
+    from oracle import torch_ref
+    w = torch_ref.to_weights(sd, dev, torch.bfloat16)
     gen = torch.Generator().manual_seed(9)
     lat = torch.randn(B, T, geom.vae_dim, generator=gen).to(torch.bfloat16).to(dev)
     with torch.no_grad():
-        y = decode(lat[:1, :8])                       # agreement check on a small piece (both bf16 paths vs each other)
+        y = torch_ref.decode(w, geom, lat[:1, :8])    # agreement check on a small piece (both bf16 paths vs each other)
         ours = dec.decode(lat[:1, :8])
         err = (y.float() - ours.float())
         snr = float(10 * torch.log10(ours.float().pow(2).sum() / err.pow(2).sum().clamp_min(1e-30)))
         del y, ours, err
-        decode(lat)                                   # warm-up (cuDNN heuristics, allocator)
+        torch_ref.decode(w, geom, lat)                # warm-up (cuDNN heuristics, allocator)
         torch.cuda.synchronize()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         for _ in range(steps):
-            decode(lat)
+            torch_ref.decode(w, geom, lat)
         e1.record()
         torch.cuda.synchronize()
     ms = e0.elapsed_time(e1) / steps
@@ -344,70 +454,89 @@ def torch_eager_leg(sd, geom, dev, dec, B=8, T=450, steps=3):
             "snr_vs_b200_path_db": snr, "torch": torch.__version__}
 
 
-def longform_leg(dec, geom, dev, world, rank, dist, steps, frames=40_500):
-    """BASELINE.json configs[2]: one 90-minute utterance (40,500 latent frames) split into time chunks across the ranks,
-    each rank recomputing its causal halo (58 frames); no collective on the data path, one NCCL gather of the finished
-    waveform slices to rank 0 at the end (strong scaling: the utterance is fixed, N varies).  All ranks call this."""
+def longform_leg(dec, geom, dev, world, rank, dist, steps, sd=None, frames=40_500, parity=True):
+    """BASELINE.json configs[2]: one 90-minute utterance (40,500 latent frames) through vvdec.decode_sharded -- time chunks
+    across the ranks, each rank recomputing its causal halo (58 frames), no collective on the data path, one batched
+    point-to-point gather of the finished waveform slices into rank 0's tensor (strong scaling: the utterance is fixed,
+    N varies).  All ranks call this.  Rank 0 then checks sampled windows of the gathered waveform against the CPU
+    reference (one window straddles a shard boundary when there is one) and, at N > 1, times the same utterance on its
+    GPU alone so that the line carries the strong-scaling speed-up measured in one run."""
     import torch
-    from vvdec.shard import plan_shards
+    import vvdec
+    from vvdec.sharded import plan_for
     halo, hop, D = dec.halo_frames, geom.hop, geom.vae_dim
-    shards = plan_shards([frames], world, halo)
-    mine = sorted((s for s in shards if s.rank == rank), key=lambda s: s.start)
     gen = torch.Generator().manual_seed(3)
     lat_all = torch.randn(1, frames, D, generator=gen)
     seg = frames // 4
     for k, mu in enumerate((-0.5, 0.0, 0.5, 1.0)):                    # four "speakers": four segments, shifted means
         lat_all[:, k * seg:(k + 1) * seg if k < 3 else frames] += mu
-    lats = [lat_all[:, s.start - s.halo:s.end].to(torch.bfloat16).to(dev) for s in mine]
-    owned = sum(s.frames for s in mine)
-    per_rank = [sum(s.frames for s in shards if s.rank == r) for r in range(world)]
-    cap = max(per_rank) * hop
-    buf = torch.zeros(cap, dtype=torch.bfloat16, device=dev)
-    gl = [torch.empty(cap, dtype=torch.bfloat16, device=dev) for _ in range(world)] if (rank == 0 and world > 1) else None
-    final = torch.empty(frames * hop, dtype=torch.bfloat16, device=dev) if rank == 0 else None
-
-    def step():
-        off = 0
-        for s, x in zip(mine, lats):
-            y = dec.decode(x)                                         # [1, 1, (halo + owned) * hop]
-            n = s.frames * hop
-            buf[off:off + n].copy_(y.view(-1)[s.halo * hop:])
-            off += n
-
-    def gather():
-        if world > 1:
-            dist.gather(buf, gl, dst=0)
-        if rank == 0:
-            offs = [0] * world
-            for s in sorted(shards, key=lambda s: (s.rank, s.start)):
-                src = gl[s.rank] if world > 1 else buf
-                n = s.frames * hop
-                final[s.start * hop:s.start * hop + n].copy_(src[offs[s.rank]:offs[s.rank] + n])
-                offs[s.rank] += n
+    lat_all = lat_all.to(torch.bfloat16)
+    lat_dev = lat_all.to(dev)
+    shards = plan_for([frames], world, halo)
 
     def sync():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
-    step(); gather(); sync()
-    e0, e1, e2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+
+    final = vvdec.decode_sharded(dec, lat_dev, shards=shards)
+    sync()
     t_dec = t_all = 0.0
     for _ in range(steps):
         sync()
-        e0.record(); step(); e1.record(); gather(); e2.record()
+        tm = {}
+        e0 = torch.cuda.Event(enable_timing=True)
+        e0.record()
+        final = vvdec.decode_sharded(dec, lat_dev, shards=shards, timings=tm)
         sync()
-        t_dec += e0.elapsed_time(e1); t_all += e0.elapsed_time(e2)
+        t_dec += e0.elapsed_time(tm["decode_done"]); t_all += e0.elapsed_time(tm["gather_done"])
     t = torch.tensor([t_dec / steps, t_all / steps], device=dev, dtype=torch.float64)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms_dec, ms_all = float(t[0]), float(t[1])
-    ok = bool(torch.isfinite(final.float()).all()) if rank == 0 else True
-    return {"workload": f"one {frames / FRAME_RATE / 60:.0f}-minute utterance ({frames} frames), time-chunk shards with a "
-                        f"{halo}-frame recomputed halo, waveform gathered to rank 0",
-            "scaling": "strong", "n_gpus": world, "shards": len(shards), "halo_frames": halo,
-            "frames_owned_rank0": owned, "recomputed_halo_frames_total": sum(s.halo for s in shards),
-            "ms_decode": ms_dec, "ms_decode_plus_gather": ms_all, "gather_bytes": (frames * hop * 2 if world > 1 else 0),
-            "value": frames / FRAME_RATE / (ms_all / 1e3), "unit": UNIT, "finite": ok}
+    out = {"workload": f"one {frames / FRAME_RATE / 60:.0f}-minute utterance ({frames} frames) through vvdec.decode_sharded: "
+                       f"time-chunk shards with a {halo}-frame recomputed halo, waveform slices sent point-to-point into "
+                       f"rank 0's tensor",
+           "scaling": "strong", "n_gpus": world, "shards": len(shards), "halo_frames": halo,
+           "frames_owned_rank0": sum(s.frames for s in shards if s.rank == 0),
+           "recomputed_halo_frames_total": sum(s.halo for s in shards),
+           "ms_decode": ms_dec, "ms_decode_plus_gather": ms_all, "ms_gather": ms_all - ms_dec,
+           "gather_bytes": (sum(s.frames for s in shards if s.rank != 0) * hop * 2 if world > 1 else 0),
+           "value": frames / FRAME_RATE / (ms_all / 1e3), "unit": UNIT}
+    if rank != 0:
+        return out
+    out["finite"] = bool(torch.isfinite(final.float()).all())
+    if world > 1:                                                     # the same utterance on rank 0's GPU alone
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        solo = dec.decode(lat_dev)
+        torch.cuda.synchronize()
+        e0.record()
+        solo = dec.decode(lat_dev)
+        e1.record()
+        torch.cuda.synchronize()
+        ms1 = e0.elapsed_time(e1)
+        out["single_gpu_ms_same_run"] = ms1
+        out["speedup_vs_single_gpu"] = ms1 / ms_all
+        out["gathered_vs_single_gpu"] = _metrics(final, solo)          # halo recompute vs one causal pass: rounding only
+        del solo
+    if parity and sd is not None:
+        bounds = sorted(s.start for s in shards if s.start > 0)
+        wins = [(0, 8), ((bounds[len(bounds) // 2] - 4) if bounds else frames // 2, 8), (frames - 8, 8)]
+        from oracle import torch_ref
+        torch_ref.use_all_host_threads()
+        wts = torch_ref.to_weights(sd)
+        res = []
+        for w0, n in wins:
+            lo = max(0, w0 - halo)
+            t0 = time.perf_counter()
+            ref = torch_ref.decode(wts, geom, lat_all[:, lo:w0 + n].float())[:, :, (w0 - lo) * hop:]
+            m = _verdict(_metrics(final[:, :, w0 * hop:(w0 + n) * hop].float().cpu(), ref))
+            m.update({"frames": [w0, w0 + n], "straddles_shard_boundary": any(w0 < b < w0 + n for b in bounds),
+                      "cpu_seconds": time.perf_counter() - t0})
+            res.append(m)
+        out["parity_windows"] = res
+        out["parity_ok"] = all(m["ok"] for m in res)
+    return out
 
 
 def enc_kernel_work(geom, kind: str, stage: int):
@@ -502,22 +631,27 @@ def encoder_leg(geom, dev, pk, steps, warmup, B=32, L=720_000, kernels_out="", c
     if kernels_out:
         with open(kernels_out, "w") as f:
             json.dump({"config": {"B": B, "L": L, "ms_per_step": ms}, "kernels": table}, f, indent=1)
+    row = 11 % B                                               # one K5 row kept for the parity sample below
+    mean_row = enc.encode(audio).mean[row:row + 1].float().cpu()
     del enc
-    cpu = None
+    cpu, parity = None, None
     if cpu_baseline:
-        # reported CPU figure for the encoder: the numpy port on a bounded sample (batch 1 x 2 s), all host threads
-        from oracle.geometry import FULL
-        from oracle.vv_oracle import OracleEncoder
-        from oracle.weights import make_audio
-        oe = OracleEncoder({k: v.numpy() for k, v in sd_cpu.items()}, FULL)
-        a = make_audio(1, 48_000, 5)
-        oe.encode(a[:, :, :6400])
+        # the reference's ATen call sequence (oracle/torch_ref.py, fp32, all host threads) on ONE row of this batch: the
+        # reported CPU figure for the encoder AND the K5-sized parity sample (tolerance as for the decoder)
+        from oracle import torch_ref
+        threads = torch_ref.use_all_host_threads()
+        wts = torch_ref.to_weights(sd_cpu)
+        a_row = a_host[row:row + 1].float()
+        torch_ref.encode(wts, geom, a_row[:, :, :32_000])
         t0 = time.perf_counter()
-        oe.encode(a)
+        ref = torch_ref.encode(wts, geom, a_row)
         sec = time.perf_counter() - t0
-        cpu = {"value": 2.0 / sec, "unit": "encoded audio-s/s", "cores": os.cpu_count(), "kind": "port",
-               "sample": f"batch 1 x 2 s (48000 samples), numpy fp32 port, {sec:.2f} s"}
-    return {"cpu_baseline": cpu,
+        cpu = {"value": (L / 24000.0) / sec, "unit": "encoded audio-s/s", "cores": threads, "kind": "port",
+               "sample": f"batch 1 x {L / 24000:.0f} s ({L} samples = one row of this batch), the reference's ATen call "
+                         f"sequence in fp32, {sec:.2f} s"}
+        parity = _verdict(_metrics(mean_row, ref))
+        parity["what"] = f"row {row} of the batch ({L} samples -> {T} frames) vs the CPU reference"
+    return {"cpu_baseline": cpu, "parity": parity,
             "workload": f"acoustic tokenizer encoder, batch {B} x {L / 24000:.0f} s ({L} samples -> {T} frames), bf16 audio in",
             "value": audio_s / (ms / 1e3), "unit": "encoded audio-s/s", "ms_per_step": ms, "gpu_launches": int(launches),
             "e2e": {"value": audio_s / (ms_e2e / 1e3), "ms_per_step": ms_e2e, "h2d_bytes_per_step": a_host.numel() * 2,
@@ -625,7 +759,8 @@ def main():
     if not args.no_longform:
         y = None
         try:
-            longform = longform_leg(dec, geom, dev, world, rank, dist, max(2, args.steps // 2))
+            longform = longform_leg(dec, geom, dev, world, rank, dist, max(2, min(5, args.steps // 2)), sd=sd,
+                                    parity=not args.no_cpu_baseline)
         except Exception as e:                                  # report, do not hide
             longform = {"error": f"{type(e).__name__}: {e}"[:300]}
             if world > 1:
@@ -686,7 +821,7 @@ def main():
     streaming = None
     if not args.no_streaming:
         y = None
-        streaming = streaming_leg(dec, geom, dev)
+        streaming = streaming_leg(dec, geom, dev, sd)
 
     # ---- encoder leg (BASELINE.json configs[4]) ---------------------------------------------------------
     encoder = None
@@ -712,22 +847,31 @@ def main():
             torch.cuda.empty_cache()
 
     # ---- CPU baseline (reported, not the target): bounded sample on the host cores -----------------
-    cpu = None
+    cpu, parity = None, None
     if not args.no_cpu_baseline:
-        torch.set_num_threads(os.cpu_count() or 1)
-        v, sec = cpu_port_audio_s_per_s(sd, 2, 1)
-        cpu = {"value": v, "unit": UNIT, "cores": os.cpu_count(), "kind": "port",
-               "sample": f"batch {CPU_SAMPLE_B} x {CPU_SAMPLE_T} frames (10 s), numpy fp32 port, {sec:.2f} s per decode"}
+        v, sec, threads = cpu_reference_audio_s_per_s(sd, 3, 1)
+        cpu = {"value": v, "unit": UNIT, "cores": threads, "kind": "port",
+               "sample": CPU_SAMPLE + f"; {sec:.2f} s per decode", "torch": torch.__version__}
+        # ---- parity at the headline's own size: one utterance of the K2 batch against the CPU reference ------------------
+        u = 17 % B
+        y = dec.decode(lat)                                     # the timed call, once more (same routing, same tiles)
+        parity = {"k2": parity_decode_sample(sd, geom, lat_host[u:u + 1].float(), y[u:u + 1],
+                                             f"utterance {u} of the batch {B} x {T} frames ({T / FRAME_RATE:.0f} s), bf16 output "
+                                             f"vs the CPU reference (fp32)"),
+                  "k3": ({"ok": longform.get("parity_ok"), "windows": longform.get("parity_windows")} if longform else None),
+                  "k4": ({"ok": streaming.get("schedule", {}).get("parity_ok"), "streams": streaming.get("schedule", {}).get("parity")}
+                         if streaming else None),
+                  "k5": (encoder.get("parity") if encoder else None),
+                  "tolerance": "SNR >= 40 dB and max|d| <= 2e-2 of the reference peak (BASELINE.json north_star)"}
+        del y
 
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16",
         "data": "synthetic",
-        "config": {"workload": f"acoustic decoder bf16, batch {B} x {T / FRAME_RATE:.0f} s ({T} latent frames) synthetic "
-                               f"latents per GPU, random-init (stress) weights",
-                   "l2": "inputs >> L2 (each pass streams >700 MB of activations per utterance group)",
-                   "sharding": "utterances per rank, no data-path collective"},
+        "config": workload_config(B, T),
         "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roof, "cpu_baseline": cpu,
+        "parity": parity,
         "streaming": streaming, "encoder": encoder, "longform": longform,
         "torch_eager_gpu": eager,
     }
