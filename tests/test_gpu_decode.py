@@ -145,6 +145,31 @@ def test_streaming_equals_offline_and_uneven_chunks(full_decoder):
     assert torch.equal(st, off), parity_metrics(st.cpu().numpy(), off.cpu().numpy())
 
 
+def test_both_block_kernels_stream_equal_offline(full_decoder):
+    """block_kernel 0 (block_fused_kernel) and 1 (block_tma_kernel: halo rows patched from / saved to the stream state by
+    its S1 warps) each reproduce their own offline decode bit for bit when streamed in uneven chunks, and agree with each
+    other to fp32 rounding."""
+    dec, _ = full_decoder
+    lat = torch.from_numpy(make_latents(2, 9, 64, 47)).cuda()
+    outs = {}
+    try:
+        for k in (0, 1):
+            dec.set_option("block_kernel", k)
+            off = dec.decode(lat)
+            cache = dec.new_cache(4)
+            idx = torch.tensor([3, 1], device="cuda")
+            parts, t = [], 0
+            for n in (1, 2, 1, 5):
+                parts.append(dec.decode(lat[:, t:t + n], cache=cache, sample_indices=idx, use_cache=True))
+                t += n
+            assert torch.equal(torch.cat(parts, -1), off), k
+            outs[k] = off
+    finally:
+        dec.set_option("block_kernel", 1)
+    m = parity_metrics(outs[1].cpu().numpy(), outs[0].cpu().numpy())
+    assert m["snr_db"] > 60.0, m
+
+
 def test_state_zero_export_import(full_decoder):
     dec, _ = full_decoder
     lat = torch.from_numpy(make_latents(1, 4, 64, 43)).cuda()

@@ -78,11 +78,14 @@ def test_ffn_half(full_decoder, stage, B, rows):
     assert m["snr_db"] > 50 and m["rel_max"] < 5e-3, m
 
 
+@pytest.mark.parametrize("kernel", [1, 0])
 @pytest.mark.parametrize("stage,B,rows", [(6, 2, 300), (5, 1, 129), (6, 1, 1), (5, 3, 5), (6, 1, 6), (5, 2, 127),
-                                          (6, 3, 40001), (5, 2, 60001)])
-def test_block_fused(full_decoder, stage, B, rows):
-    """Whole Block1D in one kernel (C <= 64) against the oracle's mixer half followed by its FFN half."""
+                                          (6, 3, 40001), (5, 2, 60001), (5, 1, 128), (6, 2, 8), (5, 4, 263)])
+def test_block_fused(full_decoder, stage, B, rows, kernel):
+    """Whole Block1D in one kernel (C <= 64) against the oracle's mixer half followed by its FFN half.
+    kernel 1 = block_tma_kernel (x tile staged by TMA, the product default), 0 = block_fused_kernel."""
     dec, w = full_decoder
+    dec.set_option("block_kernel", kernel)
     Cc = FULL.stage_channels(stage)
     x = (_rng(31000 + stage * 100 + rows).standard_normal((B, rows, Cc)).astype(np.float32) * 1.7)
     p = f"decoder.stages.{stage}.0."
@@ -96,9 +99,12 @@ def test_block_fused(full_decoder, stage, B, rows):
     ref = y.transpose(0, 2, 1) + f * w[p + "ffn_gamma"][None, None, :]
     xt = torch.from_numpy(x).cuda()
     out = torch.full_like(xt, float("nan"))
-    rc = dec._lib.vv_kernel_block(dec._h, stage, 0, _ptr(xt), _ptr(out), B, rows, _stream())
-    _check(dec, rc, "vv_kernel_block")
-    torch.cuda.synchronize()
+    try:
+        rc = dec._lib.vv_kernel_block(dec._h, stage, 0, _ptr(xt), _ptr(out), B, rows, _stream())
+        _check(dec, rc, "vv_kernel_block")
+        torch.cuda.synchronize()
+    finally:
+        dec.set_option("block_kernel", 1)
     o = out.cpu().numpy()
     assert np.isfinite(o).all()
     m = O.parity_metrics(o, ref)

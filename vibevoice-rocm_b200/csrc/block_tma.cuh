@@ -1,0 +1,581 @@
+// block_tma.cuh — second-generation whole-Block1D kernel for the narrow stages (C = 32, 64): the x tile is STAGED ONCE by
+// TMA into shared memory and every row statistic is computed exactly once, by a thread that owns the row.
+//
+//   y   = x + gamma * ( dwconv7( RMSNorm(x) * norm_w ) + conv_bias )                      (reference :927-932 / :667-672)
+//   out = y + ffn_gamma * ( W2 * gelu_erf( W1 * (RMSNorm(y) * ffn_norm_w) + b1 ) + b2 )   (:936-942 / :675-682)
+//
+// Why (ncu of block_fused_kernel, profiles/block_fused_s5_r01.txt + the SASS page of the C = 32 capture): that kernel
+// moves exactly the algorithmic bytes but runs at 31-36 % of HBM speed because it is bound INSIDE the SM: its mixer warps
+// load x rows global -> registers with 6 warm-up rows per 8 produced (1.75x L1 read amplification, L1TEX the busiest unit),
+// normalise every row 1.75 times and reduce every statistic with a 16-lane butterfly (8 of ~50 instructions per row and
+// lane, twice), at ~0.2 IPC on the critical path.  Per 128-row tile it executes ~10 000 warp instructions at C = 64 of
+// which ~4 800 belong to the mixer.  Here:
+//   * TMA loads the [8 halo + 128, C] fp32 tile (3-D map, rows before the item start are zero-filled by the hardware =
+//     the causal left pad, :398-403) into a 128B-swizzled ring slot; nothing is loaded twice.
+//   * S1 warps (thread = row) read their row once, conflict-free, and write rstd[row]: no shuffles, no redundancy.
+//   * S2 warps (lane = 4 channels, register sliding window over a 16- or 8-row strip) do the depthwise conv; warm-up rows
+//     cost a load and a multiply, not a statistic.  y is written IN PLACE over x in the slot.
+//   * S3 warps (thread = row) compute the second statistic and write a = bf16(y * rstd2) into the swizzled GEMM-1 operand
+//     tile (ffn_norm_w is folded into W1 at pack time, ffn_gamma into W2, ffn_gamma * b2 is a per-channel constant).
+//   * GEMM 1 / E1 (GELU, H back into tensor memory) / GEMM 2 (A from TMEM) as in block_fused_kernel, with HC-column
+//     chunks (HC = 128: the a tile is read twice per tile from shared memory instead of four times).
+//   * E2 (thread = row): out = y + d2 + gb2, in place in the slot -> TMA store; the slot then goes back to the loader.
+// Mixer instruction count per tile: ~2 200 (C = 64) instead of ~4 800; no global load instruction on the hot path.
+// Streaming (STATE): the first tile of an item patches its 6 halo rows from the stream's cached raw rows before S1 runs;
+// S1 saves the item's last 6 raw rows (reference :327-382; same state layout as block_fused_kernel / mixer_kernel).
+#pragma once
+#include <cuda.h>
+#include "ptx.cuh"
+#include "epilogue.cuh"
+#include "mixer.cuh"        // StateRef
+#include "block_fused.cuh"  // reg_dec / reg_inc, rstd_of
+
+namespace vv {
+
+#ifndef VV_BT_HC
+#define VV_BT_HC 128        // hidden units per GEMM-1 chunk (64 or 128)
+#endif
+#ifndef VV_BT_NX64
+#define VV_BT_NX64 3        // x/y ring slots at C = 64 (34 KB each)
+#endif
+#ifndef VV_BT_NX32
+#define VV_BT_NX32 6        // at C = 32 (17 KB each)
+#endif
+
+struct BlockTmaArgs {
+  int nbatch, rows_pb;
+  int tiles_pb;              // ceil(rows_pb / 128)
+  float eps;
+  const float* x;            // [nbatch, rows_pb, C] fp32: only the STATE form reads it directly (nothing offline)
+  const float* norm_w;       // [C]
+  const float* dw_w;         // [7][C] tap-major
+  const float* dw_b;         // [C]
+  const float* gamma;        // [C]
+  const float* b1;           // [4C]  pre-scaled by 0.5 like W1
+  const float* gb2;          // [C]   ffn_gamma * b2
+  __nv_bfloat16* out_bf16;   // optional padded bf16 copy: [nbatch, ob_rpb, C], row t of an item lands at row ob_off + t
+  long long ob_rpb;
+  int ob_off;
+  StateRef st;               // mixer context: fp32 [6][C] raw rows per stream (null base = offline)
+};
+
+template <int C>
+struct BlockTmaCfg {
+  static_assert(C == 32 || C == 64, "block_tma_kernel is laid out for C = 32 / 64");
+  static constexpr int HC = (VV_BT_HC == 128 && C == 64) ? 128 : 64;   // 4C = 128 at C = 32: two 64-wide chunks
+  static constexpr int NCH = 4 * C / HC;
+  static constexpr int ROWB = C * 2;                 // bytes per a / W1 row (64 or 128 = the swizzle span)
+  static constexpr int NBOX = C / 32;
+  static constexpr int LPR = C / 4;                  // S2 lanes per row
+  static constexpr int HALO = 8, XROWS = 128 + HALO;
+  static constexpr int XBOX_BYTES = XROWS * 128;     // 17 408 = 17 KB: box bases stay 1 KB aligned
+  static constexpr int XY_BYTES = NBOX * XBOX_BYTES;
+  static constexpr int NX = (C == 64) ? VV_BT_NX64 : VV_BT_NX32;
+  static constexpr int NA = (C == 64) ? 2 : 4;
+  static constexpr int E1W = 8, E2W = 4, S1W = 4, S3W = 4, S2W = 4, CTRL = 4;
+  static constexpr int STRIPS = S2W * 32 / LPR;      // 8 (C = 64) or 16 (C = 32)
+  static constexpr int R = 128 / STRIPS;             // rows per strip: 16 or 8
+  static constexpr int WARPS = E1W + E2W + S1W + S3W + S2W + CTRL;
+  static constexpr int THREADS = WARPS * 32;
+  static constexpr int W1_BYTES = 4 * C * ROWB;
+  static constexpr int W2_BYTES = (4 * C / 64) * C * 128;   // K-blocks of [C rows, 64]
+  static constexpr int A_BYTES = 128 * ROWB;
+  static constexpr int RSTD_STRIDE = 144;            // floats per slot (row + 2 is the index: 16 B aligned strip windows)
+  static constexpr int OFF_W1 = 0;
+  static constexpr int OFF_W2 = OFF_W1 + W1_BYTES;
+  static constexpr int OFF_A = OFF_W2 + W2_BYTES;
+  static constexpr int OFF_XY = OFF_A + NA * A_BYTES;
+  static constexpr int OFF_RSTD = OFF_XY + NX * XY_BYTES;
+  static constexpr int OFF_BAR = OFF_RSTD + NX * RSTD_STRIDE * 4;
+  static constexpr int NBARS = 1 + 5 * NX + 2 * NA + 12;
+  static constexpr int TOTAL = OFF_BAR + 512 + 1024;
+  static_assert(NBARS * 8 + 8 <= 512, "barrier block");
+  static_assert(OFF_XY % 1024 == 0 && XBOX_BYTES % 1024 == 0, "swizzled boxes need 1 KB aligned bases");
+  static_assert(TOTAL <= 232448, "exceeds the 227 KB dynamic shared memory limit");
+  static constexpr uint32_t TMEM_COLS = 512;         // D1: 2 x HC at 0; H: 2 x HC/2 at 2 HC; D2: 2 x C at 3 HC
+  static constexpr uint32_t H_COL0 = 2 * HC, D2_COL0 = 3 * HC;
+  static_assert(3 * HC + 2 * C <= 512, "tensor memory columns");
+  // register budgets (setmaxnreg draws from the CTA's launch allocation: threads x launch registers)
+  static constexpr int REG_LAUNCH = (65536 / THREADS) / 8 * 8;
+  static constexpr int REG_E1 = 64, REG_E2 = 64, REG_S1 = 40, REG_S3 = (C == 64) ? 96 : 64, REG_S2 = 112, REG_CTRL = 32;
+  static_assert(32 * (E1W * REG_E1 + E2W * REG_E2 + S1W * REG_S1 + S3W * REG_S3 + S2W * REG_S2 + CTRL * REG_CTRL) <=
+                    THREADS * REG_LAUNCH, "setmaxnreg budget exceeds the CTA's launch allocation");
+};
+
+template <int FROM, int TO> __device__ __forceinline__ void reg_set() {
+  if constexpr (TO < FROM) reg_dec<TO>();
+  else if constexpr (TO > FROM) reg_inc<TO>();
+}
+
+// address of the 16-byte cell (row, 4-float chunk q of a 32-channel box) inside a 128B-swizzled [rows, 32 fp32] box
+__device__ __forceinline__ uint32_t xy_cell(int row, int q) { return (uint32_t)(row * 128 + ((q ^ (row & 7)) << 4)); }
+
+template <int C, bool STATE>
+__global__ void __launch_bounds__(BlockTmaCfg<C>::THREADS, 1)
+block_tma_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmO,
+                 const __grid_constant__ CUtensorMap tmW1, const __grid_constant__ CUtensorMap tmW2,
+                 const BlockTmaArgs p) {
+  using L = BlockTmaCfg<C>;
+  constexpr int NX = L::NX, NA = L::NA, NCH = L::NCH, NBOX = L::NBOX, HC = L::HC, LPR = L::LPR, R = L::R;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  uint8_t* sW1 = smem + L::OFF_W1;
+  uint8_t* sW2 = smem + L::OFF_W2;
+  uint8_t* sA = smem + L::OFF_A;
+  uint8_t* sXY = smem + L::OFF_XY;
+  float* sRstd = (float*)(smem + L::OFF_RSTD);
+  uint64_t* bars = (uint64_t*)(smem + L::OFF_BAR);
+  uint64_t* w_full = bars;                 // [1]
+  uint64_t* x_full = bars + 1;             // [NX] TMA landed the x tile
+  uint64_t* st_ready = x_full + NX;        // [NX] S1 wrote rstd[] (and patched / saved the stream context)
+  uint64_t* y_full = st_ready + NX;        // [NX] S2 wrote y in place
+  uint64_t* y_ready = y_full + NX;         // [NX] E2 turned it into the block output
+  uint64_t* y_empty = y_ready + NX;        // [NX] the TMA store has read it (and S3 is done with it: S3 precedes E2)
+  uint64_t* a_full = y_empty + NX;         // [NA] S3 wrote the a tile
+  uint64_t* a_empty = a_full + NA;         // [NA] GEMM 1 has read it
+  uint64_t* d1_full = a_empty + NA;        // [2]
+  uint64_t* d1_empty = d1_full + 2;        // [2]
+  uint64_t* h_full = d1_empty + 2;         // [2]
+  uint64_t* h_empty = h_full + 2;          // [2]
+  uint64_t* d2_full = h_empty + 2;         // [2]
+  uint64_t* d2_empty = d2_full + 2;        // [2]
+  uint32_t* tmem_slot = (uint32_t*)(d2_empty + 2);
+
+  // hardware warps: [0, 8) E1, [8, 12) E2, [12, 16) S1, [16, 20) S3, [20, 24) S2, [24, 28): loader, G1, G2, store
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  constexpr int WARP_E2 = L::E1W, WARP_S1 = WARP_E2 + L::E2W, WARP_S3 = WARP_S1 + L::S1W, WARP_S2 = WARP_S3 + L::S3W,
+                WARP_CTRL = WARP_S2 + L::S2W;
+  const int ntiles = p.nbatch * p.tiles_pb;
+  const int my_tiles = (ntiles > (int)blockIdx.x) ? (ntiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
+  const int total_g = my_tiles * NCH;
+  auto tile_of = [&](int it, int& b, int& t0) {
+    const int tile = (int)blockIdx.x + it * (int)gridDim.x;
+    b = tile / p.tiles_pb;
+    t0 = (tile - b * p.tiles_pb) * 128;
+  };
+
+  if (threadIdx.x == 0) {
+    tma_prefetch_desc(&tmX);
+    tma_prefetch_desc(&tmO);
+    tma_prefetch_desc(&tmW1);
+    tma_prefetch_desc(&tmW2);
+    mbar_init(w_full, 1);
+    for (int i = 0; i < NX; ++i) {
+      mbar_init(&x_full[i], 1);
+      mbar_init(&st_ready[i], L::S1W);
+      mbar_init(&y_full[i], L::S2W);
+      mbar_init(&y_ready[i], L::E2W);
+      mbar_init(&y_empty[i], 1);
+    }
+    for (int i = 0; i < NA; ++i) { mbar_init(&a_full[i], L::S3W); mbar_init(&a_empty[i], 1); }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&d1_full[i], 1);
+      mbar_init(&d1_empty[i], L::E1W / 2);
+      mbar_init(&h_full[i], L::E1W / 2);
+      mbar_init(&h_empty[i], 1);
+      mbar_init(&d2_full[i], 1);
+      mbar_init(&d2_empty[i], L::E2W);
+    }
+    fence_mbar_init();
+  }
+  if (warp == WARP_CTRL + 1) {
+    tmem_alloc(tmem_slot, L::TMEM_COLS);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  pdl_launch();
+  // weights are constants (written at finalize): their loads go out before this CTA waits for the previous kernel
+  if (warp == WARP_CTRL && elect_one()) {
+    mbar_expect_tx(w_full, L::W1_BYTES + L::W2_BYTES);
+#pragma unroll
+    for (int j = 0; j < 4 * C / 128; ++j) tma_load_2d(sW1 + j * 128 * L::ROWB, &tmW1, w_full, 0, j * 128);
+#pragma unroll
+    for (int kb = 0; kb < 4 * C / 64; ++kb) tma_load_2d(sW2 + kb * (C * 128), &tmW2, w_full, kb * 64, 0);
+  }
+  pdl_wait();
+
+  if (warp >= WARP_CTRL) {
+    reg_set<L::REG_LAUNCH, L::REG_CTRL>();
+    const int role = warp - WARP_CTRL;
+    if (role == 0) {
+      // ===== x loader: one [XROWS, 32] box per 32 channels, rows t0 - 8 .. t0 + 127 (rows outside the item read as zero)
+      if (elect_one()) {
+        for (int it = 0; it < my_tiles; ++it) {
+          const int s = it % NX;
+          int b, t0;
+          tile_of(it, b, t0);
+          mbar_wait_sleep(&y_empty[s], (uint32_t)(((it / NX) & 1) ^ 1), 64);
+          mbar_expect_tx(&x_full[s], L::XY_BYTES);
+#pragma unroll
+          for (int c = 0; c < NBOX; ++c)
+            tma_load_3d(sXY + s * L::XY_BYTES + c * L::XBOX_BYTES, &tmX, &x_full[s], c * 32, t0 - L::HALO, b);
+        }
+      }
+    } else if (role == 1) {
+      // ===== GEMM 1 issuer: D1[g & 1] = a * W1_chunk^T ========================================================
+      if (elect_one()) {
+        constexpr uint32_t idesc1 = umma_idesc_bf16(128, HC);
+        const uint64_t da0 = umma_smem_desc<L::ROWB>(smem_u32(sA));
+        const uint64_t dw0 = umma_smem_desc<L::ROWB>(smem_u32(sW1));
+        mbar_wait(w_full, 0);
+        int g = 0;
+        for (int it = 0; it < my_tiles; ++it) {
+          const int sa = it % NA;
+          mbar_wait_sleep(&a_full[sa], (uint32_t)((it / NA) & 1), 64);
+          const uint64_t da = da0 + (uint64_t)((sa * L::A_BYTES) >> 4);
+#pragma unroll 1
+          for (int j = 0; j < NCH; ++j, ++g) {
+            const int db = g & 1;
+            mbar_wait(&d1_empty[db], (uint32_t)(((g >> 1) & 1) ^ 1));
+            tc_fence_after();
+            const uint64_t dw = dw0 + (uint64_t)((j * HC * L::ROWB) >> 4);
+            const uint32_t d = tmem_base + (uint32_t)(db * HC);
+#pragma unroll
+            for (int kk = 0; kk < C / 16; ++kk)
+              umma_bf16(d, da + (uint64_t)(kk * 2), dw + (uint64_t)(kk * 2), idesc1, kk != 0);
+            umma_commit(&d1_full[db]);
+          }
+          umma_commit(&a_empty[sa]);
+        }
+      }
+    } else if (role == 2) {
+      // ===== GEMM 2 issuer: D2[it & 1] += H * W2_chunk^T (A operand from tensor memory) ==========================
+      if (elect_one()) {
+        constexpr uint32_t idesc2 = umma_idesc_bf16(128, C);
+        const uint64_t dw0 = umma_smem_desc<128>(smem_u32(sW2));
+        mbar_wait(w_full, 0);
+        int g = 0;
+        for (int it = 0; it < my_tiles; ++it) {
+          const int d2b = it & 1;
+          mbar_wait_sleep(&d2_empty[d2b], (uint32_t)(((it >> 1) & 1) ^ 1), 64);
+          const uint32_t d = tmem_base + L::D2_COL0 + (uint32_t)(d2b * C);
+#pragma unroll 1
+          for (int j = 0; j < NCH; ++j, ++g) {
+            const int hb = g & 1;
+            mbar_wait(&h_full[hb], (uint32_t)((g >> 1) & 1));
+            tc_fence_after();
+            const uint32_t ah = tmem_base + L::H_COL0 + (uint32_t)(hb * (HC / 2));
+#pragma unroll
+            for (int kk = 0; kk < HC / 16; ++kk) {
+              // hidden units [j HC + 16 kk, +16): K-block (j HC + 16 kk) / 64 of W2, 16-element step (kk & 3) inside it
+              const uint64_t dw = dw0 + (uint64_t)((((j * HC + kk * 16) >> 6) * C * 128) >> 4) + (uint64_t)((kk & 3) * 2);
+              umma_bf16_ts(d, ah + (uint32_t)(kk * 8), dw, idesc2, (j | kk) != 0);
+            }
+            umma_commit(&h_empty[hb]);
+          }
+          umma_commit(&d2_full[d2b]);
+        }
+      }
+    } else {
+      // ===== TMA store issuer: finished slot -> global, then the slot goes back to the loader =====================
+      if (elect_one()) {
+        for (int it = 0; it < my_tiles; ++it) {
+          const int s = it % NX;
+          int b, t0;
+          tile_of(it, b, t0);
+          mbar_wait_sleep(&y_ready[s], (uint32_t)((it / NX) & 1), 128);
+#pragma unroll
+          for (int c = 0; c < NBOX; ++c)
+            tma_store_3d(&tmO, sXY + s * L::XY_BYTES + c * L::XBOX_BYTES + L::HALO * 128, c * 32, t0, b);
+          tma_store_commit();
+          tma_store_wait_read<0>();
+          mbar_arrive(&y_empty[s]);
+        }
+        tma_store_wait_all<0>();
+      }
+    }
+  } else if (warp < WARP_E2) {
+    // ===== E1: D1 -> + b1 -> GELU -> bf16 pairs -> H in tensor memory ===========================================
+    // Two groups of 4 warps alternate chunks (group G owns D1 buffer G and H buffer G); a warp owns 32 rows.
+    reg_set<L::REG_LAUNCH, L::REG_E1>();
+    const int q = warp & 3;
+    const int grp = warp >> 2;
+    const uint32_t lane_base = (uint32_t)(q * 32) << 16;
+    const uint32_t d1addr = tmem_base + lane_base + (uint32_t)(grp * HC);
+    const uint32_t haddr = tmem_base + lane_base + L::H_COL0 + (uint32_t)(grp * (HC / 2));
+    for (int g = grp; g < total_g; g += 2) {
+      const int j = g % NCH;
+      const uint32_t ph = (uint32_t)((g >> 1) & 1);
+      const float* bp = p.b1 + j * HC;
+      mbar_wait(&d1_full[grp], ph);
+      tc_fence_after();
+#pragma unroll
+      for (int hf = 0; hf < HC / 32; ++hf) {
+        uint32_t v[32];
+        tmem_ld_32x32(d1addr + (uint32_t)(hf * 32), v);
+        tmem_ld_wait();
+        if (hf == HC / 32 - 1) {                     // whole accumulator is in registers: the next G1 may overwrite it
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&d1_empty[grp]);
+        }
+        uint32_t hv[16];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const float4 b0 = __ldg(reinterpret_cast<const float4*>(bp + hf * 32 + i * 8));
+          const float4 b1v = __ldg(reinterpret_cast<const float4*>(bp + hf * 32 + i * 8 + 4));
+          hv[i * 4 + 0] = gelu2_bias_pack(__uint_as_float(v[i * 8 + 0]), __uint_as_float(v[i * 8 + 1]), b0.x, b0.y);
+          hv[i * 4 + 1] = gelu2_bias_pack(__uint_as_float(v[i * 8 + 2]), __uint_as_float(v[i * 8 + 3]), b0.z, b0.w);
+          hv[i * 4 + 2] = gelu2_bias_pack(__uint_as_float(v[i * 8 + 4]), __uint_as_float(v[i * 8 + 5]), b1v.x, b1v.y);
+          hv[i * 4 + 3] = gelu2_bias_pack(__uint_as_float(v[i * 8 + 6]), __uint_as_float(v[i * 8 + 7]), b1v.z, b1v.w);
+        }
+        if (hf == 0) {
+          mbar_wait(&h_empty[grp], ph ^ 1);          // GEMM 2 has consumed this group's previous H chunk
+          tc_fence_after();
+        }
+        tmem_st_32x16(haddr + (uint32_t)(hf * 16), hv);   // thread = row: pair (k, k+1) -> one 32-bit column
+      }
+      tmem_st_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&h_full[grp]);
+    }
+  } else if (warp < WARP_S1) {
+    // ===== E2: out = y + (D2 + gb2), in place in the slot (thread = row) -> TMA store ==============================
+    reg_set<L::REG_LAUNCH, L::REG_E2>();
+    const int q = warp & 3;
+    const int r = q * 32 + lane;
+    for (int it = 0; it < my_tiles; ++it) {
+      const int d2b = it & 1, s = it % NX;
+      int b, t0;
+      tile_of(it, b, t0);
+      const int t = t0 + r;
+      const bool valid = t < p.rows_pb;
+      const long long brow = (long long)b * p.ob_rpb + p.ob_off + t;
+      mbar_wait(&y_full[s], (uint32_t)((it / NX) & 1));      // (long complete: orders this thread after S2's stores)
+      mbar_wait(&d2_full[d2b], (uint32_t)((it >> 1) & 1));   // implies S3 is done with the slot (a_full -> G1 -> ... -> G2)
+      tc_fence_after();
+      uint8_t* slot = sXY + s * L::XY_BYTES;
+#pragma unroll
+      for (int c = 0; c < NBOX; ++c) {
+        uint32_t v[32];
+        tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + L::D2_COL0 + (uint32_t)(d2b * C + c * 32), v);
+        tmem_ld_wait();
+        uint8_t* box = slot + c * L::XBOX_BYTES;
+        float o[32];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          float4* cell = reinterpret_cast<float4*>(box + xy_cell(L::HALO + r, i));
+          const float4 yv = *cell;
+          const float4 gv = __ldg(reinterpret_cast<const float4*>(p.gb2 + c * 32 + i * 4));
+          o[i * 4 + 0] = (yv.x + gv.x) + __uint_as_float(v[i * 4 + 0]);
+          o[i * 4 + 1] = (yv.y + gv.y) + __uint_as_float(v[i * 4 + 1]);
+          o[i * 4 + 2] = (yv.z + gv.z) + __uint_as_float(v[i * 4 + 2]);
+          o[i * 4 + 3] = (yv.w + gv.w) + __uint_as_float(v[i * 4 + 3]);
+          *cell = make_float4(o[i * 4], o[i * 4 + 1], o[i * 4 + 2], o[i * 4 + 3]);
+        }
+        if (valid && p.out_bf16 != nullptr) {
+          __nv_bfloat16* bp = p.out_bf16 + brow * C + c * 32;
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            uint4 pk;
+            pk.x = pack_bf16x2(o[i * 8 + 0], o[i * 8 + 1]);
+            pk.y = pack_bf16x2(o[i * 8 + 2], o[i * 8 + 3]);
+            pk.z = pack_bf16x2(o[i * 8 + 4], o[i * 8 + 5]);
+            pk.w = pack_bf16x2(o[i * 8 + 6], o[i * 8 + 7]);
+            *reinterpret_cast<uint4*>(bp + i * 8) = pk;
+          }
+        }
+      }
+      tc_fence_before();
+      fence_proxy_async_smem();                 // staged tile -> visible to the TMA store
+      __syncwarp();
+      if (lane == 0) {
+        mbar_arrive(&d2_empty[d2b]);
+        mbar_arrive(&y_ready[s]);
+      }
+    }
+  } else if (warp < WARP_S3) {
+    // ===== S1: thread = row: rstd of the raw row (first RMSNorm), stream context in / out ===========================
+    reg_set<L::REG_LAUNCH, L::REG_S1>();
+    const int r = (warp - WARP_S1) * 32 + lane;           // tile row 0..127 -> slot row HALO + r
+    const float inv_c = 1.0f / (float)C;
+    auto row_rstd = [&](const uint8_t* slot, int srow) -> float {
+      f32x2 acc = 0ull;
+#pragma unroll
+      for (int c = 0; c < NBOX; ++c) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const ulonglong2 v = *reinterpret_cast<const ulonglong2*>(slot + c * L::XBOX_BYTES + xy_cell(srow, i));
+          acc = f2_fma(v.x, v.x, acc);
+          acc = f2_fma(v.y, v.y, acc);
+        }
+      }
+      float s0, s1;
+      f2_unpack(acc, s0, s1);
+      return rstd_of(s0 + s1, inv_c, p.eps);
+    };
+    for (int it = 0; it < my_tiles; ++it) {
+      const int s = it % NX;
+      int b, t0;
+      tile_of(it, b, t0);
+      uint8_t* slot = sXY + s * L::XY_BYTES;
+      float* rs = sRstd + s * L::RSTD_STRIDE;
+      mbar_wait(&x_full[s], (uint32_t)((it / NX) & 1));
+      const uint8_t* rd8 = nullptr;
+      uint8_t* wr8 = nullptr;
+      if (STATE && p.st.base != nullptr) p.st.resolve(b, rd8, wr8);
+      if (warp == WARP_S1 && lane < L::HALO) {
+        // halo rows (slot rows 0..7 = t0 - 8 .. t0 - 1): at the item start rows 2..7 are the stream's cached raw rows
+        // (TMA delivered zeros = the offline causal pad, :398-403)
+        if (STATE && t0 == 0 && rd8 != nullptr && lane >= 2) {
+          const float* src = reinterpret_cast<const float*>(rd8) + (lane - 2) * C;
+#pragma unroll
+          for (int c = 0; c < NBOX; ++c)
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+              *reinterpret_cast<float4*>(slot + c * L::XBOX_BYTES + xy_cell(lane, i)) =
+                  *reinterpret_cast<const float4*>(src + c * 32 + i * 4);
+        }
+        rs[lane + 2] = row_rstd(slot, lane);
+        // the stream's new context = last 6 raw rows of [old context, x] (:371-382): rows before the item start count
+        if (STATE && wr8 != nullptr && t0 == 0) {
+          const int t = lane - L::HALO;                                     // -8 .. -1
+          const int dst = t - (p.rows_pb - 6);
+          if (dst >= 0) {
+            float* o = reinterpret_cast<float*>(wr8) + dst * C;
+#pragma unroll
+            for (int c = 0; c < NBOX; ++c)
+#pragma unroll
+              for (int i = 0; i < 8; ++i)
+                *reinterpret_cast<float4*>(o + c * 32 + i * 4) =
+                    *reinterpret_cast<const float4*>(slot + c * L::XBOX_BYTES + xy_cell(lane, i));
+          }
+        }
+      }
+      rs[L::HALO + r + 2] = row_rstd(slot, L::HALO + r);
+      if (STATE && wr8 != nullptr) {
+        const int t = t0 + r;
+        const int dst = t - (p.rows_pb - 6);
+        if (dst >= 0 && t < p.rows_pb) {
+          float* o = reinterpret_cast<float*>(wr8) + dst * C;
+#pragma unroll
+          for (int c = 0; c < NBOX; ++c)
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+              *reinterpret_cast<float4*>(o + c * 32 + i * 4) =
+                  *reinterpret_cast<const float4*>(slot + c * L::XBOX_BYTES + xy_cell(L::HALO + r, i));
+        }
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&st_ready[s]);
+    }
+  } else if (warp < WARP_S2) {
+    // ===== S3: thread = row: second RMSNorm statistic, a = bf16(y * rstd2) -> swizzled GEMM-1 operand tile ============
+    reg_set<L::REG_LAUNCH, L::REG_S3>();
+    const int r = (warp - WARP_S3) * 32 + lane;
+    const float inv_c = 1.0f / (float)C;
+    for (int it = 0; it < my_tiles; ++it) {
+      const int s = it % NX, sa = it % NA;
+      const uint8_t* slot = sXY + s * L::XY_BYTES;
+      uint8_t* arow = sA + sa * L::A_BYTES + r * L::ROWB;
+      mbar_wait(&y_full[s], (uint32_t)((it / NX) & 1));
+      ulonglong2 y[C / 4];
+      f32x2 acc = 0ull;
+#pragma unroll
+      for (int c = 0; c < NBOX; ++c)
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          y[c * 8 + i] = *reinterpret_cast<const ulonglong2*>(slot + c * L::XBOX_BYTES + xy_cell(L::HALO + r, i));
+          acc = f2_fma(y[c * 8 + i].x, y[c * 8 + i].x, acc);
+          acc = f2_fma(y[c * 8 + i].y, y[c * 8 + i].y, acc);
+        }
+      float s0, s1;
+      f2_unpack(acc, s0, s1);
+      const float rstd2 = rstd_of(s0 + s1, inv_c, p.eps);
+      const f32x2 rr = f2_pack(rstd2, rstd2);
+      mbar_wait(&a_empty[sa], (uint32_t)(((it / NA) & 1) ^ 1));
+#pragma unroll
+      for (int k = 0; k < C / 8; ++k) {                  // 16-byte chunk k of the row = channels [8k, 8k + 8)
+        float a0, a1, a2, a3, a4, a5, a6, a7;
+        f2_unpack(f2_mul(y[2 * k].x, rr), a0, a1);
+        f2_unpack(f2_mul(y[2 * k].y, rr), a2, a3);
+        f2_unpack(f2_mul(y[2 * k + 1].x, rr), a4, a5);
+        f2_unpack(f2_mul(y[2 * k + 1].y, rr), a6, a7);
+        uint4 pk;
+        pk.x = pack_bf16x2(a0, a1);
+        pk.y = pack_bf16x2(a2, a3);
+        pk.z = pack_bf16x2(a4, a5);
+        pk.w = pack_bf16x2(a6, a7);
+        const int sw = (L::ROWB == 128) ? (k ^ (r & 7)) : (k ^ ((r >> 1) & 3));
+        *reinterpret_cast<uint4*>(arow + (sw << 4)) = pk;
+      }
+      fence_proxy_async_smem();                 // a tile (generic-proxy stores) -> visible to tcgen05.mma
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&a_full[sa]);
+    }
+  } else {
+    // ===== S2: depthwise causal conv k7 over the normalised rows; lane = 4 channels, strip = R consecutive rows =======
+    reg_set<L::REG_LAUNCH, L::REG_S2>();
+    struct P4 { f32x2 lo, hi; };
+    const int gi = (warp - WARP_S2) * (32 / LPR) + lane / LPR;      // strip 0..STRIPS-1: tile rows [R gi, R gi + R)
+    const int c0 = (lane % LPR) * 4;
+    const int box = c0 >> 5, qc = (c0 & 31) >> 2;
+    // folded taps: y = x + gb + sum_j wq[j] * n[t-6+j],  n = x * rstd,  wq = gamma * w * norm_w,  gb = gamma * conv_bias
+    P4 wq[7], gb;
+    {
+      const float4 nw = __ldg(reinterpret_cast<const float4*>(p.norm_w + c0));
+      const float4 gm = __ldg(reinterpret_cast<const float4*>(p.gamma + c0));
+      const float4 cb = __ldg(reinterpret_cast<const float4*>(p.dw_b + c0));
+      gb.lo = f2_pack(gm.x * cb.x, gm.y * cb.y);
+      gb.hi = f2_pack(gm.z * cb.z, gm.w * cb.w);
+#pragma unroll
+      for (int j = 0; j < 7; ++j) {
+        const float4 w = __ldg(reinterpret_cast<const float4*>(p.dw_w + j * C + c0));
+        wq[j].lo = f2_pack(gm.x * w.x * nw.x, gm.y * w.y * nw.y);
+        wq[j].hi = f2_pack(gm.z * w.z * nw.z, gm.w * w.w * nw.w);
+      }
+    }
+    const int sr0 = L::HALO + gi * R;                               // slot row of the strip's first output row
+    for (int it = 0; it < my_tiles; ++it) {
+      const int s = it % NX;
+      uint8_t* bx = sXY + s * L::XY_BYTES + box * L::XBOX_BYTES;
+      const float* rs = sRstd + s * L::RSTD_STRIDE + sr0 - 4;      // rs[i] = rstd of slot row sr0 - 6 + i  (16 B aligned)
+      mbar_wait(&st_ready[s], (uint32_t)((it / NX) & 1));
+      float rv[R + 8];
+#pragma unroll
+      for (int i = 0; i < (R + 8) / 4; ++i) {
+        const float4 t4 = *reinterpret_cast<const float4*>(rs + i * 4);
+        rv[i * 4] = t4.x; rv[i * 4 + 1] = t4.y; rv[i * 4 + 2] = t4.z; rv[i * 4 + 3] = t4.w;
+      }
+      P4 win[7];
+#pragma unroll
+      for (int i = 0; i < 6; ++i) {                                  // warm-up rows: a load and a multiply each
+        const ulonglong2 v = *reinterpret_cast<const ulonglong2*>(bx + xy_cell(sr0 - 6 + i, qc));
+        const f32x2 rr = f2_pack(rv[i], rv[i]);
+        win[i].lo = f2_mul(v.x, rr);
+        win[i].hi = f2_mul(v.y, rr);
+      }
+      // y is written in place: every strip must hold its warm-up rows (its neighbour's last rows) before anyone stores
+      named_bar_sync(1, L::S2W * 32);
+#pragma unroll
+      for (int k = 0; k < R; ++k) {
+        ulonglong2* cell = reinterpret_cast<ulonglong2*>(bx + xy_cell(sr0 + k, qc));
+        const ulonglong2 v = *cell;
+        const f32x2 rr = f2_pack(rv[6 + k], rv[6 + k]);
+        win[(6 + k) % 7].lo = f2_mul(v.x, rr);
+        win[(6 + k) % 7].hi = f2_mul(v.y, rr);
+        P4 acc;
+        acc.lo = f2_add(v.x, gb.lo);
+        acc.hi = f2_add(v.y, gb.hi);
+#pragma unroll
+        for (int j = 0; j < 7; ++j) {                                // tap j reads n[t - 6 + j] = win[(k + j) % 7]
+          acc.lo = f2_fma(wq[j].lo, win[(k + j) % 7].lo, acc.lo);
+          acc.hi = f2_fma(wq[j].hi, win[(k + j) % 7].hi, acc.hi);
+        }
+        *cell = make_ulonglong2(acc.lo, acc.hi);
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&y_full[s]);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == WARP_CTRL + 1) tmem_dealloc(tmem_base, L::TMEM_COLS);
+}
+
+}  // namespace vv

@@ -14,6 +14,7 @@
 #include "ffn_fused.cuh"
 #include "ffn_stream.cuh"
 #include "block_fused.cuh"
+#include "block_tma.cuh"
 #include "gemm_tc2.cuh"
 #include "encoder.cuh"
 #include "pcm16.cuh"
@@ -230,6 +231,7 @@ static int32_t init_core(const vv_config* cfg, vv_decoder* d) {
   if (const char* ev = getenv("VV_GEMM_BN256")) d->opt_bn256 = atoi(ev);            // defaults; vv_decoder_set_option overrides
   if (const char* ev = getenv("VV_GEMM_BN256_WAVES")) d->opt_bn256_waves = atoi(ev);
   if (const char* ev = getenv("VV_GEMM_BN64")) d->opt_bn64 = atoi(ev);
+  if (const char* ev = getenv("VV_BLOCK_KERNEL")) d->opt_block_kernel = atoi(ev) != 0;
   d->hop = 1;
   for (int i = 0; i + 1 < cfg->n_stages; ++i) d->hop *= cfg->ratios[i];
   // causal receptive field in latent frames: sum of left taps / layer input rate
@@ -269,6 +271,7 @@ extern "C" int32_t vv_decoder_set_option(vv_decoder* d, const char* key, int64_t
   if (strcmp(key, "gemm_bn256") == 0 && value >= 0 && value <= 2) { d->opt_bn256 = (int)value; return VV_OK; }
   if (strcmp(key, "gemm_bn256_waves") == 0 && value >= 0) { d->opt_bn256_waves = (int)value; return VV_OK; }
   if (strcmp(key, "gemm_bn64") == 0 && value >= 0 && value <= 1) { d->opt_bn64 = (int)value; return VV_OK; }
+  if (strcmp(key, "block_kernel") == 0 && value >= 0 && value <= 1) { d->opt_block_kernel = (int)value; return VV_OK; }
   set_error("unknown option '%s' or value %lld out of range", key, (long long)value);
   return VV_ERR_INVALID_ARG;
 }
@@ -414,6 +417,19 @@ bool Packer::block(const std::string& p, int C, BlockW& bw) {
     dense(bw.lin1, to_bf16(w1h), b1h, 4 * C, C, 1);
   }
   dense(bw.lin2, to_bf16(*w2), *b2, C, 4 * C, 1);
+  if (status == VV_OK && C <= 64) {    // operands of block_tma_kernel with the per-channel scales folded in
+    std::vector<float> w1f(*w1), b1h(*b1), w2f(*w2), gb2((size_t)C);
+    for (int n = 0; n < 4 * C; ++n)
+      for (int k = 0; k < C; ++k) w1f[(size_t)n * C + k] *= 0.5f * (*fnw)[k];
+    for (float& v : b1h) v *= 0.5f;
+    for (int c = 0; c < C; ++c) {
+      for (int k = 0; k < 4 * C; ++k) w2f[(size_t)c * 4 * C + k] *= (*fg)[c];
+      gb2[c] = (*fg)[c] * (*b2)[c];
+    }
+    dense(bw.lin1f, to_bf16(w1f), b1h, 4 * C, C, 1);
+    dense(bw.lin2f, to_bf16(w2f), *b2, C, 4 * C, 1);
+    bw.gb2 = upload(gb2);
+  }
   if (status == VV_OK && C == 128) {   // ffn_stream_kernel reads linear1 in chunks of 64 hidden units
     const uint64_t dims[2] = {(uint64_t)C, (uint64_t)(4 * C)};
     const uint64_t strides[1] = {(uint64_t)C * 2};
@@ -774,10 +790,49 @@ int launch_block_fused_inst(vv_decoder* d, const CUtensorMap& tmO, const BlockW&
   return VV_OK;
 }
 
+template <int C, bool STATE>
+int launch_block_tma_inst(vv_decoder* d, const CUtensorMap& tmX, const CUtensorMap& tmO, const BlockW& bw,
+                          const BlockTmaArgs& a, cudaStream_t s) {
+  const int arc = ensure_smem(block_tma_kernel<C, STATE>, (int)BlockTmaCfg<C>::TOTAL, d->cfg.device);
+  if (arc != VV_OK) return arc;
+  const long long ntiles = (long long)a.nbatch * a.tiles_pb;
+  const unsigned grid = (unsigned)std::min<long long>(ntiles, d->num_sms);
+  launch_k(block_tma_kernel<C, STATE>, dim3(grid), dim3(BlockTmaCfg<C>::THREADS), BlockTmaCfg<C>::TOTAL, s, tmX, tmO,
+           bw.lin1f.tm, bw.lin2f.tm, a);
+  VV_LAUNCH_OK();
+  return VV_OK;
+}
+
+int launch_block_tma(vv_decoder* d, int C, const BlockW& bw, const float* x, float* out, __nv_bfloat16* out_bf16,
+                     int nbatch, int rows_pb, vv_state* st, const int32_t* slots, cudaStream_t s, PadOut po) {
+  BlockTmaArgs a;
+  a.x = x; a.nbatch = nbatch; a.rows_pb = rows_pb; a.tiles_pb = (rows_pb + 127) / 128; a.eps = d->cfg.eps;
+  a.norm_w = bw.norm_w; a.dw_w = bw.dw_w; a.dw_b = bw.dw_b; a.gamma = bw.gamma;
+  a.b1 = bw.lin1f.bias; a.gb2 = bw.gb2; a.out_bf16 = out_bf16;
+  a.st = make_state_ref(st, slots, bw.state_off);
+  a.ob_rpb = po.rpb > 0 ? po.rpb : rows_pb + po.off; a.ob_off = po.off;
+  if ((long long)nbatch * a.tiles_pb >= (1LL << 31) / 8) { set_error("block_tma: too many tiles"); return VV_ERR_BAD_SHAPE; }
+  // x and out: fp32 [nbatch, rows_pb, C]; load boxes [8 halo + 128 rows, 32 floats] (rows before the item start and past
+  // its end are zero-filled), store boxes [128 rows, 32 floats] (rows past the end are clipped)
+  CUtensorMap tmX, tmO;
+  const uint64_t dims[3] = {(uint64_t)C, (uint64_t)rows_pb, (uint64_t)nbatch};
+  const uint64_t strides[2] = {(uint64_t)C * 4, (uint64_t)rows_pb * C * 4};
+  const uint32_t xbox[3] = {32u, (uint32_t)BlockTmaCfg<32>::XROWS, 1u};
+  const uint32_t obox[3] = {32u, 128u, 1u};
+  int rc = encode_map(&tmX, x, 3, dims, strides, xbox, true);
+  if (rc == VV_OK) rc = encode_map(&tmO, out, 3, dims, strides, obox, true);
+  if (rc != VV_OK) return rc;
+  d->launches++;
+  const bool streaming = a.st.base != nullptr;
+  if (C == 32) return streaming ? launch_block_tma_inst<32, true>(d, tmX, tmO, bw, a, s) : launch_block_tma_inst<32, false>(d, tmX, tmO, bw, a, s);
+  return streaming ? launch_block_tma_inst<64, true>(d, tmX, tmO, bw, a, s) : launch_block_tma_inst<64, false>(d, tmX, tmO, bw, a, s);
+}
+
 int launch_block_fused(vv_decoder* d, int C, const BlockW& bw, const float* x, float* out, __nv_bfloat16* out_bf16,
                        int nbatch, int rows_pb, vv_state* st, const int32_t* slots, cudaStream_t s,
                        PadOut po = PadOut()) {
   if (x == out) { set_error("block_fused: input and output must not alias"); return VV_ERR_INVALID_ARG; }
+  if (d->opt_block_kernel == 1) return launch_block_tma(d, C, bw, x, out, out_bf16, nbatch, rows_pb, st, slots, s, po);
   BlockFusedArgs a;
   a.x = x; a.nbatch = nbatch; a.rows_pb = rows_pb; a.tiles_pb = (rows_pb + 127) / 128; a.eps = d->cfg.eps;
   a.norm_w = bw.norm_w; a.dw_w = bw.dw_w; a.dw_b = bw.dw_b; a.gamma = bw.gamma; a.ffn_norm_w = bw.ffn_norm_w;

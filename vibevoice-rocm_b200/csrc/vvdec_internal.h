@@ -40,6 +40,10 @@ struct BlockW {
         *ffn_gamma = nullptr;
   DenseW lin1, lin2;            // lin1 is stored pre-scaled by 0.5 (weights and bias), see epilogue.cuh
   CUtensorMap tm_w1s;           // lin1 through a [64 x 64] box (ffn_stream_kernel), C = 128 only
+  // block_tma_kernel (C <= 64) folds the per-channel scales into the GEMM operands: lin1f = 0.5 * W1 * diag(ffn_norm_w),
+  // lin2f = diag(ffn_gamma) * W2, gb2 = ffn_gamma * b2  (lin1f.bias = 0.5 * b1 as in lin1)
+  DenseW lin1f, lin2f;
+  float* gb2 = nullptr;
   long long state_off = 0;      // fp32 [6][C]
 };
 
@@ -71,6 +75,7 @@ struct vv_decoder {
   int opt_bn256 = 1;                // gemm_tc2 tile width: 0 never 256, 1 auto (>= opt_bn256_waves waves of wide tiles), 2 whenever N % 256 == 0
   int opt_bn256_waves = 2;
   int opt_bn64 = 1;                 // N = 64 layers on the persistent kernel's 64-wide tile (0: one-tile-per-CTA kernel)
+  int opt_block_kernel = 1;         // whole-Block1D kernel at C <= 64: 1 = block_tma_kernel (x tile staged by TMA), 0 = block_fused_kernel
   // optional per-launch timing (vv_decoder_set_profiling): CUDA events recorded on the decode stream
   bool prof_on = false;
   struct ProfMark { cudaEvent_t ev; int kind; int stage; };
