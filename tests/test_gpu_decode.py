@@ -147,8 +147,11 @@ def test_streaming_equals_offline_and_uneven_chunks(full_decoder):
 
 def test_both_block_kernels_stream_equal_offline(full_decoder):
     """block_kernel 0 (block_fused_kernel) and 1 (block_tma_kernel: halo rows patched from / saved to the stream state by
-    its S1 warps) each reproduce their own offline decode bit for bit when streamed in uneven chunks, and agree with each
-    other to fp32 rounding."""
+    its S1 warps) each reproduce their own offline decode bit for bit when streamed in uneven chunks.  They do NOT agree
+    with each other to fp32 rounding: block_tma folds ffn_norm_w into W1 and ffn_gamma into W2 BEFORE the bf16 rounding of
+    the weights, so its GEMM operands differ from block_fused's by one bf16 rounding (2^-9 relative).  Measured on B200:
+    54.1 dB between the two end-to-end outputs, each of which is 44-47 dB from the fp32 reference; the bound below is the
+    tolerance of the path itself (BASELINE.json: 40 dB) plus margin, not a rounding-noise bound."""
     dec, _ = full_decoder
     lat = torch.from_numpy(make_latents(2, 9, 64, 47)).cuda()
     outs = {}
@@ -167,7 +170,7 @@ def test_both_block_kernels_stream_equal_offline(full_decoder):
     finally:
         dec.set_option("block_kernel", 1)
     m = parity_metrics(outs[1].cpu().numpy(), outs[0].cpu().numpy())
-    assert m["snr_db"] > 60.0, m
+    assert m["snr_db"] > 48.0 and m["rel_max"] < 1e-2, m
 
 
 def test_state_zero_export_import(full_decoder):
