@@ -266,6 +266,23 @@ int32_t vv_kernel_head(vv_decoder* dec, const float* x, void* out, int32_t out_d
 int32_t vv_pcm16(const void* wave, int32_t wave_dtype, int32_t B, int64_t L, int64_t row_stride, int16_t* pcm,
                  float* peak, void* cuda_stream);
 
+/* ---- PCM16 without any allocation -----------------------------------------------------------------------------------
+ * NO COUNTERPART IN THE REFERENCE: added for callers that cannot allocate (code under
+ * CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  Same result as vv_pcm16, bit for bit; the
+ * per-row peak scratch the long-row form needs lives in a file-scope `static __device__` array inside the library instead
+ * of a caller buffer, and the call performs no cudaMalloc / cudaFree and calls no allocating routine.
+ *   limit    : B <= VV_PCM16_STATIC_MAX_ROWS rows per call (VV_ERR_BAD_SHAPE beyond it; L is unlimited);
+ *   cost     : every GPU that loads the library holds the array (4 B x VV_PCM16_STATIC_MAX_ROWS = 16 KB) until exit;
+ *   sharing  : all calls on a device share the array, which keeps the last call's contents; each call clears what it
+ *              needs on `cuda_stream`, so calls ordered on one stream are safe, while calls that OVERLAP on the GPU
+ *              (different streams without ordering) RACE on it -- use vv_pcm16 with separate peak buffers for those;
+ *   set-up   : the first call on a device resolves the array's device address (cudaGetSymbolAddress, once per device,
+ *              with that device current) -- make that first call outside stream capture.
+ * Runs on the calling thread's current device, like vv_pcm16. */
+#define VV_PCM16_STATIC_MAX_ROWS 4096
+int32_t vv_pcm16_static(const void* wave, int32_t wave_dtype, int32_t B, int64_t L, int64_t row_stride, int16_t* pcm,
+                        void* cuda_stream);
+
 /* The GELU of the FFN epilogue (:589, :594), alone: y[i] = gelu(x[i]); device pointers.  Accuracy test hook. */
 int32_t vv_test_gelu(const float* x, float* y, int32_t n, void* cuda_stream);
 

@@ -1422,6 +1422,76 @@ extern "C" int32_t vv_pcm16(const void* wave, int32_t wave_dtype, int32_t B, int
   return VV_OK;
 }
 
+// ---- vv_pcm16_static: vv_pcm16 for callers that cannot allocate --------------------------------------------------------
+// No counterpart in the reference.  Same arithmetic and same kernels as
+// vv_pcm16; the only difference is where the per-row peak scratch lives: in this file-scope device array instead of a
+// caller-provided buffer, so the call needs no allocation of any kind (no cudaMalloc / cudaFree, no allocating library
+// routine): usable under CUDA graph capture, in serving loops and in harnesses that forbid allocation.
+//   * every GPU that loads this library holds the array (VV_PCM16_STATIC_MAX_ROWS floats = 16 KB) until the process exits;
+//   * ALL calls on a device share it and it keeps the last call's contents: the two-pass form clears the rows it uses
+//     (the peak pass is an atomicMax and must start at zero) with cudaMemsetAsync on the caller's stream;
+//   * therefore two calls that overlap on the GPU (different streams, no ordering between them) RACE on it.
+// In host code `g_pcm16_static_peak` is a host-side stand-in for the symbol, NOT a device address: the address a kernel
+// can use comes from cudaGetSymbolAddress, resolved once per device with that device current (below) and cached.
+static __device__ __align__(256) float g_pcm16_static_peak[VV_PCM16_STATIC_MAX_ROWS];
+
+namespace {
+constexpr int kMaxDevices = 64;
+float* g_pcm16_static_ptr[kMaxDevices] = {};
+std::mutex g_pcm16_static_mu;
+
+// device address of the scratch array on the CURRENT device (set-up: the first call on a device resolves it)
+int pcm16_static_scratch(float** out) {
+  int dev = -1;
+  VV_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kMaxDevices) { set_error("device ordinal %d outside [0, %d)", dev, kMaxDevices); return VV_ERR_NO_DEVICE; }
+  std::lock_guard<std::mutex> lk(g_pcm16_static_mu);
+  if (g_pcm16_static_ptr[dev] == nullptr) {
+    void* ptr = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(&ptr, g_pcm16_static_peak);
+    if (e != cudaSuccess || ptr == nullptr) {
+      set_error("cudaGetSymbolAddress(pcm16 scratch) failed on device %d: %s", dev, cudaGetErrorString(e));
+      (void)cudaGetLastError();
+      return VV_ERR_CUDA;
+    }
+    g_pcm16_static_ptr[dev] = reinterpret_cast<float*>(ptr);
+  }
+  *out = g_pcm16_static_ptr[dev];
+  return VV_OK;
+}
+}  // namespace
+
+extern "C" int32_t vv_pcm16_static(const void* wave, int32_t wave_dtype, int32_t B, int64_t L, int64_t row_stride,
+                                   int16_t* pcm, void* cuda_stream) {
+  if (!wave || !pcm || B < 1 || L < 1 || row_stride < L) { set_error("bad argument"); return VV_ERR_INVALID_ARG; }
+  if (wave_dtype != VV_F32 && wave_dtype != VV_BF16) { set_error("wave must be f32 or bf16"); return VV_ERR_BAD_DTYPE; }
+  if (B > VV_PCM16_STATIC_MAX_ROWS) {
+    set_error("vv_pcm16_static: %d rows exceed the static scratch of %d rows per call (split the batch, or use vv_pcm16 "
+              "with a peak buffer of your own)", B, VV_PCM16_STATIC_MAX_ROWS);
+    return VV_ERR_BAD_SHAPE;
+  }
+  float* peak = nullptr;
+  const int rc = pcm16_static_scratch(&peak);
+  if (rc != VV_OK) return rc;
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(cuda_stream);
+  Pcm16Args p;
+  p.wave = wave; p.wave_is_bf16 = (wave_dtype == VV_BF16); p.B = B; p.L = L; p.row_stride = row_stride;
+  p.pcm = pcm; p.peak = peak;
+  p.vec_ok = ((reinterpret_cast<uintptr_t>(wave) | reinterpret_cast<uintptr_t>(pcm)) % 16 == 0) && row_stride % 8 == 0 &&
+             (B == 1 || L % 8 == 0);
+  if (L <= PCM_ROW_MAX) {
+    pcm16_row_kernel<<<(unsigned)B, PCM_THREADS, 0, s>>>(p);            // writes peak[b], reads nothing from the scratch
+  } else {
+    const long long chunks = (L + PCM_CHUNK - 1) / PCM_CHUNK;
+    if (chunks > 0x7fffffffLL) { set_error("row too long"); return VV_ERR_BAD_SHAPE; }
+    VV_CUDA(cudaMemsetAsync(peak, 0, sizeof(float) * (size_t)B, s));    // the previous call's peaks are still in there
+    pcm16_peak_kernel<<<dim3((unsigned)chunks, (unsigned)B), PCM_THREADS, 0, s>>>(p);
+    pcm16_convert_kernel<<<dim3((unsigned)chunks, (unsigned)B), PCM_THREADS, 0, s>>>(p);
+  }
+  VV_CUDA(cudaGetLastError());
+  return VV_OK;
+}
+
 #ifdef VV_FS_TRACE
 extern "C" int32_t vv_debug_read_trace(long long* host, int32_t n) {
   return (int32_t)cudaMemcpyFromSymbol(host, vv::vv_fs_trace, sizeof(long long) * (size_t)n);

@@ -75,6 +75,7 @@ SIGNATURES = {
     "vv_test_gelu": (_I32, [_P, _P, _I32, _P]),
     "vv_kernel_head": (_I32, [_P, _P, _P, _I32, _I32, _I32, _P]),
     "vv_pcm16": (_I32, [_P, _I32, _I32, _I64, _I64, _P, _P, _P]),
+    "vv_pcm16_static": (_I32, [_P, _I32, _I32, _I64, _I64, _P, _P]),
     "vv_encoder_create": (_I32, [C.POINTER(VvConfig), C.POINTER(_P)]),
     "vv_encoder_destroy": (_I32, [_P]),
     "vv_encoder_load_tensor": (_I32, [_P, C.c_char_p, _P, _I32, C.POINTER(_I64), _I32, _I32]),
