@@ -132,7 +132,7 @@ block_fused_kernel(const __grid_constant__ CUtensorMap tmO, const __grid_constan
   using L = BlockFusedCfg<C>;
   constexpr int NA = L::NA, NY = L::NY, NCH = L::NCH, NBOX = L::NBOX, MXW = L::MXW, LPR = L::LPR;
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  uint8_t* smem = smem_align_1k(smem_raw);
   uint8_t* sW1 = smem + L::OFF_W1;
   uint8_t* sW2 = smem + L::OFF_W2;
   uint8_t* sA = smem + L::OFF_A;

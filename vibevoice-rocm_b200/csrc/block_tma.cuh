@@ -21,6 +21,12 @@
 //     chunks (HC = 128: the a tile is read twice per tile from shared memory instead of four times).
 //   * E2 (thread = row): out = y + d2 + gb2, in place in the slot -> TMA store; the slot then goes back to the loader.
 // Mixer instruction count per tile: ~2 200 (C = 64) instead of ~4 800; no global load instruction on the hot path.
+// Second build, after ncu of the first (profiles/block_tma_s{5,6}_r02.txt: DRAM traffic = algorithmic bytes, the busiest
+// unit is the LSU DATA PIPE at 60 / 75 % -- ~1340 shared-memory wavefronts per tile at C = 32, conflict-free, plus ~790
+// wavefronts of warp-uniform __ldg bias loads): (1) b1 and ffn_gamma * b2 travel in the kernel's CONSTANT bank (by-value
+// arguments), so E1 / S3 read them as constant operands instead of LSU loads; (2) S3 -- thread = row = TMEM lane, y already
+// in registers -- writes y + gb2 into the D2 ACCUMULATOR with tcgen05.st and GEMM 2 accumulates on top of it, so E2 no
+// longer re-reads y from shared memory (tcgen05.ld -> st.shared -> TMA store); four D2 buffers keep S3 ahead of E2.
 // Streaming (STATE): the first tile of an item patches its 6 halo rows from the stream's cached raw rows before S1 runs;
 // S1 saves the item's last 6 raw rows (reference :327-382; same state layout as block_fused_kernel / mixer_kernel).
 #pragma once
@@ -33,7 +39,7 @@
 namespace vv {
 
 #ifndef VV_BT_HC
-#define VV_BT_HC 128        // hidden units per GEMM-1 chunk (64 or 128)
+#define VV_BT_HC 64         // hidden units per GEMM-1 chunk (64, or 128 at C = 64 with two D2 buffers)
 #endif
 #ifndef VV_BT_NX64
 #define VV_BT_NX64 3        // x/y ring slots at C = 64 (34 KB each)
@@ -51,8 +57,8 @@ struct BlockTmaArgs {
   const float* dw_w;         // [7][C] tap-major
   const float* dw_b;         // [C]
   const float* gamma;        // [C]
-  const float* b1;           // [4C]  pre-scaled by 0.5 like W1
-  const float* gb2;          // [C]   ffn_gamma * b2
+  float b1c[256];            // [4C]  linear1 bias pre-scaled by 0.5 like W1: lives in the constant bank with the other
+  float gb2c[64];            // [C]   arguments; ffn_gamma * b2
   __nv_bfloat16* out_bf16;   // optional padded bf16 copy: [nbatch, ob_rpb, C], row t of an item lands at row ob_off + t
   long long ob_rpb;
   int ob_off;
@@ -87,14 +93,15 @@ struct BlockTmaCfg {
   static constexpr int OFF_XY = OFF_A + NA * A_BYTES;
   static constexpr int OFF_RSTD = OFF_XY + NX * XY_BYTES;
   static constexpr int OFF_BAR = OFF_RSTD + NX * RSTD_STRIDE * 4;
-  static constexpr int NBARS = 1 + 5 * NX + 2 * NA + 12;
+  static constexpr int ND2 = (3 * HC + 4 * C <= 512) ? 4 : 2;      // D2 accumulators (S3 preloads one while E2 drains another)
+  static constexpr int NBARS = 1 + 5 * NX + 2 * NA + 8 + 3 * ND2;
   static constexpr int TOTAL = OFF_BAR + 512 + 1024;
   static_assert(NBARS * 8 + 8 <= 512, "barrier block");
   static_assert(OFF_XY % 1024 == 0 && XBOX_BYTES % 1024 == 0, "swizzled boxes need 1 KB aligned bases");
   static_assert(TOTAL <= 232448, "exceeds the 227 KB dynamic shared memory limit");
-  static constexpr uint32_t TMEM_COLS = 512;         // D1: 2 x HC at 0; H: 2 x HC/2 at 2 HC; D2: 2 x C at 3 HC
+  static constexpr uint32_t TMEM_COLS = 512;         // D1: 2 x HC at 0; H: 2 x HC/2 at 2 HC; D2: ND2 x C at 3 HC
   static constexpr uint32_t H_COL0 = 2 * HC, D2_COL0 = 3 * HC;
-  static_assert(3 * HC + 2 * C <= 512, "tensor memory columns");
+  static_assert(3 * HC + ND2 * C <= 512, "tensor memory columns");
   // register budgets (setmaxnreg draws from the CTA's launch allocation: threads x launch registers)
   static constexpr int REG_LAUNCH = (65536 / THREADS) / 8 * 8;
   static constexpr int REG_E1 = 64, REG_E2 = 64, REG_S1 = 40, REG_S3 = (C == 64) ? 96 : 64, REG_S2 = 112, REG_CTRL = 32;
@@ -118,7 +125,7 @@ block_tma_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
   using L = BlockTmaCfg<C>;
   constexpr int NX = L::NX, NA = L::NA, NCH = L::NCH, NBOX = L::NBOX, HC = L::HC, LPR = L::LPR, R = L::R;
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  uint8_t* smem = smem_align_1k(smem_raw);
   uint8_t* sW1 = smem + L::OFF_W1;
   uint8_t* sW2 = smem + L::OFF_W2;
   uint8_t* sA = smem + L::OFF_A;
@@ -137,9 +144,11 @@ block_tma_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
   uint64_t* d1_empty = d1_full + 2;        // [2]
   uint64_t* h_full = d1_empty + 2;         // [2]
   uint64_t* h_empty = h_full + 2;          // [2]
-  uint64_t* d2_full = h_empty + 2;         // [2]
-  uint64_t* d2_empty = d2_full + 2;        // [2]
-  uint32_t* tmem_slot = (uint32_t*)(d2_empty + 2);
+  constexpr int ND2 = L::ND2;
+  uint64_t* d2_full = h_empty + 2;         // [ND2] GEMM 2 finished the tile's accumulator
+  uint64_t* d2_empty = d2_full + ND2;      // [ND2] E2 has read it
+  uint64_t* d2_init = d2_empty + ND2;      // [ND2] S3 preloaded it with y + gb2
+  uint32_t* tmem_slot = (uint32_t*)(d2_init + ND2);
 
   // hardware warps: [0, 8) E1, [8, 12) E2, [12, 16) S1, [16, 20) S3, [20, 24) S2, [24, 28): loader, G1, G2, store
   const int warp = threadIdx.x >> 5;
@@ -174,8 +183,11 @@ block_tma_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
       mbar_init(&d1_empty[i], L::E1W / 2);
       mbar_init(&h_full[i], L::E1W / 2);
       mbar_init(&h_empty[i], 1);
+    }
+    for (int i = 0; i < ND2; ++i) {
       mbar_init(&d2_full[i], 1);
       mbar_init(&d2_empty[i], L::E2W);
+      mbar_init(&d2_init[i], L::S3W);
     }
     fence_mbar_init();
   }
@@ -250,8 +262,9 @@ block_tma_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
         mbar_wait(w_full, 0);
         int g = 0;
         for (int it = 0; it < my_tiles; ++it) {
-          const int d2b = it & 1;
-          mbar_wait_sleep(&d2_empty[d2b], (uint32_t)(((it >> 1) & 1) ^ 1), 64);
+          const int d2b = it % ND2;
+          mbar_wait_sleep(&d2_init[d2b], (uint32_t)((it / ND2) & 1), 64);     // the accumulator holds y + gb2
+          tc_fence_after();
           const uint32_t d = tmem_base + L::D2_COL0 + (uint32_t)(d2b * C);
 #pragma unroll 1
           for (int j = 0; j < NCH; ++j, ++g) {
@@ -263,7 +276,7 @@ block_tma_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
             for (int kk = 0; kk < HC / 16; ++kk) {
               // hidden units [j HC + 16 kk, +16): K-block (j HC + 16 kk) / 64 of W2, 16-element step (kk & 3) inside it
               const uint64_t dw = dw0 + (uint64_t)((((j * HC + kk * 16) >> 6) * C * 128) >> 4) + (uint64_t)((kk & 3) * 2);
-              umma_bf16_ts(d, ah + (uint32_t)(kk * 8), dw, idesc2, (j | kk) != 0);
+              umma_bf16_ts(d, ah + (uint32_t)(kk * 8), dw, idesc2, 1u);
             }
             umma_commit(&h_empty[hb]);
           }
@@ -300,7 +313,7 @@ block_tma_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
     for (int g = grp; g < total_g; g += 2) {
       const int j = g % NCH;
       const uint32_t ph = (uint32_t)((g >> 1) & 1);
-      const float* bp = p.b1 + j * HC;
+      const float* bp = p.b1c + j * HC;                  // constant bank (by-value kernel argument)
       mbar_wait(&d1_full[grp], ph);
       tc_fence_after();
 #pragma unroll
@@ -316,12 +329,11 @@ block_tma_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
         uint32_t hv[16];
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
-          const float4 b0 = __ldg(reinterpret_cast<const float4*>(bp + hf * 32 + i * 8));
-          const float4 b1v = __ldg(reinterpret_cast<const float4*>(bp + hf * 32 + i * 8 + 4));
-          hv[i * 4 + 0] = gelu2_bias_pack(__uint_as_float(v[i * 8 + 0]), __uint_as_float(v[i * 8 + 1]), b0.x, b0.y);
-          hv[i * 4 + 1] = gelu2_bias_pack(__uint_as_float(v[i * 8 + 2]), __uint_as_float(v[i * 8 + 3]), b0.z, b0.w);
-          hv[i * 4 + 2] = gelu2_bias_pack(__uint_as_float(v[i * 8 + 4]), __uint_as_float(v[i * 8 + 5]), b1v.x, b1v.y);
-          hv[i * 4 + 3] = gelu2_bias_pack(__uint_as_float(v[i * 8 + 6]), __uint_as_float(v[i * 8 + 7]), b1v.z, b1v.w);
+          const float* bq = bp + hf * 32 + i * 8;
+          hv[i * 4 + 0] = gelu2_bias_pack(__uint_as_float(v[i * 8 + 0]), __uint_as_float(v[i * 8 + 1]), bq[0], bq[1]);
+          hv[i * 4 + 1] = gelu2_bias_pack(__uint_as_float(v[i * 8 + 2]), __uint_as_float(v[i * 8 + 3]), bq[2], bq[3]);
+          hv[i * 4 + 2] = gelu2_bias_pack(__uint_as_float(v[i * 8 + 4]), __uint_as_float(v[i * 8 + 5]), bq[4], bq[5]);
+          hv[i * 4 + 3] = gelu2_bias_pack(__uint_as_float(v[i * 8 + 6]), __uint_as_float(v[i * 8 + 7]), bq[6], bq[7]);
         }
         if (hf == 0) {
           mbar_wait(&h_empty[grp], ph ^ 1);          // GEMM 2 has consumed this group's previous H chunk
@@ -335,19 +347,20 @@ block_tma_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
       if (lane == 0) mbar_arrive(&h_full[grp]);
     }
   } else if (warp < WARP_S1) {
-    // ===== E2: out = y + (D2 + gb2), in place in the slot (thread = row) -> TMA store ==============================
+    // ===== E2: the accumulator already holds out = (y + gb2) + H W2^T: tcgen05.ld -> slot (thread = row) -> TMA store ====
     reg_set<L::REG_LAUNCH, L::REG_E2>();
     const int q = warp & 3;
     const int r = q * 32 + lane;
     for (int it = 0; it < my_tiles; ++it) {
-      const int d2b = it & 1, s = it % NX;
+      const int d2b = it % ND2, s = it % NX;
       int b, t0;
       tile_of(it, b, t0);
       const int t = t0 + r;
       const bool valid = t < p.rows_pb;
       const long long brow = (long long)b * p.ob_rpb + p.ob_off + t;
-      mbar_wait(&y_full[s], (uint32_t)((it / NX) & 1));      // (long complete: orders this thread after S2's stores)
-      mbar_wait(&d2_full[d2b], (uint32_t)((it >> 1) & 1));   // implies S3 is done with the slot (a_full -> G1 -> ... -> G2)
+      // d2_full implies that S3 is done with the slot's y rows (its preload of this accumulator came after it read them,
+      // and GEMM 2 waited for the preload), so the slot can be overwritten with the block output
+      mbar_wait(&d2_full[d2b], (uint32_t)((it / ND2) & 1));
       tc_fence_after();
       uint8_t* slot = sXY + s * L::XY_BYTES;
 #pragma unroll
@@ -356,27 +369,18 @@ block_tma_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
         tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + L::D2_COL0 + (uint32_t)(d2b * C + c * 32), v);
         tmem_ld_wait();
         uint8_t* box = slot + c * L::XBOX_BYTES;
-        float o[32];
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          float4* cell = reinterpret_cast<float4*>(box + xy_cell(L::HALO + r, i));
-          const float4 yv = *cell;
-          const float4 gv = __ldg(reinterpret_cast<const float4*>(p.gb2 + c * 32 + i * 4));
-          o[i * 4 + 0] = (yv.x + gv.x) + __uint_as_float(v[i * 4 + 0]);
-          o[i * 4 + 1] = (yv.y + gv.y) + __uint_as_float(v[i * 4 + 1]);
-          o[i * 4 + 2] = (yv.z + gv.z) + __uint_as_float(v[i * 4 + 2]);
-          o[i * 4 + 3] = (yv.w + gv.w) + __uint_as_float(v[i * 4 + 3]);
-          *cell = make_float4(o[i * 4], o[i * 4 + 1], o[i * 4 + 2], o[i * 4 + 3]);
-        }
+        for (int i = 0; i < 8; ++i)
+          *reinterpret_cast<uint4*>(box + xy_cell(L::HALO + r, i)) = make_uint4(v[i * 4], v[i * 4 + 1], v[i * 4 + 2], v[i * 4 + 3]);
         if (valid && p.out_bf16 != nullptr) {
           __nv_bfloat16* bp = p.out_bf16 + brow * C + c * 32;
 #pragma unroll
           for (int i = 0; i < 4; ++i) {
             uint4 pk;
-            pk.x = pack_bf16x2(o[i * 8 + 0], o[i * 8 + 1]);
-            pk.y = pack_bf16x2(o[i * 8 + 2], o[i * 8 + 3]);
-            pk.z = pack_bf16x2(o[i * 8 + 4], o[i * 8 + 5]);
-            pk.w = pack_bf16x2(o[i * 8 + 6], o[i * 8 + 7]);
+            pk.x = pack_bf16x2(__uint_as_float(v[i * 8 + 0]), __uint_as_float(v[i * 8 + 1]));
+            pk.y = pack_bf16x2(__uint_as_float(v[i * 8 + 2]), __uint_as_float(v[i * 8 + 3]));
+            pk.z = pack_bf16x2(__uint_as_float(v[i * 8 + 4]), __uint_as_float(v[i * 8 + 5]));
+            pk.w = pack_bf16x2(__uint_as_float(v[i * 8 + 6]), __uint_as_float(v[i * 8 + 7]));
             *reinterpret_cast<uint4*>(bp + i * 8) = pk;
           }
         }
@@ -507,6 +511,31 @@ block_tma_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
       fence_proxy_async_smem();                 // a tile (generic-proxy stores) -> visible to tcgen05.mma
       __syncwarp();
       if (lane == 0) mbar_arrive(&a_full[sa]);
+      // D2[it % ND2] = y + gb2 (thread = row = TMEM lane; this warp's lane quarter is warp % 4): GEMM 2 accumulates on it
+      const int d2b = it % ND2;
+      mbar_wait(&d2_empty[d2b], (uint32_t)(((it / ND2) & 1) ^ 1));
+      tc_fence_after();
+      const uint32_t daddr = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + L::D2_COL0 + (uint32_t)(d2b * C);
+#pragma unroll
+      for (int hcol = 0; hcol < C / 16; ++hcol) {        // 16 columns = 4 cells of 4 floats per tcgen05.st
+        uint32_t w[16];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const int cell = hcol * 4 + i;                 // channels [4 cell, 4 cell + 4)
+          float a0, a1, a2, a3;
+          f2_unpack(y[cell].x, a0, a1);
+          f2_unpack(y[cell].y, a2, a3);
+          w[i * 4 + 0] = __float_as_uint(a0 + p.gb2c[cell * 4 + 0]);
+          w[i * 4 + 1] = __float_as_uint(a1 + p.gb2c[cell * 4 + 1]);
+          w[i * 4 + 2] = __float_as_uint(a2 + p.gb2c[cell * 4 + 2]);
+          w[i * 4 + 3] = __float_as_uint(a3 + p.gb2c[cell * 4 + 3]);
+        }
+        tmem_st_32x16(daddr + (uint32_t)(hcol * 16), w);
+      }
+      tmem_st_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&d2_init[d2b]);
     }
   } else {
     // ===== S2: depthwise causal conv k7 over the normalised rows; lane = 4 channels, strip = R consecutive rows =======

@@ -74,7 +74,7 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   constexpr uint32_t TMEM_COLS = 512;
   constexpr uint32_t D2_COL0 = 256;
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  uint8_t* smem = smem_align_1k(smem_raw);
   uint8_t* sW1 = smem + L::OFF_W1;
   uint8_t* sW2 = smem + L::OFF_W2;
   uint8_t* sA = smem + L::OFF_A;

@@ -87,7 +87,7 @@ ffn_stream_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   constexpr int NA = L::NA, S1 = L::S1, S2 = L::S2, NY = L::NY, NCH = L::NCH, KB = L::KB, NBOX = L::NBOX;
   constexpr int ND1 = L::ND1;
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  uint8_t* smem = smem_align_1k(smem_raw);
   uint8_t* sA = smem + L::OFF_A;
   uint8_t* sW1 = smem + L::OFF_W1;
   uint8_t* sW2 = smem + L::OFF_W2;

@@ -70,7 +70,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   constexpr int B_BYTES = BN * BK * 2;
   constexpr int ROW_BYTES = BK * 2;            // 128 (SWIZZLE_128B) or 64 (SWIZZLE_64B)
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  uint8_t* smem = smem_align_1k(smem_raw);
   uint8_t* sA = smem;
   uint8_t* sB = smem + (size_t)g.stages * A_BYTES;
   uint64_t* bars = (uint64_t*)(sB + (size_t)g.stages * B_BYTES);

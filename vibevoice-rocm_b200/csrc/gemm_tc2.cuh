@@ -83,7 +83,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   constexpr int EW = G2Warps<EPI>::EPI_WARPS;
   constexpr int CPW = SUBW / (EW / 4);      // columns per epilogue warp inside a sub-tile: 64 or 32
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  uint8_t* smem = smem_align_1k(smem_raw);
   uint8_t* sA = smem + Cfg::OFF_RING;
   uint8_t* sB = sA + S * G2_A_BYTES;
   uint8_t* sStg = smem + Cfg::OFF_STG;

@@ -12,6 +12,16 @@ __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));
 }
 
+// 1 KB-aligned start of the dynamic shared memory (swizzled TMA boxes and UMMA operand tiles need it).  The offset is
+// computed in the SHARED window and added to the __shared__ array itself: rounding the GENERIC pointer through uintptr_t
+// (what every kernel here did until round 2) makes the compiler lose the address space, and every later access becomes a
+// generic LD.E / ST.E with 64-bit addressing, tracked on the long scoreboard, instead of LDS / STS (found in the SASS of
+// block_tma_kernel: 43 LD.E + 22 ST.E against 2 LDS + 3 STS).
+__device__ __forceinline__ uint8_t* smem_align_1k(uint8_t* dyn_smem) {
+  const uint32_t base = static_cast<uint32_t>(__cvta_generic_to_shared(dyn_smem));
+  return dyn_smem + (((base + 1023u) & ~1023u) - base);
+}
+
 __device__ __forceinline__ bool elect_one() {
   uint32_t pred;
   asm volatile(

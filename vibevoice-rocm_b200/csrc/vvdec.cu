@@ -429,6 +429,8 @@ bool Packer::block(const std::string& p, int C, BlockW& bw) {
     dense(bw.lin1f, to_bf16(w1f), b1h, 4 * C, C, 1);
     dense(bw.lin2f, to_bf16(w2f), *b2, C, 4 * C, 1);
     bw.gb2 = upload(gb2);
+    bw.h_b1c = b1h;
+    bw.h_gb2c = gb2;
   }
   if (status == VV_OK && C == 128) {   // ffn_stream_kernel reads linear1 in chunks of 64 hidden units
     const uint64_t dims[2] = {(uint64_t)C, (uint64_t)(4 * C)};
@@ -808,7 +810,12 @@ int launch_block_tma(vv_decoder* d, int C, const BlockW& bw, const float* x, flo
   BlockTmaArgs a;
   a.x = x; a.nbatch = nbatch; a.rows_pb = rows_pb; a.tiles_pb = (rows_pb + 127) / 128; a.eps = d->cfg.eps;
   a.norm_w = bw.norm_w; a.dw_w = bw.dw_w; a.dw_b = bw.dw_b; a.gamma = bw.gamma;
-  a.b1 = bw.lin1f.bias; a.gb2 = bw.gb2; a.out_bf16 = out_bf16;
+  a.out_bf16 = out_bf16;
+  if (bw.h_b1c.size() != (size_t)4 * C || bw.h_gb2c.size() != (size_t)C || 4 * C > 256) { set_error("block_tma: constants missing"); return VV_ERR_NOT_FINALIZED; }
+  memset(a.b1c, 0, sizeof(a.b1c));
+  memset(a.gb2c, 0, sizeof(a.gb2c));
+  memcpy(a.b1c, bw.h_b1c.data(), sizeof(float) * 4 * C);
+  memcpy(a.gb2c, bw.h_gb2c.data(), sizeof(float) * C);
   a.st = make_state_ref(st, slots, bw.state_off);
   a.ob_rpb = po.rpb > 0 ? po.rpb : rows_pb + po.off; a.ob_off = po.off;
   if ((long long)nbatch * a.tiles_pb >= (1LL << 31) / 8) { set_error("block_tma: too many tiles"); return VV_ERR_BAD_SHAPE; }
