@@ -37,6 +37,12 @@ struct FfnFusedArgs {
   __nv_bfloat16* out_bf16; // optional padded bf16 copy: [batch, ob_rpb, C], row t of an item lands at row ob_off + t
   long long ob_rpb;        //   (decoder: ob_rpb = rows_pb + 1, ob_off = 1 = the upsampler halo row)
   int ob_off;
+  // ffn_stream_kernel (C = 128) reads the three per-channel vectors from the CONSTANT bank (by-value argument) instead of
+  // warp-uniform __ldg loads: ncu of block_tma_kernel showed such loads costing ~4 LSU data-pipe wavefronts each, a third
+  // of that kernel's LSU traffic (profiles/block_tma_s6_r02.txt).  Filled by the host when C == 128.
+  float b1c[512];          // = b1 (pre-scaled by 0.5)
+  float b2c[128];
+  float gammac[128];
 };
 
 template <int C>

@@ -27,6 +27,9 @@
 #include "epilogue.cuh"
 #include "ffn_fused.cuh"   // FfnFusedArgs
 
+#ifndef VV_FS_CONST
+#define VV_FS_CONST 1     // 1: b1 / b2 / ffn_gamma from the constant bank (by-value kernel argument); 0: plain global loads
+#endif
 namespace vv {
 
 #ifdef VV_FS_TRACE     // timeline instrumentation (A/B builds only): clock64 stamps of CTA 0 for chunks [TR_G0, TR_G0+32)
@@ -290,7 +293,11 @@ ffn_stream_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
 #pragma unroll
       for (int hf = 0; hf < NHF; ++hf) {
         const int ch = ch0 + hf;                          // 32-column half of the 64-column chunk
-        const float* bp = p.b1 + j * L::HC + ch * 32;
+#if VV_FS_CONST
+        const float* bp = p.b1c + j * L::HC + ch * 32;    // constant bank
+#else
+        const float* bp = p.b1 + j * L::HC + ch * 32;     // global (A/B build: -DVV_FS_CONST=0)
+#endif
         uint32_t v[32];
         tmem_ld_32x32(taddr + (uint32_t)(db * L::HC + ch * 32), v);
         tmem_ld_wait();
@@ -303,12 +310,11 @@ ffn_stream_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         uint32_t hv[16];
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
-          const float4 b0 = __ldg(reinterpret_cast<const float4*>(bp + i * 8));
-          const float4 b1v = __ldg(reinterpret_cast<const float4*>(bp + i * 8 + 4));
-          hv[i * 4 + 0] = gelu2_bias_pack(__uint_as_float(v[i * 8 + 0]), __uint_as_float(v[i * 8 + 1]), b0.x, b0.y);
-          hv[i * 4 + 1] = gelu2_bias_pack(__uint_as_float(v[i * 8 + 2]), __uint_as_float(v[i * 8 + 3]), b0.z, b0.w);
-          hv[i * 4 + 2] = gelu2_bias_pack(__uint_as_float(v[i * 8 + 4]), __uint_as_float(v[i * 8 + 5]), b1v.x, b1v.y);
-          hv[i * 4 + 3] = gelu2_bias_pack(__uint_as_float(v[i * 8 + 6]), __uint_as_float(v[i * 8 + 7]), b1v.z, b1v.w);
+          const float* bq = bp + i * 8;
+          hv[i * 4 + 0] = gelu2_bias_pack(__uint_as_float(v[i * 8 + 0]), __uint_as_float(v[i * 8 + 1]), bq[0], bq[1]);
+          hv[i * 4 + 1] = gelu2_bias_pack(__uint_as_float(v[i * 8 + 2]), __uint_as_float(v[i * 8 + 3]), bq[2], bq[3]);
+          hv[i * 4 + 2] = gelu2_bias_pack(__uint_as_float(v[i * 8 + 4]), __uint_as_float(v[i * 8 + 5]), bq[4], bq[5]);
+          hv[i * 4 + 3] = gelu2_bias_pack(__uint_as_float(v[i * 8 + 6]), __uint_as_float(v[i * 8 + 7]), bq[6], bq[7]);
         }
         if (hf == 0) {
           if (q == 0 && ch0 == 0 && lane == 0) VV_TR(9, g);
@@ -354,12 +360,17 @@ ffn_stream_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
           const int col = c * 32 + i * 4;
           float4* cell = reinterpret_cast<float4*>(rrow + ((i ^ (r & 7)) * 16));
           const float4 rv = *cell;
-          const float4 bv = __ldg(reinterpret_cast<const float4*>(p.b2 + col));
-          const float4 gv = __ldg(reinterpret_cast<const float4*>(p.gamma + col));
-          x[i * 4 + 0] = fmaf(gv.x, __uint_as_float(v[i * 4 + 0]) + bv.x, rv.x);
-          x[i * 4 + 1] = fmaf(gv.y, __uint_as_float(v[i * 4 + 1]) + bv.y, rv.y);
-          x[i * 4 + 2] = fmaf(gv.z, __uint_as_float(v[i * 4 + 2]) + bv.z, rv.z);
-          x[i * 4 + 3] = fmaf(gv.w, __uint_as_float(v[i * 4 + 3]) + bv.w, rv.w);
+#if VV_FS_CONST
+          const float* bv = p.b2c + col;                  // constant bank, same arithmetic as before
+          const float* gv = p.gammac + col;
+#else
+          const float* bv = p.b2 + col;
+          const float* gv = p.gamma + col;
+#endif
+          x[i * 4 + 0] = fmaf(gv[0], __uint_as_float(v[i * 4 + 0]) + bv[0], rv.x);
+          x[i * 4 + 1] = fmaf(gv[1], __uint_as_float(v[i * 4 + 1]) + bv[1], rv.y);
+          x[i * 4 + 2] = fmaf(gv[2], __uint_as_float(v[i * 4 + 2]) + bv[2], rv.z);
+          x[i * 4 + 3] = fmaf(gv[3], __uint_as_float(v[i * 4 + 3]) + bv[3], rv.w);
           *cell = make_float4(x[i * 4], x[i * 4 + 1], x[i * 4 + 2], x[i * 4 + 3]);
         }
         if (valid && p.out_bf16 != nullptr) {

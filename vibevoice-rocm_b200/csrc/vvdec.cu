@@ -417,6 +417,12 @@ bool Packer::block(const std::string& p, int C, BlockW& bw) {
     dense(bw.lin1, to_bf16(w1h), b1h, 4 * C, C, 1);
   }
   dense(bw.lin2, to_bf16(*w2), *b2, C, 4 * C, 1);
+  if (C == 128) {                      // host copies for ffn_stream_kernel's by-value constants
+    bw.h_b1 = *b1;
+    for (float& v : bw.h_b1) v *= 0.5f;
+    bw.h_b2 = *b2;
+    bw.h_fgamma = *fg;
+  }
   if (status == VV_OK && C <= 64) {    // operands of block_tma_kernel with the per-channel scales folded in
     std::vector<float> w1f(*w1), b1h(*b1), w2f(*w2), gb2((size_t)C);
     for (int n = 0; n < 4 * C; ++n)
@@ -762,6 +768,10 @@ int launch_ffn_fused(vv_decoder* d, int C, const BlockW& bw, const __nv_bfloat16
   if (C == 32) return launch_ffn_fused_inst<32>(d, tmA, tmR, tmO, bw, fa, s);
   if (C == 64) return launch_ffn_fused_inst<64>(d, tmA, tmR, tmO, bw, fa, s);
   // C = 128: hidden on chip, weights streamed (ffn_stream.cuh); a is read in [128 rows x 64] K blocks
+  if (bw.h_b1.size() != 512 || bw.h_b2.size() != 128 || bw.h_fgamma.size() != 128) { set_error("ffn_stream: constants missing"); return VV_ERR_NOT_FINALIZED; }
+  memcpy(fa.b1c, bw.h_b1.data(), sizeof(fa.b1c));
+  memcpy(fa.b2c, bw.h_b2.data(), sizeof(fa.b2c));
+  memcpy(fa.gammac, bw.h_fgamma.data(), sizeof(fa.gammac));
   rc = ensure_smem(ffn_stream_kernel<128>, (int)FfnStreamCfg<128>::TOTAL, d->cfg.device);
   if (rc != VV_OK) return rc;
   const int num_sms = d->num_sms;

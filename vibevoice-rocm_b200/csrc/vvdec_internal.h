@@ -44,6 +44,7 @@ struct BlockW {
   // lin2f = diag(ffn_gamma) * W2, gb2 = ffn_gamma * b2  (lin1f.bias = 0.5 * b1 as in lin1)
   DenseW lin1f, lin2f;
   float* gb2 = nullptr;
+  std::vector<float> h_b1, h_b2, h_fgamma;   // C == 128: 0.5 * b1, b2, ffn_gamma for ffn_stream_kernel's constant-bank arguments
   std::vector<float> h_b1c, h_gb2c;   // host copies: block_tma_kernel takes 0.5 * b1 and gb2 as by-value (constant-bank) arguments
   long long state_off = 0;      // fp32 [6][C]
 };
