@@ -47,6 +47,9 @@ namespace vv {
 #ifndef VV_BT_NX32
 #define VV_BT_NX32 6        // at C = 32 (17 KB each)
 #endif
+#ifndef VV_BT_NA64
+#define VV_BT_NA64 2        // GEMM-1 operand (a) tiles at C = 64 (16 KB each); 1 frees room for a fourth x/y slot
+#endif
 
 struct BlockTmaArgs {
   int nbatch, rows_pb;
@@ -77,7 +80,7 @@ struct BlockTmaCfg {
   static constexpr int XBOX_BYTES = XROWS * 128;     // 17 408 = 17 KB: box bases stay 1 KB aligned
   static constexpr int XY_BYTES = NBOX * XBOX_BYTES;
   static constexpr int NX = (C == 64) ? VV_BT_NX64 : VV_BT_NX32;
-  static constexpr int NA = (C == 64) ? 2 : 4;
+  static constexpr int NA = (C == 64) ? VV_BT_NA64 : 4;
   static constexpr int E1W = 8, E2W = 4, S1W = 4, S3W = 4, S2W = 4, CTRL = 4;
   static constexpr int STRIPS = S2W * 32 / LPR;      // 8 (C = 64) or 16 (C = 32)
   static constexpr int R = 128 / STRIPS;             // rows per strip: 16 or 8
