@@ -283,6 +283,46 @@ int32_t vv_pcm16(const void* wave, int32_t wave_dtype, int32_t B, int64_t L, int
 int32_t vv_pcm16_static(const void* wave, int32_t wave_dtype, int32_t B, int64_t L, int64_t row_stride, int16_t* pcm,
                         void* cuda_stream);
 
+/* ---- diffusion-head sampler (the step right before the decoder) -------------------------------------
+ * Replaces VibeVoiceForConditionalGenerationInference.sample_speech_tokens (modeling_vibevoice_inference.py:695-708): for n
+ * streams, ddpm_num_inference_steps x [ VibeVoiceDiffusionHead.forward on 2n rows (modular_vibevoice_diffusion_head.py:
+ * 254-280), classifier-free guidance (:703-705), DPMSolverMultistepScheduler.step (vibevoice/schedule/dpm_solver.py:
+ * 935-1022) ] with the scheduler as the model builds it (modeling_vibevoice.py:138-142: cosine betas, v-prediction; every
+ * other argument at its default: order 2, dpmsolver++, midpoint, lower_order_final, final sigma 0, linspace spacing).
+ * Tensor names are the head's own state-dict keys ("noisy_images_proj.weight", "layers.0.ffn.gate_proj.weight", ...;
+ * under "model.prediction_head." in the full model).  The initial noise (torch.randn, :698) is an INPUT. */
+typedef struct vv_sampler_config {
+  int32_t hidden;        /* VibeVoiceDiffusionHeadConfig.hidden_size (1536 / 3584); multiple of 128, <= 4096      */
+  int32_t layers;        /* head_layers (4)                                                                      */
+  int32_t ffn;           /* int(hidden_size * head_ffn_ratio) (4608 / 10752); multiple of 64                     */
+  int32_t latent;        /* latent_size (64; the kernels take exactly 64)                                        */
+  float   eps;           /* rms_norm_eps (1e-5)                                                                  */
+  int32_t train_steps;   /* ddpm_num_steps (1000)                                                                */
+  int32_t device;
+} vv_sampler_config;
+typedef struct vv_sampler vv_sampler;
+int32_t vv_sampler_create(const vv_sampler_config* cfg, vv_sampler** out);
+int32_t vv_sampler_destroy(vv_sampler* sp);
+int32_t vv_sampler_load_tensor(vv_sampler* sp, const char* name, const void* data, int32_t dtype, const int64_t* shape,
+                               int32_t ndim, int32_t is_device);
+int32_t vv_sampler_finalize(vv_sampler* sp);
+int64_t vv_sampler_param_count(const vv_sampler* sp);
+/* Solver coefficients and timestep embeddings for a step count (set_timesteps, :321-424; TimestepEmbedder :48-93), computed on
+ * the host in fp32 and uploaded; allocates once per distinct `steps`.  vv_sampler_sample calls it lazily: call it yourself
+ * before capturing a CUDA graph. */
+int32_t vv_sampler_prepare(vv_sampler* sp, int32_t steps);
+int64_t vv_sampler_workspace_bytes(const vv_sampler* sp, int32_t n);
+/* condition, neg_condition: device [n, hidden] (f32 | bf16);  noise: device fp32 [n, latent] = the initial latent;
+ * out: device fp32 [n, latent] = sample_speech_tokens' return value.  Enqueues on the stream, never synchronises. */
+int32_t vv_sampler_sample(vv_sampler* sp, const void* condition, const void* neg_condition, int32_t cond_dtype, int32_t n,
+                          const float* noise, float cfg_scale, int32_t steps, float* out, void* workspace,
+                          int64_t workspace_bytes, void* cuda_stream);
+/* Per-kernel hook (tests): ONE head forward (:254-280) on R rows (R even): noisy fp32 [R, latent], one timestep for all rows,
+ * condition [R, hidden] -> v fp32 [R, latent].  Synchronises the stream (it uploads the timestep embedding). */
+int32_t vv_sampler_head(vv_sampler* sp, const float* noisy, float timestep, const void* condition, int32_t cond_dtype,
+                        int32_t R, float* v_out, void* workspace, int64_t workspace_bytes, void* cuda_stream);
+int64_t vv_sampler_take_launch_count(vv_sampler* sp);
+
 /* The GELU of the FFN epilogue (:589, :594), alone: y[i] = gelu(x[i]); device pointers.  Accuracy test hook. */
 int32_t vv_test_gelu(const float* x, float* y, int32_t n, void* cuda_stream);
 

@@ -18,6 +18,7 @@
 #include "gemm_tc2.cuh"
 #include "encoder.cuh"
 #include "pcm16.cuh"
+#include "sampler.cuh"
 
 namespace vv {
 
@@ -1519,3 +1520,8 @@ extern "C" int32_t vv_debug_read_trace(long long* host, int32_t n) {
 // encoder path (TokenizerEncoder, :687-813)
 // =====================================================================================================
 #include "vvenc.inl"
+
+// =====================================================================================================
+// diffusion-head sampler
+// =====================================================================================================
+#include "vvsamp.inl"

@@ -33,6 +33,11 @@ class VvConfig(C.Structure):
     ]
 
 
+class VvSamplerConfig(C.Structure):
+    _fields_ = [("hidden", C.c_int32), ("layers", C.c_int32), ("ffn", C.c_int32), ("latent", C.c_int32), ("eps", C.c_float),
+                ("train_steps", C.c_int32), ("device", C.c_int32)]
+
+
 class VvProfileRecord(C.Structure):
     _fields_ = [("kind", C.c_int32), ("stage", C.c_int32), ("launches", C.c_int64), ("ms", C.c_double)]
 
@@ -75,6 +80,16 @@ SIGNATURES = {
     "vv_test_gelu": (_I32, [_P, _P, _I32, _P]),
     "vv_kernel_head": (_I32, [_P, _P, _P, _I32, _I32, _I32, _P]),
     "vv_pcm16": (_I32, [_P, _I32, _I32, _I64, _I64, _P, _P, _P]),
+    "vv_sampler_create": (_I32, [C.POINTER(VvSamplerConfig), C.POINTER(_P)]),
+    "vv_sampler_destroy": (_I32, [_P]),
+    "vv_sampler_load_tensor": (_I32, [_P, C.c_char_p, _P, _I32, C.POINTER(_I64), _I32, _I32]),
+    "vv_sampler_finalize": (_I32, [_P]),
+    "vv_sampler_param_count": (_I64, [_P]),
+    "vv_sampler_prepare": (_I32, [_P, _I32]),
+    "vv_sampler_workspace_bytes": (_I64, [_P, _I32]),
+    "vv_sampler_sample": (_I32, [_P, _P, _P, _I32, _I32, _P, C.c_float, _I32, _P, _P, _I64, _P]),
+    "vv_sampler_head": (_I32, [_P, _P, C.c_float, _P, _I32, _I32, _P, _P, _I64, _P]),
+    "vv_sampler_take_launch_count": (_I64, [_P]),
     "vv_pcm16_static": (_I32, [_P, _I32, _I32, _I64, _I64, _P, _P]),
     "vv_encoder_create": (_I32, [C.POINTER(VvConfig), C.POINTER(_P)]),
     "vv_encoder_destroy": (_I32, [_P]),
