@@ -332,6 +332,77 @@ def streaming_leg(dec, geom, dev, sd, n_streams=256, steps=300, warmup=30):
     return out
 
 
+def sampler_leg(dev, n_streams=256, steps=20, iters=20, parity=True):
+    """the diffusion-head sampler that produces the latents the decoder consumes -- sample_speech_tokens
+    (modeling_vibevoice_inference.py:695-708) for `n_streams` streams, `steps` DPM-Solver++ steps of the 1.5B model's head
+    (hidden 1536, 4 layers) on 2 x n_streams rows.  Per-call device time, eager and as one CUDA graph; two streams are
+    checked against the numpy oracle (fp32)."""
+    import numpy as np
+    import torch
+    import vvdec
+    from oracle.sampler_oracle import OracleSampler, SamplerGeometry, make_sampler_weights
+    og = SamplerGeometry()
+    w = make_sampler_weights(og, 2026)
+    smp = vvdec.B200DiffusionSampler(vvdec.SamplerGeometry(inference_steps=steps), device=dev.index)
+    smp.load_state_dict({k: torch.from_numpy(v) for k, v in w.items()})
+    gen = torch.Generator().manual_seed(6)
+    cond = torch.randn(n_streams, og.hidden, generator=gen).to(torch.bfloat16)
+    neg = torch.randn(n_streams, og.hidden, generator=gen).to(torch.bfloat16)
+    noise = torch.randn(n_streams, og.latent, generator=gen)
+    cd, nd, zd = cond.to(dev), neg.to(dev), noise.to(dev)
+
+    def call():
+        return smp.sample_speech_tokens(cd, nd, cfg_scale=3.0, noise=zd)
+
+    def timed(fn, k):
+        ts = []
+        for _ in range(k):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(); fn(); e1.record(); e1.synchronize()
+            ts.append(e0.elapsed_time(e1))
+        ts.sort()
+        return ts[len(ts) // 2]
+    for _ in range(3):
+        y = call()
+    torch.cuda.synchronize()
+    smp.take_launch_count()
+    eager = timed(call, iters)
+    launches = smp.take_launch_count() // iters
+    flop = 2.0 * steps * 2 * n_streams * ((3 * og.layers + 2) * og.hidden * og.hidden + og.layers * 3 * og.hidden * og.ffn
+                                          + 2 * og.hidden * og.latent)
+    out = {"workload": f"sample_speech_tokens, {n_streams} streams x {steps} steps, head hidden {og.hidden} x {og.layers} layers "
+                       f"({2 * n_streams} rows per head pass), bf16 conditions",
+           "eager_p50_ms": eager, "launches_per_call": int(launches), "tflops_eager": flop / (eager * 1e-3) / 1e12}
+    try:
+        side = torch.cuda.Stream(device=dev)
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            call()
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            yg = call()
+        for _ in range(3):
+            graph.replay()
+        torch.cuda.synchronize()
+        gms = timed(graph.replay, iters)
+        out.update({"graph_p50_ms": gms, "tflops_graph": flop / (gms * 1e-3) / 1e12,
+                    "graph_equals_eager": bool(torch.equal(yg, y))})
+    except Exception as e:
+        out["graph_error"] = f"{type(e).__name__}: {e}"[:200]
+    if parity:
+        k = 2
+        t0 = time.perf_counter()
+        ref = OracleSampler(w, og).sample(cond[:k].float().numpy(), neg[:k].float().numpy(), noise[:k].numpy(), cfg_scale=3.0, steps=steps)
+        sub = smp.sample_speech_tokens(cd[:k], nd[:k], cfg_scale=3.0, noise=zd[:k])
+        m = _verdict(_metrics(sub.float().cpu(), torch.from_numpy(ref)))
+        m.update({"what": f"{k} streams vs the numpy oracle (fp32)", "cpu_seconds": time.perf_counter() - t0})
+        out["parity"] = m
+    del smp
+    return out
+
+
 def streaming_schedule_leg(dec, geom, dev, sd, n_streams=256, steps=320, p_active=0.8, zero_every=300, track=(3, 200)):
     """SURVEY 8d's K4 schedule: every step a random subset of the streams (p = 0.8) decodes one frame, every stream ends a
     speech segment (set_to_zero on both caches) about once per `zero_every` steps -- driven through vvdec.FrameStep
@@ -823,6 +894,15 @@ def main():
         y = None
         streaming = streaming_leg(dec, geom, dev, sd)
 
+    # ---- diffusion-head sampler ---------------------------------------------------------------
+    sampler = None
+    if not args.no_streaming:
+        try:
+            sampler = sampler_leg(dev, parity=not args.no_cpu_baseline)
+        except Exception as e:                                  # report, do not hide
+            sampler = {"error": f"{type(e).__name__}: {e}"[:300]}
+            torch.cuda.empty_cache()
+
     # ---- encoder leg (BASELINE.json configs[4]) ---------------------------------------------------------
     encoder = None
     if not args.no_encoder:
@@ -872,7 +952,7 @@ def main():
         "config": workload_config(B, T),
         "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roof, "cpu_baseline": cpu,
         "parity": parity,
-        "streaming": streaming, "encoder": encoder, "longform": longform,
+        "streaming": streaming, "sampler": sampler, "encoder": encoder, "longform": longform,
         "torch_eager_gpu": eager,
     }
     print(json.dumps(line), flush=True)

@@ -22,7 +22,7 @@ class FakeLib:
     def __getattr__(self, name):
         def fn(*args):
             self.calls.append((name, args))
-            if name in ("vv_decoder_create", "vv_encoder_create", "vv_state_create", "vv_encoder_state_create"):
+            if name in ("vv_decoder_create", "vv_encoder_create", "vv_state_create", "vv_encoder_state_create", "vv_sampler_create"):
                 args[-1]._obj.value = 0x1000 + len(self.calls)
             if name in ("vv_decoder_halo_frames", "vv_encoder_halo_frames"):
                 return 58
@@ -152,3 +152,32 @@ def test_patch_finds_the_tokenizer_inside_a_wrapping_model(fake):
     outer = Outer()
     dec = vvdec.patch(outer)
     assert outer.model.acoustic_tokenizer.decode == dec.decode
+
+
+def test_sampler_geometry_names_and_patch_with_genuine_objects(fake):
+    """the genuine VibeVoiceDiffusionHeadConfig (shipped JSON block) -> SamplerGeometry; a genuine
+    VibeVoiceDiffusionHead's state-dict names / shapes == what the packer expects; patch_sampler() swaps
+    sample_speech_tokens on a model-shaped object and loads every tensor under its own name."""
+    import json
+    import types
+    import vvdec
+    from oracle.ref_shim import import_reference_sampler
+    from oracle.sampler_oracle import SamplerGeometry as OG
+    _, Head, HeadCfg, _ = import_reference_sampler()
+    with open("/root/reference/vibevoice/configs/qwen2.5_1.5b_64k.json") as f:
+        blk = {k: v for k, v in json.load(f)["diffusion_head_config"].items() if k != "model_type"}
+    g = vvdec.SamplerGeometry.from_config(HeadCfg(**blk))
+    assert (g.hidden, g.layers, g.ffn, g.latent, g.train_steps, g.inference_steps) == (1536, 4, 4608, 64, 1000, 20)
+    assert g == vvdec.SamplerGeometry()                                       # the defaults ARE the 1.5B model's head
+    for field, bad in (("prediction_type", "epsilon"), ("ddpm_beta_schedule", "linear")):
+        with pytest.raises(ValueError):
+            vvdec.SamplerGeometry.from_config(HeadCfg(**dict(blk, **{field: bad})))
+    head = Head(HeadCfg(hidden_size=256, head_layers=2)).eval()
+    want = {n: tuple(s) for n, s, _, _ in OG(hidden=256, layers=2).tensor_specs()}
+    assert {k: tuple(v.shape) for k, v in head.state_dict().items()} == want
+    model = types.SimpleNamespace(model=types.SimpleNamespace(prediction_head=head), ddpm_inference_steps=10)
+    smp = vvdec.patch_sampler(model)
+    assert sorted(fake.names("vv_sampler_load_tensor")) == sorted(want)
+    assert model.sample_speech_tokens == smp.sample_speech_tokens and smp.ddpm_inference_steps == 10
+    cfg = [a for n, a in fake.calls if n == "vv_sampler_create"][0][0]._obj
+    assert (cfg.hidden, cfg.layers, cfg.ffn, cfg.latent, cfg.train_steps) == (256, 2, 768, 64, 1000)
