@@ -42,13 +42,16 @@ namespace vv {
 #define VV_BT_HC 64         // hidden units per GEMM-1 chunk (64, or 128 at C = 64 with two D2 buffers)
 #endif
 #ifndef VV_BT_NX64
-#define VV_BT_NX64 3        // x/y ring slots at C = 64 (34 KB each)
+#define VV_BT_NX64 4        // x/y ring slots at C = 64 (34 KB each).  A slot is held from its TMA load until its TMA store has
+                            // drained (~3 tile times): with 3 slots the pipeline starved (ncu: nothing saturated, issue 51 %);
+                            // 4 slots + ONE a tile: 1.371 -> 1.240 ms per 5760 frames (same box, profiles/block_tma_nx4_ab_r02.txt)
 #endif
 #ifndef VV_BT_NX32
 #define VV_BT_NX32 6        // at C = 32 (17 KB each)
 #endif
 #ifndef VV_BT_NA64
-#define VV_BT_NA64 2        // GEMM-1 operand (a) tiles at C = 64 (16 KB each); 1 frees room for a fourth x/y slot
+#define VV_BT_NA64 1        // GEMM-1 operand (a) tiles at C = 64 (16 KB each): GEMM 1 has read the tile half a tile time before
+                            // E1 is done with its last chunk, so S3 refills a single tile in time; 1 frees room for the 4th slot
 #endif
 
 struct BlockTmaArgs {
