@@ -875,7 +875,7 @@ def main():
     kname = f"{top['kind']}@stage{top['stage']}"
     traffic, traffic_src = None, None
     try:                                                      # DRAM bytes per launch from the committed ncu capture
-        with open(os.path.join(ROOT, "profiles", "traffic_r01.json")) as f:
+        with open(os.path.join(ROOT, "profiles", "traffic_r02.json")) as f:
             tr = json.load(f).get(kname)
         if tr:
             traffic, traffic_src = tr["dram_bytes_per_frame"] * top["frames_per_launch"], tr["source"]
