@@ -105,6 +105,9 @@ int64_t vv_decoder_param_count(const vv_decoder* dec);
  *                      gemm_bn256_waves waves of wide tiles), 2 = whenever N % 256 == 0
  *   "gemm_bn256_waves" threshold of the automatic mode, in waves of one tile per SM (default 2)
  *   "gemm_bn64"        1 (default) = N = 64 layers on the persistent kernel's 64-wide tile, 0 = one-tile-per-CTA kernel
+ *   "gemm_bn64_small"  1 (default) = residual-epilogue GEMMs whose 128-wide tiles would occupy fewer than half the SMs
+ *                      (streaming frame steps) use the 64-wide tile; 0 = never.  Results are bit-identical either way
+ *   "block_kernel"     1 (default) = block_tma_kernel for whole Block1Ds at C <= 64, 0 = block_fused_kernel
  * Unknown keys / values out of range: VV_ERR_INVALID_ARG.  The environment variables VV_GEMM_BN256,
  * VV_GEMM_BN256_WAVES, VV_GEMM_BN64 set the defaults a decoder is created with.
  */

@@ -280,3 +280,37 @@ def test_narrow_tile_routes_still_match(full_decoder, opts):
         mu = _upsample_case(dec, w, 6, 2, 200, 19002)
     assert m["snr_db"] > 50 and m["rel_max"] < 5e-3, m
     assert mu["rel_max"] < 2e-5, mu
+
+
+@pytest.mark.parametrize("stage,rows", [(0, 256), (0, 7), (1, 300), (2, 130)])
+def test_few_tile_residual_gemm_on_the_64_wide_tile_is_bit_identical(full_decoder, stage, rows):
+    """Streaming frame steps have few rows (256 streams = 256 rows at stage 0): linear2's 128-wide tiles would occupy fewer
+    than half the SMs, so it routes to gemm_tc2_kernel<EPI_RESID, *, 64> ("gemm_bn64_small").  Every output element still
+    accumulates its k-blocks in the same order, so the result must equal the 128-wide route BIT FOR BIT (which is what keeps
+    streaming == offline bit-equal however the two calls route) -- and match the oracle."""
+    dec, w = full_decoder
+    Cc = FULL.stage_channels(stage)
+    g = _rng(23000 + stage * 10 + rows)
+    a = round_to_bf16(g.standard_normal((rows, Cc), dtype=np.float32))
+    resid = g.standard_normal((rows, Cc), dtype=np.float32)
+    at = torch.from_numpy(a).cuda().to(torch.bfloat16)
+    rt = torch.from_numpy(resid).cuda()
+    hid = torch.empty((rows, 4 * Cc), dtype=torch.bfloat16, device="cuda")
+    outs = {}
+    try:
+        for mode in (1, 0):
+            dec.set_option("gemm_bn64_small", mode)
+            out = torch.full_like(rt, float("nan"))
+            rc = dec._lib.vv_kernel_ffn(dec._h, stage, 0, _ptr(at), _ptr(rt), _ptr(out), _ptr(hid), 1, rows, _stream())
+            _check(dec, rc, "vv_kernel_ffn")
+            torch.cuda.synchronize()
+            outs[mode] = out.clone()
+    finally:
+        dec.set_option("gemm_bn64_small", 1)
+    assert torch.isfinite(outs[1]).all()
+    assert torch.equal(outs[1], outs[0])
+    p = f"decoder.stages.{stage}.0."
+    f = O.ffn(a[None], w[p + "ffn.linear1.weight"], w[p + "ffn.linear1.bias"], w[p + "ffn.linear2.weight"],
+              w[p + "ffn.linear2.bias"])[0]
+    m = O.parity_metrics(outs[1].cpu().numpy(), resid + f * w[p + "ffn_gamma"][None, :])
+    assert m["snr_db"] > 50 and m["rel_max"] < 5e-3, m

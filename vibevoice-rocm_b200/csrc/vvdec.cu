@@ -272,6 +272,7 @@ extern "C" int32_t vv_decoder_set_option(vv_decoder* d, const char* key, int64_t
   if (strcmp(key, "gemm_bn256") == 0 && value >= 0 && value <= 2) { d->opt_bn256 = (int)value; return VV_OK; }
   if (strcmp(key, "gemm_bn256_waves") == 0 && value >= 0) { d->opt_bn256_waves = (int)value; return VV_OK; }
   if (strcmp(key, "gemm_bn64") == 0 && value >= 0 && value <= 1) { d->opt_bn64 = (int)value; return VV_OK; }
+  if (strcmp(key, "gemm_bn64_small") == 0 && value >= 0 && value <= 1) { d->opt_bn64_small = (int)value; return VV_OK; }
   if (strcmp(key, "block_kernel") == 0 && value >= 0 && value <= 1) { d->opt_block_kernel = (int)value; return VV_OK; }
   set_error("unknown option '%s' or value %lld out of range", key, (long long)value);
   return VV_ERR_INVALID_ARG;
@@ -378,6 +379,11 @@ struct Packer {
       const uint32_t box256[2] = {64u, 256u};
       status = encode_map(&w.tm256, w.w, 2, dims, strides, box256);
       w.has_tm256 = (status == VV_OK);
+    }
+    if (status == VV_OK && w.BK == 64 && w.BN == 128) {
+      const uint32_t box64[2] = {64u, 64u};
+      status = encode_map(&w.tm64, w.w, 2, dims, strides, box64);
+      w.has_tm64 = (status == VV_OK);
     }
   }
   // one Block1D (:915-945) under state-dict prefix p: folded mixer vectors + the two FFN GEMM operands
@@ -666,7 +672,13 @@ int launch_gemm_impl(vv_decoder* d, const __nv_bfloat16* A, long long a_rpb, int
     const long long ntiles256 = best_tiles * (w.N / 256);
     const bool wide = w.has_tm256 && d->opt_bn256 > 0 &&
                       (d->opt_bn256 == 2 || ntiles256 >= (long long)d->opt_bn256_waves * num_sms);
-    const long long ntiles = wide ? ntiles256 : best_tiles * (w.N / w.BN);
+    // few tiles (streaming: a frame step of 256 streams has 256 rows at stage 0, i.e. 2 x 16 tiles of 128 x 128 for linear2,
+    // each streaming 2 MB of weights through ONE SM): the 64-wide tile doubles the CTAs pulling weights.  Every output
+    // element still accumulates its k-blocks in the same order, so results are bit-identical to the 128 / 256-wide tiles
+    // (streaming == offline stays bit-equal whichever way the two calls route).  Residual epilogue only (fp32 out).
+    const bool small64 = !wide && w.has_tm64 && e.epi == EPI_RESID && d->opt_bn64_small != 0 && d->cfg.gemm_path == 0 &&
+                         best_tiles * (w.N / w.BN) * 2 <= (long long)num_sms;
+    const long long ntiles = wide ? ntiles256 : small64 ? best_tiles * (w.N / 64) : best_tiles * (w.N / w.BN);
     const unsigned grid2 = (unsigned)std::min<long long>(ntiles, num_sms);
     const bool deep = nk >= 32;   // K >= 2048: mainloop-dominated
 #define VV_G2_LAUNCH(E, D)                                                                                  \
@@ -681,6 +693,17 @@ int launch_gemm_impl(vv_decoder* d, const __nv_bfloat16* A, long long a_rpb, int
         launch_k(gemm_tc2_kernel<E, D, 128>, dim3(grid2), dim3(G2Warps<E>::THREADS), Gemm2Cfg<E, D, 128>::TOTAL, s, tmA, w.tm, tmR, tmO, g);  \
       }                                                                                                       \
     } while (0)
+    if (small64) {                       // residual epilogue on the 64-wide tile (only ever set with e.epi == EPI_RESID)
+      if (deep) {
+        rc = ensure_smem(gemm_tc2_kernel<EPI_RESID, true, 64>, (int)Gemm2Cfg<EPI_RESID, true, 64>::TOTAL, d->cfg.device);
+        if (rc != VV_OK) return rc;
+        launch_k(gemm_tc2_kernel<EPI_RESID, true, 64>, dim3(grid2), dim3(G2Warps<EPI_RESID>::THREADS), Gemm2Cfg<EPI_RESID, true, 64>::TOTAL, s, tmA, w.tm64, tmR, tmO, g);
+      } else {
+        rc = ensure_smem(gemm_tc2_kernel<EPI_RESID, false, 64>, (int)Gemm2Cfg<EPI_RESID, false, 64>::TOTAL, d->cfg.device);
+        if (rc != VV_OK) return rc;
+        launch_k(gemm_tc2_kernel<EPI_RESID, false, 64>, dim3(grid2), dim3(G2Warps<EPI_RESID>::THREADS), Gemm2Cfg<EPI_RESID, false, 64>::TOTAL, s, tmA, w.tm64, tmR, tmO, g);
+      }
+    } else
     if (e.epi == EPI_BIAS_F32) { if (deep) VV_G2_LAUNCH(EPI_BIAS_F32, true); else VV_G2_LAUNCH(EPI_BIAS_F32, false); }
     else if (e.epi == EPI_GELU_BF16) { if (deep) VV_G2_LAUNCH(EPI_GELU_BF16, true); else VV_G2_LAUNCH(EPI_GELU_BF16, false); }
     else { if (deep) VV_G2_LAUNCH(EPI_RESID, true); else VV_G2_LAUNCH(EPI_RESID, false); }

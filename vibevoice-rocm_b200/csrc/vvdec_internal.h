@@ -33,6 +33,8 @@ struct DenseW {                 // one packed GEMM weight: bf16 [N, K] K-major +
   CUtensorMap tm;
   bool has_tm256 = false;       // N % 256 == 0 and BK == 64: second map with a [64 x 256] box (gemm_tc2 BN = 256)
   CUtensorMap tm256;
+  bool has_tm64 = false;        // BN == 128 and BK == 64: third map with a [64 x 64] box (gemm_tc2 BN = 64 for launches with few tiles)
+  CUtensorMap tm64;
 };
 
 struct BlockW {
@@ -77,6 +79,7 @@ struct vv_decoder {
   int opt_bn256 = 1;                // gemm_tc2 tile width: 0 never 256, 1 auto (>= opt_bn256_waves waves of wide tiles), 2 whenever N % 256 == 0
   int opt_bn256_waves = 2;
   int opt_bn64 = 1;                 // N = 64 layers on the persistent kernel's 64-wide tile (0: one-tile-per-CTA kernel)
+  int opt_bn64_small = 1;           // residual-epilogue GEMMs whose 128-wide tiles would occupy fewer than half the SMs use the 64-wide tile
   int opt_block_kernel = 1;         // whole-Block1D kernel at C <= 64: 1 = block_tma_kernel (x tile staged by TMA), 0 = block_fused_kernel
   // optional per-launch timing (vv_decoder_set_profiling): CUDA events recorded on the decode stream
   bool prof_on = false;
