@@ -173,6 +173,31 @@ def test_both_block_kernels_stream_equal_offline(full_decoder):
     assert m["snr_db"] > 48.0 and m["rel_max"] < 1e-2, m
 
 
+def test_block_ws_on_and_off_stream_equal_offline(full_decoder):
+    """Stage 4 (C = 128) as one kernel (block_ws, the default) and as mixer_kernel + ffn_stream_kernel (block_ws 0): each
+    reproduces its own offline decode bit for bit when streamed in uneven chunks, and the two agree to the path's tolerance
+    (block_ws folds ffn_norm_w / ffn_gamma into the bf16 weights like block_tma_kernel, see the test above)."""
+    dec, _ = full_decoder
+    lat = torch.from_numpy(make_latents(2, 9, 64, 53)).cuda()
+    outs = {}
+    try:
+        for k in (0, 1):
+            dec.set_option("block_ws", k)
+            off = dec.decode(lat)
+            cache = dec.new_cache(4)
+            idx = torch.tensor([0, 2], device="cuda")
+            parts, t = [], 0
+            for n in (2, 1, 1, 5):
+                parts.append(dec.decode(lat[:, t:t + n], cache=cache, sample_indices=idx, use_cache=True))
+                t += n
+            assert torch.equal(torch.cat(parts, -1), off), k
+            outs[k] = off
+    finally:
+        dec.set_option("block_ws", 1)
+    m = parity_metrics(outs[1].cpu().numpy(), outs[0].cpu().numpy())
+    assert m["snr_db"] > 48.0 and m["rel_max"] < 1e-2, m
+
+
 def test_state_zero_export_import(full_decoder):
     dec, _ = full_decoder
     lat = torch.from_numpy(make_latents(1, 4, 64, 43)).cuda()

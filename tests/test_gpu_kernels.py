@@ -112,6 +112,40 @@ def test_block_fused(full_decoder, stage, B, rows, kernel):
     assert m["snr_db"] > 45 and m["rel_max"] < 2e-2, m
 
 
+@pytest.mark.parametrize("B,rows", [(2, 300), (1, 129), (1, 1), (3, 5), (1, 6), (2, 127), (2, 20001), (1, 128), (2, 8),
+                                    (4, 263), (5, 800), (1, 150 * 128 + 3)])
+def test_block_ws(full_decoder, B, rows):
+    """Whole Block1D at C = 128 in one kernel (block_ws_kernel: x tile staged by TMA, weights streamed in 64-unit chunks, the
+    GEMM-1 operand written into the slot's own y bytes, D2 preloaded with the residual) against the oracle's mixer half
+    followed by its FFN half.  Shapes: single rows, rows < 6 (all context from the causal pad), tile edges (127 / 128 / 129),
+    more tiles than SMs (150 tiles on one item: the two-slot ring wraps many times), several items."""
+    dec, w = full_decoder
+    stage = 4
+    Cc = FULL.stage_channels(stage)
+    assert Cc == 128
+    x = (_rng(41000 + rows * 7 + B).standard_normal((B, rows, Cc)).astype(np.float32) * 1.7)
+    p = f"decoder.stages.{stage}.1."
+    xc = x.transpose(0, 2, 1)
+    h = O.rms_norm_channels(xc, w[p + "norm.weight"], FULL.eps)
+    h, _ = O.sconv1d(h, w[p + "mixer.conv.conv.conv.weight"], w[p + "mixer.conv.conv.conv.bias"], groups=Cc)
+    y = xc + h * w[p + "gamma"][None, :, None]
+    a = O.rms_norm_channels(y, w[p + "ffn_norm.weight"], FULL.eps).transpose(0, 2, 1)
+    f = O.ffn(a, w[p + "ffn.linear1.weight"], w[p + "ffn.linear1.bias"], w[p + "ffn.linear2.weight"],
+              w[p + "ffn.linear2.bias"])
+    ref = y.transpose(0, 2, 1) + f * w[p + "ffn_gamma"][None, None, :]
+    xt = torch.from_numpy(x).cuda()
+    out = torch.full_like(xt, float("nan"))
+    rc = dec._lib.vv_kernel_block(dec._h, stage, 1, _ptr(xt), _ptr(out), B, rows, _stream())
+    _check(dec, rc, "vv_kernel_block")
+    torch.cuda.synchronize()
+    o = out.cpu().numpy()
+    assert np.isfinite(o).all()
+    m = O.parity_metrics(o, ref)
+    assert m["snr_db"] > 45 and m["rel_max"] < 2e-2, m
+    # the input is left untouched (the kernel works on its shared-memory copy)
+    assert torch.equal(xt, torch.from_numpy(x).cuda())
+
+
 @pytest.mark.parametrize("stage,B,rows", [(1, 2, 5), (2, 1, 17), (3, 2, 40), (4, 1, 130), (5, 2, 200), (6, 1, 300),
                                           (6, 3, 1), (1, 130, 1)])
 def test_polyphase_upsample(full_decoder, stage, B, rows):

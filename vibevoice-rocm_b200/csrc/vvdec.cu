@@ -15,6 +15,7 @@
 #include "ffn_stream.cuh"
 #include "block_fused.cuh"
 #include "block_tma.cuh"
+#include "block_ws.cuh"
 #include "gemm_tc2.cuh"
 #include "encoder.cuh"
 #include "pcm16.cuh"
@@ -233,6 +234,7 @@ static int32_t init_core(const vv_config* cfg, vv_decoder* d) {
   if (const char* ev = getenv("VV_GEMM_BN256_WAVES")) d->opt_bn256_waves = atoi(ev);
   if (const char* ev = getenv("VV_GEMM_BN64")) d->opt_bn64 = atoi(ev);
   if (const char* ev = getenv("VV_BLOCK_KERNEL")) d->opt_block_kernel = atoi(ev) != 0;
+  if (const char* ev = getenv("VV_BLOCK_WS")) d->opt_block_ws = atoi(ev) != 0;
   d->hop = 1;
   for (int i = 0; i + 1 < cfg->n_stages; ++i) d->hop *= cfg->ratios[i];
   // causal receptive field in latent frames: sum of left taps / layer input rate
@@ -274,6 +276,7 @@ extern "C" int32_t vv_decoder_set_option(vv_decoder* d, const char* key, int64_t
   if (strcmp(key, "gemm_bn64") == 0 && value >= 0 && value <= 1) { d->opt_bn64 = (int)value; return VV_OK; }
   if (strcmp(key, "gemm_bn64_small") == 0 && value >= 0 && value <= 1) { d->opt_bn64_small = (int)value; return VV_OK; }
   if (strcmp(key, "block_kernel") == 0 && value >= 0 && value <= 1) { d->opt_block_kernel = (int)value; return VV_OK; }
+  if (strcmp(key, "block_ws") == 0 && value >= 0 && value <= 1) { d->opt_block_ws = (int)value; return VV_OK; }
   set_error("unknown option '%s' or value %lld out of range", key, (long long)value);
   return VV_ERR_INVALID_ARG;
 }
@@ -430,7 +433,7 @@ bool Packer::block(const std::string& p, int C, BlockW& bw) {
     bw.h_b2 = *b2;
     bw.h_fgamma = *fg;
   }
-  if (status == VV_OK && C <= 64) {    // operands of block_tma_kernel with the per-channel scales folded in
+  if (status == VV_OK && C <= 128) {   // operands of block_tma_kernel / block_ws_kernel with the per-channel scales folded in
     std::vector<float> w1f(*w1), b1h(*b1), w2f(*w2), gb2((size_t)C);
     for (int n = 0; n < 4 * C; ++n)
       for (int k = 0; k < C; ++k) w1f[(size_t)n * C + k] *= 0.5f * (*fnw)[k];
@@ -444,6 +447,12 @@ bool Packer::block(const std::string& p, int C, BlockW& bw) {
     bw.gb2 = upload(gb2);
     bw.h_b1c = b1h;
     bw.h_gb2c = gb2;
+    if (status == VV_OK && C == 128) {  // block_ws_kernel reads the folded linear1 in chunks of 64 hidden units
+      const uint64_t dims[2] = {(uint64_t)C, (uint64_t)(4 * C)};
+      const uint64_t strides[1] = {(uint64_t)C * 2};
+      const uint32_t box[2] = {64u, 64u};
+      status = encode_map(&bw.tm_w1fs, bw.lin1f.w, 2, dims, strides, box);
+    }
   }
   if (status == VV_OK && C == 128) {   // ffn_stream_kernel reads linear1 in chunks of 64 hidden units
     const uint64_t dims[2] = {(uint64_t)C, (uint64_t)(4 * C)};
@@ -810,7 +819,7 @@ int launch_ffn_fused(vv_decoder* d, int C, const BlockW& bw, const __nv_bfloat16
 // Whole Block1D (mixer + FFN) in one kernel (C = 32, 64; block_fused.cuh).  x: fp32 [nbatch, rows_pb, C];
 // out: fp32, same shape, must NOT alias x (tiles read 6 rows of their left neighbour).
 bool block_fused_supported(const vv_decoder* d, int C) {
-  return d->cfg.gemm_path == 0 && (C == 32 || C == 64);
+  return d->cfg.gemm_path == 0 && (C == 32 || C == 64 || (C == 128 && d->opt_block_ws != 0));
 }
 
 template <int C, bool STATE>
@@ -869,10 +878,50 @@ int launch_block_tma(vv_decoder* d, int C, const BlockW& bw, const float* x, flo
   return streaming ? launch_block_tma_inst<64, true>(d, tmX, tmO, bw, a, s) : launch_block_tma_inst<64, false>(d, tmX, tmO, bw, a, s);
 }
 
+// Whole Block1D at C = 128 (block_ws.cuh): x tile staged by TMA, weights streamed, a tile inside the slot.
+template <bool STATE>
+int launch_block_ws_inst(vv_decoder* d, const CUtensorMap& tmX, const CUtensorMap& tmO, const BlockW& bw,
+                         const BlockWsArgs& a, cudaStream_t s) {
+  const int arc = ensure_smem(block_ws_kernel<STATE>, (int)BlockWsCfg::TOTAL, d->cfg.device);
+  if (arc != VV_OK) return arc;
+  const long long ntiles = (long long)a.nbatch * a.tiles_pb;
+  const unsigned grid = (unsigned)std::min<long long>(ntiles, d->num_sms);
+  launch_k(block_ws_kernel<STATE>, dim3(grid), dim3(BlockWsCfg::THREADS), BlockWsCfg::TOTAL, s, tmX, tmO, bw.tm_w1fs,
+           bw.lin2f.tm, a);
+  VV_LAUNCH_OK();
+  return VV_OK;
+}
+
+int launch_block_ws(vv_decoder* d, const BlockW& bw, const float* x, float* out, __nv_bfloat16* out_bf16, int nbatch,
+                    int rows_pb, vv_state* st, const int32_t* slots, cudaStream_t s, PadOut po) {
+  constexpr int C = BlockWsCfg::C;
+  BlockWsArgs a;
+  a.nbatch = nbatch; a.rows_pb = rows_pb; a.tiles_pb = (rows_pb + 127) / 128; a.eps = d->cfg.eps;
+  a.norm_w = bw.norm_w; a.dw_w = bw.dw_w; a.dw_b = bw.dw_b; a.gamma = bw.gamma;
+  a.out_bf16 = out_bf16;
+  if (bw.h_b1c.size() != (size_t)4 * C || bw.h_gb2c.size() != (size_t)C) { set_error("block_ws: constants missing"); return VV_ERR_NOT_FINALIZED; }
+  memcpy(a.b1c, bw.h_b1c.data(), sizeof(a.b1c));
+  memcpy(a.gb2c, bw.h_gb2c.data(), sizeof(a.gb2c));
+  a.st = make_state_ref(st, slots, bw.state_off);
+  a.ob_rpb = po.rpb > 0 ? po.rpb : rows_pb + po.off; a.ob_off = po.off;
+  if ((long long)nbatch * a.tiles_pb >= (1LL << 31) / 8) { set_error("block_ws: too many tiles"); return VV_ERR_BAD_SHAPE; }
+  CUtensorMap tmX, tmO;
+  const uint64_t dims[3] = {(uint64_t)C, (uint64_t)rows_pb, (uint64_t)nbatch};
+  const uint64_t strides[2] = {(uint64_t)C * 4, (uint64_t)rows_pb * C * 4};
+  const uint32_t xbox[3] = {32u, (uint32_t)BlockWsCfg::XROWS, 1u};
+  const uint32_t obox[3] = {32u, 128u, 1u};
+  int rc = encode_map(&tmX, x, 3, dims, strides, xbox, true);
+  if (rc == VV_OK) rc = encode_map(&tmO, out, 3, dims, strides, obox, true);
+  if (rc != VV_OK) return rc;
+  d->launches++;
+  return a.st.base != nullptr ? launch_block_ws_inst<true>(d, tmX, tmO, bw, a, s) : launch_block_ws_inst<false>(d, tmX, tmO, bw, a, s);
+}
+
 int launch_block_fused(vv_decoder* d, int C, const BlockW& bw, const float* x, float* out, __nv_bfloat16* out_bf16,
                        int nbatch, int rows_pb, vv_state* st, const int32_t* slots, cudaStream_t s,
                        PadOut po = PadOut()) {
   if (x == out) { set_error("block_fused: input and output must not alias"); return VV_ERR_INVALID_ARG; }
+  if (C == 128) return launch_block_ws(d, bw, x, out, out_bf16, nbatch, rows_pb, st, slots, s, po);
   if (d->opt_block_kernel == 1) return launch_block_tma(d, C, bw, x, out, out_bf16, nbatch, rows_pb, st, slots, s, po);
   BlockFusedArgs a;
   a.x = x; a.nbatch = nbatch; a.rows_pb = rows_pb; a.tiles_pb = (rows_pb + 127) / 128; a.eps = d->cfg.eps;

@@ -42,6 +42,7 @@ struct BlockW {
         *ffn_gamma = nullptr;
   DenseW lin1, lin2;            // lin1 is stored pre-scaled by 0.5 (weights and bias), see epilogue.cuh
   CUtensorMap tm_w1s;           // lin1 through a [64 x 64] box (ffn_stream_kernel), C = 128 only
+  CUtensorMap tm_w1fs;          // lin1f through a [64 x 64] box (block_ws_kernel), C = 128 only
   // block_tma_kernel (C <= 64) folds the per-channel scales into the GEMM operands: lin1f = 0.5 * W1 * diag(ffn_norm_w),
   // lin2f = diag(ffn_gamma) * W2, gb2 = ffn_gamma * b2  (lin1f.bias = 0.5 * b1 as in lin1)
   DenseW lin1f, lin2f;
@@ -80,6 +81,7 @@ struct vv_decoder {
   int opt_bn256_waves = 2;
   int opt_bn64 = 1;                 // N = 64 layers on the persistent kernel's 64-wide tile (0: one-tile-per-CTA kernel)
   int opt_bn64_small = 1;           // residual-epilogue GEMMs whose 128-wide tiles would occupy fewer than half the SMs use the 64-wide tile
+  int opt_block_ws = 1;             // whole-Block1D kernel at C = 128: 1 = block_ws_kernel, 0 = mixer_kernel + ffn_stream_kernel
   int opt_block_kernel = 1;         // whole-Block1D kernel at C <= 64: 1 = block_tma_kernel (x tile staged by TMA), 0 = block_fused_kernel
   // optional per-launch timing (vv_decoder_set_profiling): CUDA events recorded on the decode stream
   bool prof_on = false;
