@@ -7,18 +7,22 @@
 // Why: round 2's stage 4 ran mixer_kernel (10 B per element: x in, y and a out) and then ffn_stream_kernel (10 B: a and y in,
 // out out) -- 20 B per element where the block needs 8, 21 % of the K2 step.  At C = 128 the two weight matrices (128 KB
 // each) do not fit beside the tiles, which is why block_tma_kernel stops at C = 64; here they are streamed in 64-unit hidden
-// chunks through two TMA rings (they stay L2-resident), and the budget that makes the rest fit in 227 KB is:
-//   * TWO x/y slots of [8 halo + 128 rows, 128 ch] fp32 (68 KB each).  A slot carries its tile from the TMA load to the TMA
-//     store of the block output; the thread that issues the store refills the slot as soon as the store has read it.
-//   * NO separate GEMM-1 operand tile: once the row warps hold a y row in registers and have preloaded the D2 accumulator
-//     with it (tcgen05.st, as in block_tma_kernel), the slot's y bytes are dead until E2 overwrites them with the output, so
-//     a = bf16(y * rstd2) is written INTO the slot -- K block kb of the a tile over rows 8..135 of channel box kb (both are
-//     128 B per row with the same 128B swizzle phase, so a row's a bytes land inside that row's own y bytes).
-//   * W1 ring of 3 and W2 ring of 2 chunks (16 KB each).
-// Warp roles (24 warps): E1 x 8 (GELU, H back into tensor memory), E2 x 4 (accumulator -> slot), R x 4 (thread = row:
-// first statistic of tile it + 1 and second statistic / a tile / D2 preload of tile it, alternating), S2 x 4 (depthwise
-// conv, one warp = one 32-row strip, lane = 4 channels), and four single-thread roles: weight loader, GEMM 1, GEMM 2,
-// store + reload.  All hand-offs are mbarriers.  Streaming (STATE) as in block_tma_kernel: same state layout.
+// chunks through two TMA rings (they stay L2-resident).  What makes the rest fit, and keeps shared-memory BANDWIDTH (the
+// tightest resource of this kernel: the first build moved ~1.1 MB per 128-row tile through a 128 B/clk port) in check:
+//   * ONE x/y slot of [8 halo + 128 rows, 128 ch] fp32 (68 KB).  Its cycle (TMA load -> first statistic -> conv in place ->
+//     second statistic) is shorter than a tile's GEMM phase, so a single slot keeps the tensor pipe fed; the loader refills it
+//     as soon as the row warps have read y.
+//   * The GEMM-1 operand a = bf16(y * rstd2) never touches shared memory: the row warps (thread = row = TMEM lane) write it
+//     with tcgen05.st into 64 columns of TENSOR memory and GEMM 1 takes its A operand from there (like GEMM 2 takes H), which
+//     removes 8 re-reads of a 32 KB tile per tile from the shared-memory port.  The same warps preload the D2 accumulator
+//     with y + ffn_gamma * b2 (as block_tma_kernel), so E2 adds nothing and y is dead once they are done.
+//   * A separate output staging tile (64 KB): E2 writes the finished accumulator there and a dedicated thread TMA-stores it,
+//     off the slot's cycle.
+//   * W1 ring of 3 and W2 ring of 2 chunks (16 KB each).  Tensor memory: D1 2 x 64, H 2 x 32, D2 2 x 128, A 64 = 512 columns.
+// Warp roles (28 warps, 3 of them idle): E1 x 8 (GELU, H back into tensor memory), E2 x 4 (accumulator -> staging), R x 4 (thread = row: both
+// statistics, stream context, a and the D2 preload), S2 x 4 (depthwise conv, one warp = one 32-row strip, lane = 4 channels),
+// and five single-thread roles: weight loader, GEMM 1, GEMM 2, x loader, store.  All hand-offs are mbarriers.
+// Streaming (STATE) as in block_tma_kernel: same state layout.
 #pragma once
 #include <cuda.h>
 #include "ptx.cuh"
@@ -52,39 +56,55 @@ struct BlockWsArgs {
 #define VV_BW_NW2 2
 #endif
 
+#ifdef VV_BW_TRACE     // timeline instrumentation (A/B builds only): clock64 stamps of CTA 0 for its tiles [8, 24)
+__device__ long long vv_bw_trace[16 * 16];
+#define VV_BWT(slot, it)                                                                                 \
+  do {                                                                                                   \
+    if (blockIdx.x == 0 && (it) >= 8 && (it) < 24) vv_bw_trace[((it) - 8) * 16 + (slot)] = clock64();    \
+  } while (0)
+#else
+#define VV_BWT(slot, it) do { } while (0)
+#endif
+
 struct BlockWsCfg {
   static constexpr int C = 128;
   static constexpr int HC = 64;                      // hidden units per chunk
   static constexpr int NCH = 4 * C / HC;             // 8 chunks per tile
-  static constexpr int KB = C / 64;                  // 64-wide K blocks of the a tile / a W1 chunk
+  static constexpr int KB = C / 64;                  // 64-wide K blocks of a W1 chunk
   static constexpr int NBOX = C / 32;
   static constexpr int HALO = 8, XROWS = 128 + HALO;
   static constexpr int XBOX_BYTES = XROWS * 128;     // 17 KB
-  static constexpr int XY_BYTES = NBOX * XBOX_BYTES; // 68 KB
-  static constexpr int NX = 2;
+  static constexpr int X_BYTES = NBOX * XBOX_BYTES;  // 68 KB
+  static constexpr int OBOX_BYTES = 128 * 128;       // 16 KB
+  static constexpr int OUT_BYTES = NBOX * OBOX_BYTES;
   static constexpr int NW1 = VV_BW_NW1, NW2 = VV_BW_NW2, WLAG = 2;
   static constexpr int W1_BYTES = HC * C * 2;        // KB blocks of [64 rows x 128 B]
   static constexpr int W2_BYTES = C * HC * 2;        // [C rows x 128 B]
-  static constexpr int E1W = 8, E2W = 4, RW = 4, S2W = 4, CTRL = 4;
+  static constexpr int E1W = 8, E2W = 4, RW = 4, S2W = 4, CTRL = 8;   // 5 control roles + 3 idle warps: see REG_LAUNCH
   static constexpr int SROWS = 128 / S2W;            // rows per conv strip: 32
   static constexpr int WARPS = E1W + E2W + RW + S2W + CTRL;
   static constexpr int THREADS = WARPS * 32;
-  static constexpr int RSTD_STRIDE = 144;
-  static constexpr int OFF_XY = 0;
-  static constexpr int OFF_W1 = OFF_XY + NX * XY_BYTES;
+  static constexpr int RSTD_FLOATS = 144;
+  static constexpr int OFF_X = 0;
+  static constexpr int OFF_OUT = OFF_X + X_BYTES;
+  static constexpr int OFF_W1 = OFF_OUT + OUT_BYTES;
   static constexpr int OFF_W2 = OFF_W1 + NW1 * W1_BYTES;
   static constexpr int OFF_RSTD = OFF_W2 + NW2 * W2_BYTES;
-  static constexpr int OFF_BAR = OFF_RSTD + NX * RSTD_STRIDE * 4;
+  static constexpr int OFF_BAR = OFF_RSTD + RSTD_FLOATS * 4;
   static constexpr int ND2 = 2;
-  static constexpr int NBARS = 5 * NX + 2 * NW1 + 2 * NW2 + 8 + 3 * ND2;
+  static constexpr int NBARS = 8 + 2 * NW1 + 2 * NW2 + 8 + 3 * ND2;
   static constexpr int TOTAL = OFF_BAR + 512 + 1024;
   static_assert(NBARS * 8 + 8 <= 512, "barrier block");
-  static_assert(OFF_W1 % 1024 == 0 && OFF_W2 % 1024 == 0 && XBOX_BYTES % 1024 == 0, "swizzled tiles need 1 KB aligned bases");
+  static_assert(OFF_OUT % 1024 == 0 && OFF_W1 % 1024 == 0 && OFF_W2 % 1024 == 0 && XBOX_BYTES % 1024 == 0,
+                "swizzled tiles need 1 KB aligned bases");
   static_assert(TOTAL <= 232448, "exceeds the 227 KB dynamic shared memory limit");
-  static constexpr uint32_t TMEM_COLS = 512;         // D1: 2 x 64 at 0; H: 2 x 32 at 128; D2: 2 x 128 at 192
-  static constexpr uint32_t H_COL0 = 2 * HC, D2_COL0 = 3 * HC;
-  static_assert(3 * HC + ND2 * C <= 512, "tensor memory columns");
-  static constexpr int REG_LAUNCH = (65536 / THREADS) / 8 * 8;      // 80
+  static constexpr uint32_t TMEM_COLS = 512;         // D1: 2 x 64 at 0; H: 2 x 32 at 128; D2: 2 x 128 at 192; A: 64 at 448
+  static constexpr uint32_t H_COL0 = 2 * HC, D2_COL0 = 3 * HC, A_COL0 = 3 * HC + ND2 * C;
+  static_assert(A_COL0 + C / 2 <= 512, "tensor memory columns");
+  // Registers are allocated per SM sub-partition (warp id mod 4), so the warp count is kept a multiple of 4 and every
+  // sub-partition holds the same mix (2 E1, 1 E2, 1 R, 1 S2, 2 control): 2 x 64 + 64 + 128 + 120 + 2 x 32 = 504 = 7 x 72.
+  static constexpr int REG_LAUNCH = (65536 / THREADS) / 8 * 8;      // 72
+  static_assert(WARPS % 4 == 0, "warps per sub-partition must be equal");
   static constexpr int REG_E1 = 64, REG_E2 = 64, REG_R = 128, REG_S2 = 120, REG_CTRL = 32;
   static_assert(32 * (E1W * REG_E1 + E2W * REG_E2 + RW * REG_R + S2W * REG_S2 + CTRL * REG_CTRL) <= THREADS * REG_LAUNCH,
                 "setmaxnreg budget exceeds the CTA's launch allocation");
@@ -96,21 +116,25 @@ block_ws_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__
                 const __grid_constant__ CUtensorMap tmW1, const __grid_constant__ CUtensorMap tmW2,
                 const BlockWsArgs p) {
   using L = BlockWsCfg;
-  constexpr int C = L::C, NX = L::NX, NCH = L::NCH, NBOX = L::NBOX, HC = L::HC, KB = L::KB, ND2 = L::ND2;
+  constexpr int C = L::C, NCH = L::NCH, NBOX = L::NBOX, HC = L::HC, KB = L::KB, ND2 = L::ND2;
   constexpr int NW1 = L::NW1, NW2 = L::NW2;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = smem_align_1k(smem_raw);
-  uint8_t* sXY = smem + L::OFF_XY;
+  uint8_t* sX = smem + L::OFF_X;
+  uint8_t* sOut = smem + L::OFF_OUT;
   uint8_t* sW1 = smem + L::OFF_W1;
   uint8_t* sW2 = smem + L::OFF_W2;
   float* sRstd = (float*)(smem + L::OFF_RSTD);
   uint64_t* bars = (uint64_t*)(smem + L::OFF_BAR);
-  uint64_t* x_full = bars;                 // [NX] TMA landed the x tile
-  uint64_t* st_ready = x_full + NX;        // [NX] R wrote rstd[] (and patched / saved the stream context)
-  uint64_t* y_full = st_ready + NX;        // [NX] S2 wrote y in place
-  uint64_t* a_full = y_full + NX;          // [NX] R wrote the a tile into the slot
-  uint64_t* y_ready = a_full + NX;         // [NX] E2 turned the slot into the block output
-  uint64_t* w1_full = y_ready + NX;        // [NW1]
+  uint64_t* x_full = bars;                 // TMA landed the x tile
+  uint64_t* x_free = bars + 1;             // R has read y: the slot may be refilled
+  uint64_t* st_ready = bars + 2;           // R wrote rstd[] (and patched / saved the stream context)
+  uint64_t* y_full = bars + 3;             // S2 wrote y in place
+  uint64_t* a_full = bars + 4;             // R wrote the a tile into tensor memory
+  uint64_t* a_empty = bars + 5;            // GEMM 1 has read it
+  uint64_t* out_ready = bars + 6;          // E2 wrote the staging tile
+  uint64_t* out_free = bars + 7;           // the TMA store has read it
+  uint64_t* w1_full = bars + 8;            // [NW1]
   uint64_t* w1_empty = w1_full + NW1;      // [NW1]
   uint64_t* w2_full = w1_empty + NW1;      // [NW2]
   uint64_t* w2_empty = w2_full + NW2;      // [NW2]
@@ -123,7 +147,7 @@ block_ws_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__
   uint64_t* d2_init = d2_empty + ND2;      // [ND2] R preloaded it with y + gb2
   uint32_t* tmem_slot = (uint32_t*)(d2_init + ND2);
 
-  // hardware warps: [0, 8) E1, [8, 12) E2, [12, 16) R, [16, 20) S2, [20, 24): weight loader, G1, G2, store + reload
+  // hardware warps: [0, 8) E1, [8, 12) E2, [12, 16) R, [16, 20) S2, [20, 25): weights, G1, G2, x loader, store, [25, 28) idle
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   constexpr int WARP_E2 = L::E1W, WARP_R = WARP_E2 + L::E2W, WARP_S2 = WARP_R + L::RW, WARP_CTRL = WARP_S2 + L::S2W;
@@ -141,13 +165,14 @@ block_ws_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__
     tma_prefetch_desc(&tmO);
     tma_prefetch_desc(&tmW1);
     tma_prefetch_desc(&tmW2);
-    for (int i = 0; i < NX; ++i) {
-      mbar_init(&x_full[i], 1);
-      mbar_init(&st_ready[i], L::RW);
-      mbar_init(&y_full[i], L::S2W);
-      mbar_init(&a_full[i], L::RW);
-      mbar_init(&y_ready[i], L::E2W);
-    }
+    mbar_init(x_full, 1);
+    mbar_init(x_free, L::RW);
+    mbar_init(st_ready, L::RW);
+    mbar_init(y_full, L::S2W);
+    mbar_init(a_full, L::RW);
+    mbar_init(a_empty, 1);
+    mbar_init(out_ready, L::E2W);
+    mbar_init(out_free, 1);
     for (int i = 0; i < NW1; ++i) { mbar_init(&w1_full[i], 1); mbar_init(&w1_empty[i], 1); }
     for (int i = 0; i < NW2; ++i) { mbar_init(&w2_full[i], 1); mbar_init(&w2_empty[i], 1); }
     for (int i = 0; i < 2; ++i) {
@@ -199,16 +224,15 @@ block_ws_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__
         for (int gp = (total_g > L::WLAG ? total_g - L::WLAG : 0); gp < total_g; ++gp) load_w2(gp);
       }
     } else if (role == 1) {
-      // ===== GEMM 1 issuer: D1[g & 1] = a * W1_chunk^T; the a tile lives in the slot (rows 8..135 of boxes 0 and 1) ======
+      // ===== GEMM 1 issuer: D1[g & 1] = a * W1_chunk^T, A operand from tensor memory ===================================
       if (elect_one()) {
         constexpr uint32_t idesc1 = umma_idesc_bf16(128, HC);
-        const uint64_t da0 = umma_smem_desc<128>(smem_u32(sXY) + L::HALO * 128);
         const uint64_t dw0 = umma_smem_desc<128>(smem_u32(sW1));
+        const uint32_t aa = tmem_base + L::A_COL0;
         int g = 0;
         for (int it = 0; it < my_tiles; ++it) {
-          const int s = it % NX;
-          mbar_wait_sleep(&a_full[s], (uint32_t)((it / NX) & 1), 32);
-          const uint64_t da = da0 + (uint64_t)((s * L::XY_BYTES) >> 4);
+          mbar_wait_sleep(a_full, (uint32_t)(it & 1), 32);
+          VV_BWT(8, it);
 #pragma unroll 1
           for (int j = 0; j < NCH; ++j, ++g) {
             const int db = g & 1, s1 = g % NW1;
@@ -219,13 +243,15 @@ block_ws_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__
 #pragma unroll
             for (int kb = 0; kb < KB; ++kb) {
 #pragma unroll
-              for (int kk = 0; kk < 4; ++kk)
-                umma_bf16(d, da + (uint64_t)(((kb * L::XBOX_BYTES) >> 4) + kk * 2),
-                          dw + (uint64_t)(((kb * HC * 128) >> 4) + kk * 2), idesc1, (kb | kk) != 0);
+              for (int kk = 0; kk < 4; ++kk)       // channels [64 kb + 16 kk, +16) = 8 packed columns of the a tile
+                umma_bf16_ts(d, aa + (uint32_t)(kb * 32 + kk * 8), dw + (uint64_t)(((kb * HC * 128) >> 4) + kk * 2), idesc1,
+                             (kb | kk) != 0);
             }
             umma_commit(&d1_full[db]);
             umma_commit(&w1_empty[s1]);
           }
+          umma_commit(a_empty);
+          VV_BWT(9, it);
         }
       }
     } else if (role == 2) {
@@ -252,32 +278,36 @@ block_ws_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__
             umma_commit(&w2_empty[s2]);
           }
           umma_commit(&d2_full[d2b]);
+          VV_BWT(10, it);
         }
       }
-    } else {
-      // ===== x tiles in, finished tiles out: the thread that stores a slot refills it once the store has read it ==========
+    } else if (role == 3) {
+      // ===== x loader: one [XROWS, 32] box per 32 channels, rows t0 - 8 .. t0 + 127 (rows outside the item read as zero) ====
       if (elect_one()) {
-        auto load_x = [&](int it) {
-          const int s = it % NX;
-          int b, t0;
-          tile_of(it, b, t0);
-          mbar_expect_tx(&x_full[s], L::XY_BYTES);
-#pragma unroll
-          for (int c = 0; c < NBOX; ++c)
-            tma_load_3d(sXY + s * L::XY_BYTES + c * L::XBOX_BYTES, &tmX, &x_full[s], c * 32, t0 - L::HALO, b);
-        };
-        for (int it = 0; it < NX && it < my_tiles; ++it) load_x(it);
         for (int it = 0; it < my_tiles; ++it) {
-          const int s = it % NX;
           int b, t0;
           tile_of(it, b, t0);
-          mbar_wait_sleep(&y_ready[s], (uint32_t)((it / NX) & 1), 64);
+          if (it > 0) mbar_wait_sleep(x_free, (uint32_t)((it - 1) & 1), 64);
+          VV_BWT(0, it);
+          mbar_expect_tx(x_full, L::X_BYTES);
 #pragma unroll
-          for (int c = 0; c < NBOX; ++c)
-            tma_store_3d(&tmO, sXY + s * L::XY_BYTES + c * L::XBOX_BYTES + L::HALO * 128, c * 32, t0, b);
+          for (int c = 0; c < NBOX; ++c) tma_load_3d(sX + c * L::XBOX_BYTES, &tmX, x_full, c * 32, t0 - L::HALO, b);
+        }
+      }
+    } else if (role == 4) {
+      // ===== store: finished staging tile -> global =====================================================================
+      if (elect_one()) {
+        for (int it = 0; it < my_tiles; ++it) {
+          int b, t0;
+          tile_of(it, b, t0);
+          mbar_wait_sleep(out_ready, (uint32_t)(it & 1), 64);
+          VV_BWT(13, it);
+#pragma unroll
+          for (int c = 0; c < NBOX; ++c) tma_store_3d(&tmO, sOut + c * L::OBOX_BYTES, c * 32, t0, b);
           tma_store_commit();
           tma_store_wait_read<0>();
-          if (it + NX < my_tiles) load_x(it + NX);
+          mbar_arrive(out_free);
+          VV_BWT(14, it);
         }
         tma_store_wait_all<0>();
       }
@@ -327,30 +357,30 @@ block_ws_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__
       if (lane == 0) mbar_arrive(&h_full[grp]);
     }
   } else if (warp < WARP_R) {
-    // ===== E2: the accumulator holds out = (y + gb2) + H W2^T: tcgen05.ld -> slot (thread = row) -> TMA store ==============
+    // ===== E2: the accumulator holds out = (y + gb2) + H W2^T: tcgen05.ld -> staging tile (thread = row) -> TMA store ======
     reg_set<L::REG_LAUNCH, L::REG_E2>();
     const int q = warp & 3;
     const int r = q * 32 + lane;
     for (int it = 0; it < my_tiles; ++it) {
-      const int d2b = it % ND2, s = it % NX;
+      const int d2b = it % ND2;
       int b, t0;
       tile_of(it, b, t0);
       const int t = t0 + r;
       const bool valid = t < p.rows_pb;
       const long long brow = (long long)b * p.ob_rpb + p.ob_off + t;
-      // d2_full: GEMM 2 is done, hence GEMM 1 has read the a tile that lives in this slot and R is long done with y
       mbar_wait(&d2_full[d2b], (uint32_t)((it / ND2) & 1));
+      if (threadIdx.x == WARP_E2 * 32) VV_BWT(11, it);
+      mbar_wait(out_free, (uint32_t)((it & 1) ^ 1));          // the previous tile's store has read the staging tile
       tc_fence_after();
-      uint8_t* slot = sXY + s * L::XY_BYTES;
 #pragma unroll 1
       for (int c = 0; c < NBOX; ++c) {
         uint32_t v[32];
         tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + L::D2_COL0 + (uint32_t)(d2b * C + c * 32), v);
         tmem_ld_wait();
-        uint8_t* box = slot + c * L::XBOX_BYTES;
+        uint8_t* box = sOut + c * L::OBOX_BYTES;
 #pragma unroll
         for (int i = 0; i < 8; ++i)
-          *reinterpret_cast<uint4*>(box + xy_cell(L::HALO + r, i)) = make_uint4(v[i * 4], v[i * 4 + 1], v[i * 4 + 2], v[i * 4 + 3]);
+          *reinterpret_cast<uint4*>(box + xy_cell(r, i)) = make_uint4(v[i * 4], v[i * 4 + 1], v[i * 4 + 2], v[i * 4 + 3]);
         if (valid && p.out_bf16 != nullptr) {
           __nv_bfloat16* bp = p.out_bf16 + brow * C + c * 32;
 #pragma unroll
@@ -369,42 +399,44 @@ block_ws_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__
       __syncwarp();
       if (lane == 0) {
         mbar_arrive(&d2_empty[d2b]);
-        mbar_arrive(&y_ready[s]);
+        mbar_arrive(out_ready);
       }
+      if (threadIdx.x == WARP_E2 * 32) VV_BWT(12, it);
     }
   } else if (warp < WARP_S2) {
     // ===== R: thread = row.  stat1(it): rstd of the raw row (first RMSNorm) + stream context in / out, as block_tma_kernel's
-    // S1.  Then per tile: second statistic of y, a = bf16(y * rstd2) into the slot, D2 preload with y + gb2; and stat1 of
-    // the NEXT tile (whose slot the loader refills while this tile's GEMMs run).
+    // S1.  Then per tile: second statistic of y, a = bf16(y * rstd2) -> tensor memory, D2 preload with y + gb2, slot released,
+    // and stat1 of the next tile once the loader has refilled the slot.
     reg_set<L::REG_LAUNCH, L::REG_R>();
     const int r = (warp - WARP_R) * 32 + lane;            // tile row 0..127 -> slot row HALO + r
     const float inv_c = 1.0f / (float)C;
-    auto row_rstd = [&](const uint8_t* slot, int srow) -> float {
-      f32x2 acc = 0ull;
+    auto row_rstd = [&](int srow) -> float {
+      f32x2 acc[4] = {0ull, 0ull, 0ull, 0ull};            // four independent chains
 #pragma unroll
       for (int c = 0; c < NBOX; ++c) {
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
-          const ulonglong2 v = *reinterpret_cast<const ulonglong2*>(slot + c * L::XBOX_BYTES + xy_cell(srow, i));
-          acc = f2_fma(v.x, v.x, acc);
-          acc = f2_fma(v.y, v.y, acc);
+          const ulonglong2 v = *reinterpret_cast<const ulonglong2*>(sX + c * L::XBOX_BYTES + xy_cell(srow, i));
+          acc[(i & 1) * 2] = f2_fma(v.x, v.x, acc[(i & 1) * 2]);
+          acc[(i & 1) * 2 + 1] = f2_fma(v.y, v.y, acc[(i & 1) * 2 + 1]);
         }
       }
-      float s0, s1;
-      f2_unpack(acc, s0, s1);
-      return rstd_of(s0 + s1, inv_c, p.eps);
+      float s0, s1, s2, s3, s4, s5, s6, s7;
+      f2_unpack(acc[0], s0, s1);
+      f2_unpack(acc[1], s2, s3);
+      f2_unpack(acc[2], s4, s5);
+      f2_unpack(acc[3], s6, s7);
+      return rstd_of(((s0 + s1) + (s2 + s3)) + ((s4 + s5) + (s6 + s7)), inv_c, p.eps);
     };
     auto stat1 = [&](int it) {
-      const int s = it % NX;
       int b, t0;
       tile_of(it, b, t0);
-      uint8_t* slot = sXY + s * L::XY_BYTES;
-      float* rs = sRstd + s * L::RSTD_STRIDE;
-      mbar_wait(&x_full[s], (uint32_t)((it / NX) & 1));
+      mbar_wait(x_full, (uint32_t)(it & 1));
+      if (threadIdx.x == WARP_R * 32) VV_BWT(1, it);
       const uint8_t* rd8 = nullptr;
       uint8_t* wr8 = nullptr;
       if (STATE && p.st.base != nullptr) p.st.resolve(b, rd8, wr8);
-      if (warp == WARP_R && lane < L::HALO) {
+      if (warp == WARP_R + 3 && lane < L::HALO) {
         // halo rows (slot rows 0..7 = t0 - 8 .. t0 - 1): at the item start rows 2..7 are the stream's cached raw rows
         // (TMA delivered zeros = the offline causal pad, :398-403)
         if (STATE && t0 == 0 && rd8 != nullptr && lane >= 2) {
@@ -413,10 +445,10 @@ block_ws_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__
           for (int c = 0; c < NBOX; ++c)
 #pragma unroll
             for (int i = 0; i < 8; ++i)
-              *reinterpret_cast<float4*>(slot + c * L::XBOX_BYTES + xy_cell(lane, i)) =
+              *reinterpret_cast<float4*>(sX + c * L::XBOX_BYTES + xy_cell(lane, i)) =
                   *reinterpret_cast<const float4*>(src + c * 32 + i * 4);
         }
-        rs[lane + 2] = row_rstd(slot, lane);
+        sRstd[lane + 2] = row_rstd(lane);
         // the stream's new context = last 6 raw rows of [old context, x] (:371-382): rows before the item start count
         if (STATE && wr8 != nullptr && t0 == 0) {
           const int t = lane - L::HALO;                                     // -8 .. -1
@@ -428,11 +460,11 @@ block_ws_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__
 #pragma unroll
               for (int i = 0; i < 8; ++i)
                 *reinterpret_cast<float4*>(o + c * 32 + i * 4) =
-                    *reinterpret_cast<const float4*>(slot + c * L::XBOX_BYTES + xy_cell(lane, i));
+                    *reinterpret_cast<const float4*>(sX + c * L::XBOX_BYTES + xy_cell(lane, i));
           }
         }
       }
-      rs[L::HALO + r + 2] = row_rstd(slot, L::HALO + r);
+      sRstd[L::HALO + r + 2] = row_rstd(L::HALO + r);
       if (STATE && wr8 != nullptr) {
         const int t = t0 + r;
         const int dst = t - (p.rows_pb - 6);
@@ -443,104 +475,110 @@ block_ws_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__
 #pragma unroll
             for (int i = 0; i < 8; ++i)
               *reinterpret_cast<float4*>(o + c * 32 + i * 4) =
-                  *reinterpret_cast<const float4*>(slot + c * L::XBOX_BYTES + xy_cell(L::HALO + r, i));
+                  *reinterpret_cast<const float4*>(sX + c * L::XBOX_BYTES + xy_cell(L::HALO + r, i));
         }
       }
       __syncwarp();
-      if (lane == 0) mbar_arrive(&st_ready[s]);
+      if (lane == 0) mbar_arrive(st_ready);
+      if (threadIdx.x == WARP_R * 32) VV_BWT(2, it);
     };
-    // 16 columns of the row: cells q0 .. q0 + 3 (4 channels each) -> two 16-byte a chunks + one tcgen05.st of y + gb2
-    auto emit16 = [&](const ulonglong2 (&cell)[4], int q0, f32x2 rr, uint8_t* arow0, uint32_t daddr) {
+    // one box of the row (32 channels = cells[0..7]): 16 packed a columns + 32 accumulator columns of y + gb2
+    auto emit_box = [&](const ulonglong2 (&cell)[8], int c, f32x2 rr, uint32_t aaddr, uint32_t daddr) {
       uint32_t w[16];
 #pragma unroll
-      for (int h = 0; h < 2; ++h) {                       // chunk k = q0 / 2 + h: channels [8k, 8k + 8)
-        float a0, a1, a2, a3, a4, a5, a6, a7;
-        f2_unpack(f2_mul(cell[2 * h].x, rr), a0, a1);
-        f2_unpack(f2_mul(cell[2 * h].y, rr), a2, a3);
-        f2_unpack(f2_mul(cell[2 * h + 1].x, rr), a4, a5);
-        f2_unpack(f2_mul(cell[2 * h + 1].y, rr), a6, a7);
-        uint4 pk;
-        pk.x = pack_bf16x2(a0, a1);
-        pk.y = pack_bf16x2(a2, a3);
-        pk.z = pack_bf16x2(a4, a5);
-        pk.w = pack_bf16x2(a6, a7);
-        const int k = (q0 >> 1) + h;
-        *reinterpret_cast<uint4*>(arow0 + (k >> 3) * L::XBOX_BYTES + (((k & 7) ^ (r & 7)) << 4)) = pk;
+      for (int i = 0; i < 8; ++i) {
+        float a0, a1, a2, a3;
+        f2_unpack(f2_mul(cell[i].x, rr), a0, a1);
+        f2_unpack(f2_mul(cell[i].y, rr), a2, a3);
+        w[i * 2 + 0] = pack_bf16x2(a0, a1);
+        w[i * 2 + 1] = pack_bf16x2(a2, a3);
       }
+      tmem_st_32x16(aaddr + (uint32_t)(c * 16), w);
 #pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        float y0, y1, y2, y3;
-        f2_unpack(cell[i].x, y0, y1);
-        f2_unpack(cell[i].y, y2, y3);
-        const int ch = (q0 + i) * 4;
-        w[i * 4 + 0] = __float_as_uint(y0 + p.gb2c[ch + 0]);
-        w[i * 4 + 1] = __float_as_uint(y1 + p.gb2c[ch + 1]);
-        w[i * 4 + 2] = __float_as_uint(y2 + p.gb2c[ch + 2]);
-        w[i * 4 + 3] = __float_as_uint(y3 + p.gb2c[ch + 3]);
+      for (int h = 0; h < 2; ++h) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          float y0, y1, y2, y3;
+          f2_unpack(cell[h * 4 + i].x, y0, y1);
+          f2_unpack(cell[h * 4 + i].y, y2, y3);
+          const int ch = c * 32 + (h * 4 + i) * 4;
+          w[i * 4 + 0] = __float_as_uint(y0 + p.gb2c[ch + 0]);
+          w[i * 4 + 1] = __float_as_uint(y1 + p.gb2c[ch + 1]);
+          w[i * 4 + 2] = __float_as_uint(y2 + p.gb2c[ch + 2]);
+          w[i * 4 + 3] = __float_as_uint(y3 + p.gb2c[ch + 3]);
+        }
+        tmem_st_32x16(daddr + (uint32_t)(c * 32 + h * 16), w);
       }
-      tmem_st_32x16(daddr + (uint32_t)(q0 * 4), w);
     };
+    const uint32_t lane_base = (uint32_t)((warp & 3) * 32) << 16;
+    const uint32_t aaddr = tmem_base + lane_base + L::A_COL0;
     if (my_tiles > 0) stat1(0);
     for (int it = 0; it < my_tiles; ++it) {
-      const int s = it % NX, d2b = it % ND2;
-      uint8_t* slot = sXY + s * L::XY_BYTES;
-      uint8_t* arow0 = slot + (L::HALO + r) * 128;        // row r of a K block 0; K block 1 is XBOX_BYTES further
-      mbar_wait(&y_full[s], (uint32_t)((it / NX) & 1));
-      // channels 0..63 (boxes 0, 1) stay in registers: their bytes are where the a tile goes.  Channels 64..127 are read
-      // twice (statistic, then conversion): nothing overwrites boxes 2, 3 before E2
+      const int d2b = it % ND2;
+      mbar_wait(y_full, (uint32_t)(it & 1));
+      if (threadIdx.x == WARP_R * 32) VV_BWT(5, it);
+      // channels 0..63 (boxes 0, 1) stay in registers; channels 64..127 are read twice (statistic, then conversion)
       ulonglong2 ylo[16];
-      f32x2 acc = 0ull;
+      f32x2 acc[4] = {0ull, 0ull, 0ull, 0ull};
 #pragma unroll
       for (int c = 0; c < 2; ++c)
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
-          ylo[c * 8 + i] = *reinterpret_cast<const ulonglong2*>(slot + c * L::XBOX_BYTES + xy_cell(L::HALO + r, i));
-          acc = f2_fma(ylo[c * 8 + i].x, ylo[c * 8 + i].x, acc);
-          acc = f2_fma(ylo[c * 8 + i].y, ylo[c * 8 + i].y, acc);
+          ylo[c * 8 + i] = *reinterpret_cast<const ulonglong2*>(sX + c * L::XBOX_BYTES + xy_cell(L::HALO + r, i));
+          acc[(i & 1) * 2] = f2_fma(ylo[c * 8 + i].x, ylo[c * 8 + i].x, acc[(i & 1) * 2]);
+          acc[(i & 1) * 2 + 1] = f2_fma(ylo[c * 8 + i].y, ylo[c * 8 + i].y, acc[(i & 1) * 2 + 1]);
         }
 #pragma unroll
       for (int c = 2; c < 4; ++c)
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
-          const ulonglong2 v = *reinterpret_cast<const ulonglong2*>(slot + c * L::XBOX_BYTES + xy_cell(L::HALO + r, i));
-          acc = f2_fma(v.x, v.x, acc);
-          acc = f2_fma(v.y, v.y, acc);
+          const ulonglong2 v = *reinterpret_cast<const ulonglong2*>(sX + c * L::XBOX_BYTES + xy_cell(L::HALO + r, i));
+          acc[(i & 1) * 2] = f2_fma(v.x, v.x, acc[(i & 1) * 2]);
+          acc[(i & 1) * 2 + 1] = f2_fma(v.y, v.y, acc[(i & 1) * 2 + 1]);
         }
-      float s0, s1;
-      f2_unpack(acc, s0, s1);
-      const float rstd2 = rstd_of(s0 + s1, inv_c, p.eps);
+      float s0, s1, s2, s3, s4, s5, s6, s7;
+      f2_unpack(acc[0], s0, s1);
+      f2_unpack(acc[1], s2, s3);
+      f2_unpack(acc[2], s4, s5);
+      f2_unpack(acc[3], s6, s7);
+      const float rstd2 = rstd_of(((s0 + s1) + (s2 + s3)) + ((s4 + s5) + (s6 + s7)), inv_c, p.eps);
       const f32x2 rr = f2_pack(rstd2, rstd2);
       mbar_wait(&d2_empty[d2b], (uint32_t)(((it / ND2) & 1) ^ 1));      // E2 drained this accumulator two tiles ago
+      mbar_wait(a_empty, (uint32_t)((it & 1) ^ 1));                     // GEMM 1 has read the previous tile's a
       tc_fence_after();
-      const uint32_t daddr = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + L::D2_COL0 + (uint32_t)(d2b * C);
+      const uint32_t daddr = tmem_base + lane_base + L::D2_COL0 + (uint32_t)(d2b * C);
 #pragma unroll
-      for (int q0 = 0; q0 < 16; q0 += 4) {
-        const ulonglong2 cell[4] = {ylo[q0], ylo[q0 + 1], ylo[q0 + 2], ylo[q0 + 3]};
-        emit16(cell, q0, rr, arow0, daddr);
+      for (int c = 0; c < 2; ++c) {
+        const ulonglong2 cell[8] = {ylo[c * 8], ylo[c * 8 + 1], ylo[c * 8 + 2], ylo[c * 8 + 3],
+                                    ylo[c * 8 + 4], ylo[c * 8 + 5], ylo[c * 8 + 6], ylo[c * 8 + 7]};
+        emit_box(cell, c, rr, aaddr, daddr);
       }
 #pragma unroll
-      for (int q0 = 16; q0 < 32; q0 += 4) {
-        ulonglong2 cell[4];
+      for (int c = 2; c < 4; ++c) {
+        ulonglong2 cell[8];
 #pragma unroll
-        for (int i = 0; i < 4; ++i)
-          cell[i] = *reinterpret_cast<const ulonglong2*>(slot + ((q0 + i) >> 3) * L::XBOX_BYTES + xy_cell(L::HALO + r, (q0 + i) & 7));
-        emit16(cell, q0, rr, arow0, daddr);
+        for (int i = 0; i < 8; ++i)
+          cell[i] = *reinterpret_cast<const ulonglong2*>(sX + c * L::XBOX_BYTES + xy_cell(L::HALO + r, i));
+        emit_box(cell, c, rr, aaddr, daddr);
       }
-      fence_proxy_async_smem();                 // a tile (generic-proxy stores) -> visible to tcgen05.mma
       __syncwarp();
-      if (lane == 0) mbar_arrive(&a_full[s]);
+      if (lane == 0) mbar_arrive(x_free);       // every y value of this warp's rows is in registers / tensor memory
       tmem_st_wait();
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&d2_init[d2b]);
+      if (lane == 0) {
+        mbar_arrive(a_full);
+        mbar_arrive(&d2_init[d2b]);
+      }
+      if (threadIdx.x == WARP_R * 32) VV_BWT(7, it);
       if (it + 1 < my_tiles) stat1(it + 1);
     }
   } else {
     // ===== S2: depthwise causal conv k7 over the normalised rows; lane = 4 channels, one warp = one strip of 32 rows ======
     reg_set<L::REG_LAUNCH, L::REG_S2>();
     struct P4 { f32x2 lo, hi; };
-    constexpr int SR = L::SROWS;
-    const int gi = warp - WARP_S2;                                  // strip: tile rows [SR gi, SR gi + SR)
+    constexpr int SR = L::SROWS, NB = 8;                            // rows are loaded NB at a time: the in-place stores
+    const int gi = warp - WARP_S2;                                  // would otherwise order every load behind the last store
     const int c0 = lane * 4;
     const int box = c0 >> 5, qc = (c0 & 31) >> 2;
     // folded taps: y = x + gb + sum_j wq[j] * n[t-6+j],  n = x * rstd,  wq = gamma * w * norm_w,  gb = gamma * conv_bias
@@ -559,11 +597,11 @@ block_ws_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__
       }
     }
     const int sr0 = L::HALO + gi * SR;                              // slot row of the strip's first output row
+    uint8_t* bx = sX + box * L::XBOX_BYTES;
+    const float* rs = sRstd + sr0 - 4;                              // rs[i] = rstd of slot row sr0 - 6 + i
     for (int it = 0; it < my_tiles; ++it) {
-      const int s = it % NX;
-      uint8_t* bx = sXY + s * L::XY_BYTES + box * L::XBOX_BYTES;
-      const float* rs = sRstd + s * L::RSTD_STRIDE + sr0 - 4;      // rs[i] = rstd of slot row sr0 - 6 + i
-      mbar_wait(&st_ready[s], (uint32_t)((it / NX) & 1));
+      mbar_wait(st_ready, (uint32_t)(it & 1));
+      if (threadIdx.x == WARP_S2 * 32) VV_BWT(3, it);
       P4 win[7];
 #pragma unroll
       for (int i = 0; i < 6; ++i) {                                  // warm-up rows: a load and a multiply each
@@ -576,25 +614,34 @@ block_ws_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__
       // y is written in place: every strip must hold its warm-up rows (its neighbour's last rows) before anyone stores
       named_bar_sync(1, L::S2W * 32);
 #pragma unroll
-      for (int k = 0; k < SR; ++k) {
-        ulonglong2* cell = reinterpret_cast<ulonglong2*>(bx + xy_cell(sr0 + k, qc));
-        const ulonglong2 v = *cell;
-        const float rsk = rs[6 + k];
-        const f32x2 rr = f2_pack(rsk, rsk);
-        win[(6 + k) % 7].lo = f2_mul(v.x, rr);
-        win[(6 + k) % 7].hi = f2_mul(v.y, rr);
-        P4 acc;
-        acc.lo = f2_add(v.x, gb.lo);
-        acc.hi = f2_add(v.y, gb.hi);
+      for (int k0 = 0; k0 < SR; k0 += NB) {
+        ulonglong2 xv[NB];
+        float rv[NB];
 #pragma unroll
-        for (int j = 0; j < 7; ++j) {                                // tap j reads n[t - 6 + j] = win[(k + j) % 7]
-          acc.lo = f2_fma(wq[j].lo, win[(k + j) % 7].lo, acc.lo);
-          acc.hi = f2_fma(wq[j].hi, win[(k + j) % 7].hi, acc.hi);
+        for (int k = 0; k < NB; ++k) {
+          xv[k] = *reinterpret_cast<const ulonglong2*>(bx + xy_cell(sr0 + k0 + k, qc));
+          rv[k] = rs[6 + k0 + k];
         }
-        *cell = make_ulonglong2(acc.lo, acc.hi);
+#pragma unroll
+        for (int k = 0; k < NB; ++k) {
+          const int kk = k0 + k;
+          const f32x2 rr = f2_pack(rv[k], rv[k]);
+          win[(6 + kk) % 7].lo = f2_mul(xv[k].x, rr);
+          win[(6 + kk) % 7].hi = f2_mul(xv[k].y, rr);
+          P4 acc;
+          acc.lo = f2_add(xv[k].x, gb.lo);
+          acc.hi = f2_add(xv[k].y, gb.hi);
+#pragma unroll
+          for (int j = 0; j < 7; ++j) {                              // tap j reads n[t - 6 + j] = win[(kk + j) % 7]
+            acc.lo = f2_fma(wq[j].lo, win[(kk + j) % 7].lo, acc.lo);
+            acc.hi = f2_fma(wq[j].hi, win[(kk + j) % 7].hi, acc.hi);
+          }
+          *reinterpret_cast<ulonglong2*>(bx + xy_cell(sr0 + kk, qc)) = make_ulonglong2(acc.lo, acc.hi);
+        }
       }
       __syncwarp();
-      if (lane == 0) mbar_arrive(&y_full[s]);
+      if (lane == 0) mbar_arrive(y_full);
+      if (threadIdx.x == WARP_S2 * 32) VV_BWT(4, it);
     }
   }
   tc_fence_before();

@@ -1587,6 +1587,11 @@ extern "C" int32_t vv_debug_read_trace(long long* host, int32_t n) {
   return (int32_t)cudaMemcpyFromSymbol(host, vv::vv_fs_trace, sizeof(long long) * (size_t)n);
 }
 #endif
+#ifdef VV_BW_TRACE
+extern "C" int32_t vv_debug_read_bw_trace(long long* host, int32_t n) {
+  return (int32_t)cudaMemcpyFromSymbol(host, vv::vv_bw_trace, sizeof(long long) * (size_t)n);
+}
+#endif
 
 // =====================================================================================================
 // encoder path (TokenizerEncoder, :687-813)
