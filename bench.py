@@ -189,8 +189,10 @@ def kernel_work(geom, kind: str, stage: int):
         return ("tensor" if C >= 128 else "hbm"), 4 * cm, 16 * C * cm, 10 * cm
     if kind == "ffn_pair":     # both GEMMs in L2-resident row chunks: the hidden tensor never reaches HBM
         return "tensor", 4 * cm, 16 * C * cm, 10 * cm
-    if kind == "block_fused":  # whole Block1D in one launch (C <= 64): SURVEY's mixer half + FFN half = 8*C*M bytes;
-        return "hbm", 8 * cm, 20 * cm + 16 * C * cm, 8 * cm   # this design moves exactly that (fp32 x in, fp32 x out)
+    if kind == "block_fused":  # whole Block1D in one launch (C <= 128): SURVEY's mixer half + FFN half = 8*C*M bytes;
+        # this design moves exactly that (fp32 x in, fp32 x out).  (20 + 16 C) / 8 flop per byte: 132 at C = 64 (below the
+        # ~212 flop/B ridge of 1382 TFLOP/s over 6.5 TB/s: HBM-bound), 258 at C = 128 (above it: tensor-bound)
+        return ("tensor" if C >= 128 else "hbm"), 8 * cm, 20 * cm + 16 * C * cm, 8 * cm
     if kind == "upsample":     # 2*(Cin*Min + Cout*Mout) bytes, 4*Cin*Cout*r*Min flop
         cin, r = geom.stage_channels(stage - 1), geom.ratios[stage - 1]
         min_ = M // r
@@ -868,7 +870,8 @@ def main():
     top = table[0]
     if top["bound"] == "tensor":
         roof = {"bound": "tensor", "achieved": top["tflops"], "peak": pk["tf_sustained"], "unit": "TFLOP/s",
-                "frac": top["tflops"] / pk["tf_sustained"]}
+                "frac": top["tflops"] / pk["tf_sustained"], "hbm_gbs_algorithmic": top["gbs_algorithmic"],
+                "hbm_frac": top["gbs_algorithmic"] / pk["hbm_gbs"]}
     else:
         roof = {"bound": "hbm", "achieved": top["gbs_algorithmic"], "peak": pk["hbm_gbs"], "unit": "GB/s",
                 "frac": top["gbs_algorithmic"] / pk["hbm_gbs"], "moved_gbs": top["gbs_moved"]}

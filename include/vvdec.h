@@ -108,8 +108,10 @@ int64_t vv_decoder_param_count(const vv_decoder* dec);
  *   "gemm_bn64_small"  1 (default) = residual-epilogue GEMMs whose 128-wide tiles would occupy fewer than half the SMs
  *                      (streaming frame steps) use the 64-wide tile; 0 = never.  Results are bit-identical either way
  *   "block_kernel"     1 (default) = block_tma_kernel for whole Block1Ds at C <= 64, 0 = block_fused_kernel
+ *   "block_ws"         1 (default) = block_ws_kernel (whole Block1D in one kernel) at C = 128, 0 = mixer_kernel +
+ *                      ffn_stream_kernel
  * Unknown keys / values out of range: VV_ERR_INVALID_ARG.  The environment variables VV_GEMM_BN256,
- * VV_GEMM_BN256_WAVES, VV_GEMM_BN64 set the defaults a decoder is created with.
+ * VV_GEMM_BN256_WAVES, VV_GEMM_BN64, VV_BLOCK_KERNEL, VV_BLOCK_WS set the defaults a decoder is created with.
  */
 int32_t vv_decoder_set_option(vv_decoder* dec, const char* key, int64_t value);
 /* samples produced per latent frame (prod(ratios) = 3200) and causal receptive field in frames (58) */

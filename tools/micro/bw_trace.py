@@ -16,12 +16,15 @@ x = torch.randn(1, rows, 128, device="cuda"); out = torch.empty_like(x)
 for _ in range(3):
     assert lib.vv_kernel_block(h, 4, 0, P(x), P(out), 1, rows, st) == 0
 torch.cuda.synchronize()
-buf = (C.c_longlong * 256)()
+buf = (C.c_longlong * 512)()
 raw = C.CDLL(os.environ["VVDEC_LIB"])
-assert raw.vv_debug_read_bw_trace(buf, 256) == 0
+assert raw.vv_debug_read_bw_trace(buf, 512) == 0
 names = ["load", "R:x_full", "R:st_rdy", "S2:start", "S2:y_full", "R:y_seen", "R:a_full", "R:d2init", "G1:start", "G1:last",
          "G2:commit", "E2:d2full", "E2:done", "XY:y_rdy", "XY:st_read"]
 t0 = min(v for v in buf if v > 0)
+e1 = ["c0:wait", "c0:d1full", "c0:ld0", "c0:st0", "c0:ld1", "c0:st1", "c0:hfull", "", "c2:wait", "c2:d1full"]
 for ti in range(16):
-    row = [buf[ti * 16 + s] - t0 if buf[ti * 16 + s] else -1 for s in range(15)]
+    row = [buf[ti * 32 + s] - t0 if buf[ti * 32 + s] else -1 for s in range(15)]
     print(f"it={8 + ti:3d} " + " ".join(f"{n}={v:6d}" for n, v in zip(names, row)))
+    row = [buf[ti * 32 + 16 + s] - t0 if buf[ti * 32 + 16 + s] else -1 for s in range(10)]
+    print("   E1   " + " ".join(f"{n}={v:6d}" for n, v in zip(e1, row) if n))

@@ -57,10 +57,10 @@ struct BlockWsArgs {
 #endif
 
 #ifdef VV_BW_TRACE     // timeline instrumentation (A/B builds only): clock64 stamps of CTA 0 for its tiles [8, 24)
-__device__ long long vv_bw_trace[16 * 16];
+__device__ long long vv_bw_trace[16 * 32];
 #define VV_BWT(slot, it)                                                                                 \
   do {                                                                                                   \
-    if (blockIdx.x == 0 && (it) >= 8 && (it) < 24) vv_bw_trace[((it) - 8) * 16 + (slot)] = clock64();    \
+    if (blockIdx.x == 0 && (it) >= 8 && (it) < 24) vv_bw_trace[((it) - 8) * 32 + (slot)] = clock64();    \
   } while (0)
 #else
 #define VV_BWT(slot, it) do { } while (0)
@@ -324,13 +324,16 @@ block_ws_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__
       const int j = g % NCH;
       const uint32_t ph = (uint32_t)((g >> 1) & 1);
       const float* bp = p.b1c + j * HC;                  // constant bank (by-value kernel argument)
+      if (threadIdx.x == 0 && (j == 0 || j == 2)) VV_BWT(16 + j * 4, g / NCH);
       mbar_wait(&d1_full[grp], ph);
+      if (threadIdx.x == 0 && (j == 0 || j == 2)) VV_BWT(17 + j * 4, g / NCH);
       tc_fence_after();
 #pragma unroll
       for (int hf = 0; hf < HC / 32; ++hf) {
         uint32_t v[32];
         tmem_ld_32x32(d1addr + (uint32_t)(hf * 32), v);
         tmem_ld_wait();
+        if (threadIdx.x == 0 && j == 0) VV_BWT(18 + hf * 2, g / NCH);
         if (hf == HC / 32 - 1) {                     // whole accumulator is in registers: the next G1 may overwrite it
           tc_fence_before();
           __syncwarp();
@@ -350,11 +353,13 @@ block_ws_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__
           tc_fence_after();
         }
         tmem_st_32x16(haddr + (uint32_t)(hf * 16), hv);   // thread = row: pair (k, k+1) -> one 32-bit column
+        if (threadIdx.x == 0 && j == 0) VV_BWT(19 + hf * 2, g / NCH);
       }
       tmem_st_wait();
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&h_full[grp]);
+      if (threadIdx.x == 0 && j == 0) VV_BWT(22, g / NCH);
     }
   } else if (warp < WARP_R) {
     // ===== E2: the accumulator holds out = (y + gb2) + H W2^T: tcgen05.ld -> staging tile (thread = row) -> TMA store ======
