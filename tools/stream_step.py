@@ -16,6 +16,7 @@ from vvdec.synthetic import random_state_dict   # noqa: E402
 ap = argparse.ArgumentParser()
 ap.add_argument("--streams", type=int, default=256)
 ap.add_argument("--steps", type=int, default=8)
+ap.add_argument("--profile", action="store_true", help="per-kernel CUDA-event times of the step (eager launches, warm caches)")
 a = ap.parse_args()
 g = vvdec.Geometry()
 dec = vvdec.B200AcousticDecoder(g, device=0)
@@ -31,3 +32,15 @@ for i in range(a.steps):
 e1.record()
 torch.cuda.synchronize()
 print(f"last step {e0.elapsed_time(e1):.3f} ms, launches per step {dec.take_launch_count() // a.steps}, out {tuple(y.shape)}")
+if a.profile:
+    dec.set_profiling(True)
+    n = 20
+    for _ in range(n):
+        dec.decode(lat, cache=cache, sample_indices=idx, use_cache=True)
+    rows = dec.read_profile()
+    dec.set_profiling(False)
+    tot = sum(r["ms"] for r in rows) / n
+    print(f"per step (event-timed, sum {tot * 1e3:.0f} us):")
+    for r in sorted(rows, key=lambda r: (r["stage"], r["kind"])):
+        print(f"  stage {r['stage']} {r['kind']:12s} {r['launches'] // n:3d} launches  {r['ms'] / n * 1e3:7.1f} us  "
+              f"({r['ms'] / r['launches'] * 1e3:6.1f} us each)")

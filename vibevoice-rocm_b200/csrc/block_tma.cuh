@@ -425,10 +425,12 @@ block_tma_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
       tile_of(it, b, t0);
       uint8_t* slot = sXY + s * L::XY_BYTES;
       float* rs = sRstd + s * L::RSTD_STRIDE;
-      mbar_wait(&x_full[s], (uint32_t)((it / NX) & 1));
+      // the stream's state pointers (two dependent global loads) are only needed by tiles that read the context (item start)
+      // or save it (the item's last 6 rows); they are fetched before the wait for the x tile
       const uint8_t* rd8 = nullptr;
       uint8_t* wr8 = nullptr;
-      if (STATE && p.st.base != nullptr) p.st.resolve(b, rd8, wr8);
+      if (STATE && p.st.base != nullptr && (t0 == 0 || t0 + 128 > p.rows_pb - 6)) p.st.resolve(b, rd8, wr8);
+      mbar_wait(&x_full[s], (uint32_t)((it / NX) & 1));
       if (warp == WARP_S1 && lane < L::HALO) {
         // halo rows (slot rows 0..7 = t0 - 8 .. t0 - 1): at the item start rows 2..7 are the stream's cached raw rows
         // (TMA delivered zeros = the offline causal pad, :398-403)

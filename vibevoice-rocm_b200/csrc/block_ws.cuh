@@ -436,11 +436,13 @@ block_ws_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__
     auto stat1 = [&](int it) {
       int b, t0;
       tile_of(it, b, t0);
-      mbar_wait(x_full, (uint32_t)(it & 1));
-      if (threadIdx.x == WARP_R * 32) VV_BWT(1, it);
+      // the stream's state pointers are two dependent global loads: only tiles that read the context (item start) or save it
+      // (the item's last 6 rows) need them, and they are fetched while the x tile is still in flight
       const uint8_t* rd8 = nullptr;
       uint8_t* wr8 = nullptr;
-      if (STATE && p.st.base != nullptr) p.st.resolve(b, rd8, wr8);
+      if (STATE && p.st.base != nullptr && (t0 == 0 || t0 + 128 > p.rows_pb - 6)) p.st.resolve(b, rd8, wr8);
+      mbar_wait(x_full, (uint32_t)(it & 1));
+      if (threadIdx.x == WARP_R * 32) VV_BWT(1, it);
       if (warp == WARP_R + 3 && lane < L::HALO) {
         // halo rows (slot rows 0..7 = t0 - 8 .. t0 - 1): at the item start rows 2..7 are the stream's cached raw rows
         // (TMA delivered zeros = the offline causal pad, :398-403)
