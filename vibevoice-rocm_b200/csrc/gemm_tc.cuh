@@ -55,6 +55,10 @@ struct GemmArgs {
   // (nbatch = 1): the padded bf16 copy then addresses item = m / ob_rows_pb, t = m % ob_rows_pb (gemm_tc2 only).
   int ob_rows_pb;
   long long ob_row0;
+  // gemm_tc2 only, nbatch == 1, fp32-out bias epilogue: the K loop is cut into k_slices equal parts that run as separate
+  // tiles (more CTAs streaming weights when there are few output tiles) and write PARTIAL sums into k_slices output planes
+  // (the output map's third coordinate); plane 0 carries the bias.  The consumer adds the planes in a fixed order.
+  int k_slices;         // 0 / 1 = off
 };
 
 template <int BN, int BK>

@@ -105,9 +105,10 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   const int tiles_t = (g.rows + bt - 1) >> g.bt_log2;
   const int tiles_b = (g.nbatch + bb - 1) / bb;
   const int tiles_n = g.N / BN;
-  const long long ntiles = (long long)tiles_t * tiles_b * tiles_n;
+  const int KS = g.k_slices > 1 ? g.k_slices : 1;        // K slices as separate tiles (GemmArgs::k_slices)
+  const long long ntiles = (long long)tiles_t * tiles_b * tiles_n * KS;
   const long long my_tiles = (ntiles > blockIdx.x) ? (ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
-  const int nk = g.n_taps * g.kb_per_tap;
+  const int nk = g.n_taps * g.kb_per_tap / KS;           // k-blocks per tile (the host checks divisibility)
 
   if (threadIdx.x == 0) {
     tma_prefetch_desc(&tmA);
@@ -135,8 +136,10 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   pdl_wait();
 
   // tile index -> (n, t, b) coordinates
-  auto tile_coords = [&](long long it, int& tile_n, int& tile_t, int& tile_b) {
-    const long long tile = blockIdx.x + it * gridDim.x;
+  auto tile_coords = [&](long long it, int& tile_n, int& tile_t, int& tile_b, int& slice) {
+    long long tile = blockIdx.x + it * gridDim.x;
+    slice = (int)(tile % KS);
+    tile /= KS;
     tile_n = (int)(tile % tiles_n);
     const long long tm = tile / tiles_n;
     tile_t = (int)(tm % tiles_t);
@@ -148,9 +151,10 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     if (elect_one()) {
       long long kbg = 0;                                  // global k-block counter (ring position)
       for (long long it = 0; it < my_tiles; ++it) {
-        int tile_n, tile_t, tile_b;
-        tile_coords(it, tile_n, tile_t, tile_b);
-        for (int kb = 0; kb < nk; ++kb, ++kbg) {
+        int tile_n, tile_t, tile_b, slice;
+        tile_coords(it, tile_n, tile_t, tile_b, slice);
+        for (int kl = 0; kl < nk; ++kl, ++kbg) {
+          const int kb = slice * nk + kl;
           const int s = (int)(kbg % S);
           mbar_wait(&empty[s], (uint32_t)(((kbg / S) & 1) ^ 1));
           const int tap = kb / g.kb_per_tap;
@@ -191,8 +195,8 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     const int colgrp = (warp - 2) >> 2;                   // columns [colgrp*CPW, +CPW) of the tile
     const int r = q * 32 + lane;
     for (long long it = 0; it < my_tiles; ++it) {
-      int tile_n, tile_t, tile_b;
-      tile_coords(it, tile_n, tile_t, tile_b);
+      int tile_n, tile_t, tile_b, slice;
+      tile_coords(it, tile_n, tile_t, tile_b, slice);
       const int ab = (int)(it & 1);
       mbar_wait(&acc_full[ab], (uint32_t)((it >> 1) & 1));
 #pragma unroll 1
@@ -230,7 +234,8 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
           float x[32];
 #pragma unroll
           for (int i = 0; i < 8; ++i) {
-            const float4 bv = __ldg(reinterpret_cast<const float4*>(g.bias + n + i * 4));
+            float4 bv = __ldg(reinterpret_cast<const float4*>(g.bias + n + i * 4));
+            if (slice != 0) bv = make_float4(0.f, 0.f, 0.f, 0.f);          // partial-sum planes: plane 0 carries the bias
             float4* cell = reinterpret_cast<float4*>(box + ((i ^ (r & 7)) * 16));
             float4 o;
             o.x = __uint_as_float(v[i * 4 + 0]) + bv.x;
@@ -286,11 +291,11 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     if (elect_one()) {
       const long long total_e = my_tiles * NSUB;
       auto sub_coords = [&](long long e, int& col, int& t0, int& b0) {
-        int tile_n, tile_t, tile_b;
-        tile_coords(e / NSUB, tile_n, tile_t, tile_b);
+        int tile_n, tile_t, tile_b, slice;
+        tile_coords(e / NSUB, tile_n, tile_t, tile_b, slice);
         col = tile_n * BN + (int)(e % NSUB) * SUBW;
         t0 = tile_t * bt;
-        b0 = tile_b * bb;
+        b0 = tile_b * bb + slice;          // k_slices > 1 only with nbatch == 1: the output's third coordinate is the plane
       };
       auto load_resid = [&](long long e) {                // residual sub-tile -> its staging slot
         const int ss = (int)(e % NSTG);

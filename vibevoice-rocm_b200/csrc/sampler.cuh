@@ -59,7 +59,10 @@ __global__ void samp_dup_latent_kernel(const float* __restrict__ x, __nv_bfloat1
 // w == nullptr: no affine weight (FinalLayer.norm_final, elementwise_affine=False :178).
 struct SampNormArgs {
   float* x;                  // [rows, H] fp32, updated in place when f != nullptr
-  const float* f;            // [rows, H] previous layer's down_proj output, or nullptr
+  const float* f;            // [f_planes][rows, H] previous layer's down_proj output as partial sums over K slices (plane 0
+                             // carries the bias; added in plane order), or nullptr
+  int f_planes;
+  long long f_plane_stride;  // elements between planes
   const float* mod;          // [rows, NM] all adaLN outputs of this step
   int NM;
   int gate_off;              // column of the PREVIOUS layer's gate (used with f)
@@ -90,7 +93,11 @@ __global__ void __launch_bounds__(SAMP_NORM_THREADS) samp_norm_mod_kernel(const 
     if (i < nv) {
       v[k] = reinterpret_cast<const float4*>(xr)[i];
       if (p.f != nullptr) {
-        const float4 fv = reinterpret_cast<const float4*>(p.f + (long long)r * p.H)[i];
+        float4 fv = reinterpret_cast<const float4*>(p.f + (long long)r * p.H)[i];
+        for (int pl = 1; pl < p.f_planes; ++pl) {
+          const float4 pv = reinterpret_cast<const float4*>(p.f + pl * p.f_plane_stride + (long long)r * p.H)[i];
+          fv.x += pv.x; fv.y += pv.y; fv.z += pv.z; fv.w += pv.w;
+        }
         const float4 gv = *reinterpret_cast<const float4*>(mr + p.gate_off + i * 4);
         v[k].x = fmaf(gv.x, fv.x, v[k].x);
         v[k].y = fmaf(gv.y, fv.y, v[k].y);

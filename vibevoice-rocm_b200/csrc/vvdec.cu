@@ -585,6 +585,8 @@ struct EpiOut {
   long long bf16_rpb = 0;       // when > 0: rows per batch item of out_bf16 (overrides rows + bf16_halo)
   int bf16_rows_pb = 0;         // when > 0: the launch is a flat row range starting at bf16_row0 of [items, bf16_rows_pb]
   long long bf16_row0 = 0;
+  int k_slices = 1;             // > 1 (EPI_BIAS_F32, one batch item, persistent kernel): K cut into equal slices that run as
+                                // separate tiles and write partial sums into k_slices planes of out_f32 ([k_slices, rows, N])
 };
 
 // Opt a kernel into its dynamic shared memory size once per (kernel, device): the attribute is per device and
@@ -630,7 +632,16 @@ int launch_gemm_impl(vv_decoder* d, const __nv_bfloat16* A, long long a_rpb, int
   g.out_f32 = e.out_f32; g.of_rpb = rows; g.of_off = 0;
   g.out_bf16 = e.out_bf16; g.ob_rpb = e.bf16_rpb > 0 ? e.bf16_rpb : rows + e.bf16_halo; g.ob_off = e.bf16_halo;
   g.ob_rows_pb = e.bf16_rows_pb; g.ob_row0 = e.bf16_row0;
-  const int nk = g.n_taps * g.kb_per_tap;
+  int nk = g.n_taps * g.kb_per_tap;
+  const int KS = e.k_slices > 1 ? e.k_slices : 1;
+  if (KS > 1) {
+    if (e.epi != EPI_BIAS_F32 || nbatch != 1 || nk % KS != 0 || !(w.BN == G2_BN && w.BK == G2_BK) || d->cfg.gemm_path != 0) {
+      set_error("internal: k_slices=%d needs the bias epilogue, one batch item, %d k-blocks divisible and the persistent kernel", KS, nk);
+      return VV_ERR_UNSUPPORTED;
+    }
+    g.k_slices = KS;
+    nk /= KS;
+  }
   const int per_stage = GEMM_BM * w.BK * 2 + w.BN * w.BK * 2;
   g.stages = std::max(1, std::min(std::min(nk, GEMM_MAX_STAGES), (96 * 1024) / per_stage));
   // tile shape over (rows, batch): 2^k rows x 128/2^k items, whichever needs fewer tiles
@@ -661,7 +672,7 @@ int launch_gemm_impl(vv_decoder* d, const __nv_bfloat16* A, long long a_rpb, int
     // persistent kernel with TMA-staged epilogue (gemm_tc2.cuh)
     CUtensorMap tmR, tmO;
     const uint32_t bt = 1u << best_log2, bb = 128u >> best_log2;
-    const uint64_t odims[3] = {(uint64_t)w.N, (uint64_t)rows, (uint64_t)nbatch};
+    const uint64_t odims[3] = {(uint64_t)w.N, (uint64_t)rows, (uint64_t)nbatch * KS};   // KS > 1: planes of partial sums
     if (e.epi == EPI_GELU_BF16) {
       const uint64_t ostr[2] = {(uint64_t)w.N * 2, (uint64_t)rows * w.N * 2};
       const uint32_t obox[3] = {64u, bt, bb};
@@ -678,15 +689,20 @@ int launch_gemm_impl(vv_decoder* d, const __nv_bfloat16* A, long long a_rpb, int
     const int num_sms = d->num_sms;
     // 256-wide MMA tiles when there are enough of them to keep the tail short (>= 2 waves: measured on the C = 2048
     // FFN); vv_decoder_set_option("gemm_bn256" / "gemm_bn256_waves") overrides (tests force every instantiation)
+    best_tiles *= KS;                                    // K slices run as separate tiles
     const long long ntiles256 = best_tiles * (w.N / 256);
+    // ... or when the wide tiles fit ONE wave where the 128-wide ones would need two (a 256-wide tile costs 1.5-1.8x a
+    // 128-wide one: the sampler's [gate; up] GEMM at 256 streams is 144 wide tiles against 288)
+    const long long ntiles128 = best_tiles * (w.N / w.BN);
     const bool wide = w.has_tm256 && d->opt_bn256 > 0 &&
-                      (d->opt_bn256 == 2 || ntiles256 >= (long long)d->opt_bn256_waves * num_sms);
+                      (d->opt_bn256 == 2 || ntiles256 >= (long long)d->opt_bn256_waves * num_sms ||
+                       (ntiles128 > num_sms && ntiles256 <= num_sms));
     // few tiles (streaming: a frame step of 256 streams has 256 rows at stage 0, i.e. 2 x 16 tiles of 128 x 128 for linear2,
     // each streaming 2 MB of weights through ONE SM): the 64-wide tile doubles the CTAs pulling weights.  Every output
     // element still accumulates its k-blocks in the same order, so results are bit-identical to the 128 / 256-wide tiles
-    // (streaming == offline stays bit-equal whichever way the two calls route).  Residual epilogue only (fp32 out).
-    const bool small64 = !wide && w.has_tm64 && e.epi == EPI_RESID && d->opt_bn64_small != 0 && d->cfg.gemm_path == 0 &&
-                         best_tiles * (w.N / w.BN) * 2 <= (long long)num_sms;
+    // (streaming == offline stays bit-equal whichever way the two calls route).  fp32-out epilogues only (bias, residual).
+    const bool small64 = !wide && w.has_tm64 && (e.epi == EPI_RESID || e.epi == EPI_BIAS_F32) && d->opt_bn64_small != 0 &&
+                         d->cfg.gemm_path == 0 && best_tiles * (w.N / w.BN) * 2 <= (long long)num_sms;
     const long long ntiles = wide ? ntiles256 : small64 ? best_tiles * (w.N / 64) : best_tiles * (w.N / w.BN);
     const unsigned grid2 = (unsigned)std::min<long long>(ntiles, num_sms);
     const bool deep = nk >= 32;   // K >= 2048: mainloop-dominated
@@ -702,7 +718,17 @@ int launch_gemm_impl(vv_decoder* d, const __nv_bfloat16* A, long long a_rpb, int
         launch_k(gemm_tc2_kernel<E, D, 128>, dim3(grid2), dim3(G2Warps<E>::THREADS), Gemm2Cfg<E, D, 128>::TOTAL, s, tmA, w.tm, tmR, tmO, g);  \
       }                                                                                                       \
     } while (0)
-    if (small64) {                       // residual epilogue on the 64-wide tile (only ever set with e.epi == EPI_RESID)
+    if (small64 && e.epi == EPI_BIAS_F32) {     // fp32-out epilogues on the 64-wide tile
+      if (deep) {
+        rc = ensure_smem(gemm_tc2_kernel<EPI_BIAS_F32, true, 64>, (int)Gemm2Cfg<EPI_BIAS_F32, true, 64>::TOTAL, d->cfg.device);
+        if (rc != VV_OK) return rc;
+        launch_k(gemm_tc2_kernel<EPI_BIAS_F32, true, 64>, dim3(grid2), dim3(G2Warps<EPI_BIAS_F32>::THREADS), Gemm2Cfg<EPI_BIAS_F32, true, 64>::TOTAL, s, tmA, w.tm64, tmR, tmO, g);
+      } else {
+        rc = ensure_smem(gemm_tc2_kernel<EPI_BIAS_F32, false, 64>, (int)Gemm2Cfg<EPI_BIAS_F32, false, 64>::TOTAL, d->cfg.device);
+        if (rc != VV_OK) return rc;
+        launch_k(gemm_tc2_kernel<EPI_BIAS_F32, false, 64>, dim3(grid2), dim3(G2Warps<EPI_BIAS_F32>::THREADS), Gemm2Cfg<EPI_BIAS_F32, false, 64>::TOTAL, s, tmA, w.tm64, tmR, tmO, g);
+      }
+    } else if (small64) {
       if (deep) {
         rc = ensure_smem(gemm_tc2_kernel<EPI_RESID, true, 64>, (int)Gemm2Cfg<EPI_RESID, true, 64>::TOTAL, d->cfg.device);
         if (rc != VV_OK) return rc;

@@ -96,6 +96,19 @@ void samp_t_embed(const vv_sampler* sp, double t, float* out) {
 
 struct SampBufs { long long cond, cproj, sc, mod, xin, x, a, gu, hsw, f, v, xlat, mprev, total; };
 
+// K slices of the down_proj GEMM (N = hidden, K = ffn: few output tiles, long K): as many as keep every slice-tile on its
+// own SM, at most 4, dividing the k-block count.  A function of the row count only, so a captured graph and an eager
+// call of the same shape take the same summation order.
+constexpr int SAMP_MAX_KS = 4;
+int samp_down_slices(const vv_sampler* sp, long long R) {
+  const long long tiles = ((R + 127) / 128) * (sp->scfg.hidden / 128);
+  const int nk = sp->scfg.ffn / 64;
+  int ks = 1;
+  for (int k = 2; k <= SAMP_MAX_KS; ++k)
+    if (nk % k == 0 && tiles * k <= sp->core.num_sms && sp->scfg.hidden % 128 == 0) ks = k;
+  return ks;
+}
+
 SampBufs samp_bufs(const vv_sampler* sp, long long R) {
   const long long H = sp->scfg.hidden, F = sp->scfg.ffn, Ld = sp->scfg.latent, NM = sp->NM;
   SampBufs b;
@@ -103,7 +116,7 @@ SampBufs samp_bufs(const vv_sampler* sp, long long R) {
   auto take = [&](long long bytes) { const long long o = off; off += align_up(bytes, 1024); return o; };
   b.cond = take(R * H * 2); b.cproj = take(R * H * 4); b.sc = take(R * H * 2); b.mod = take(R * NM * 4);
   b.xin = take(R * Ld * 2); b.x = take(R * H * 4); b.a = take(R * H * 2); b.gu = take(R * 2 * F * 4);
-  b.hsw = take(R * F * 2); b.f = take(R * H * 4); b.v = take(R * Ld * 4); b.xlat = take(R * Ld * 4); b.mprev = take(R * Ld * 4);
+  b.hsw = take(R * F * 2); b.f = take(SAMP_MAX_KS * R * H * 4); b.v = take(R * Ld * 4); b.xlat = take(R * Ld * 4); b.mprev = take(R * Ld * 4);
   b.total = off + 1024;
   return b;
 }
@@ -132,6 +145,7 @@ int samp_head_pass(vv_sampler* sp, uint8_t* ws, const SampBufs& b, int R, cudaSt
   __nv_bfloat16* HS = reinterpret_cast<__nv_bfloat16*>(ws + b.hsw);
   float* Fo = reinterpret_cast<float*>(ws + b.f);
   float* V = reinterpret_cast<float*>(ws + b.v);
+  const int ks = samp_down_slices(sp, R);
   int rc;
   EpiOut e;
   e.epi = EPI_BIAS_F32;
@@ -145,6 +159,7 @@ int samp_head_pass(vv_sampler* sp, uint8_t* ws, const SampBufs& b, int R, cudaSt
     na.gate_off = l > 0 ? (l - 1) * 3 * H + 2 * H : 0;       // chunk(3): shift | scale | gate (:159)
     na.shift_off = l * 3 * H; na.scale_off = l * 3 * H + H;  // final layer (l == L): chunk(2) at 3 L H (:187)
     na.w = l < L ? sp->norm_w[(size_t)l] : nullptr;
+    na.f_planes = ks; na.f_plane_stride = (long long)R * H;
     launch_k(samp_norm_mod_kernel, dim3((unsigned)R), dim3(SAMP_NORM_THREADS), 0, s, na);
     d->launches++;
     VV_LAUNCH_OK();
@@ -154,8 +169,10 @@ int samp_head_pass(vv_sampler* sp, uint8_t* ws, const SampBufs& b, int R, cudaSt
     launch_k(samp_swiglu_kernel, dim3(samp_grid((long long)R * F / 4, 256)), dim3(256), 0, s, (const float*)GU, HS, R, F);
     d->launches++;
     VV_LAUNCH_OK();
-    e.out_f32 = Fo;
+    e.out_f32 = Fo;                                            // ks planes of partial sums; the next norm kernel adds them
+    e.k_slices = ks;
     if ((rc = launch_gemm(d, HS, R, R, 1, sp->w_down[(size_t)l], e, s)) != VV_OK) return rc;
+    e.k_slices = 1;
   }
   e.out_f32 = V;                                             // FinalLayer.linear (:189)
   return launch_gemm(d, A, R, R, 1, sp->w_final, e, s);
