@@ -26,7 +26,10 @@ namespace vv {
 enum GemmEpilogue : int {
   EPI_BIAS_F32 = 0,   // out_f32 = acc + bias                                  (stem, upsample)
   EPI_GELU_BF16 = 1,  // out_bf16 = bf16(gelu_erf(acc + bias))                  (FFN linear1, :594-595)
-  EPI_RESID = 2       // v = resid + gamma*(acc + bias); out_f32 = v; out_bf16 = bf16(v) if given (:941-942)
+  EPI_RESID = 2,      // v = resid + gamma*(acc + bias); out_f32 = v; out_bf16 = bf16(v) if given (:941-942)
+  EPI_SWIGLU_BF16 = 3 // gemm_tc2, 256-wide tile only: columns [0,128) of a tile = gate, [128,256) = up of the same 128 hidden
+                      // units (weights packed interleaved); out_bf16[:, tile*128 + j] = bf16(silu(gate_j) * up_j), no bias
+                      // (diffusion head FeedForwardNetwork, modular_vibevoice_diffusion_head.py:117-124)
 };
 
 constexpr int GEMM_BM = 128;

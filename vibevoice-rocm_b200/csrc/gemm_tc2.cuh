@@ -28,7 +28,7 @@ namespace vv {
 // epilogue warps: 8 (two per TMEM lane quarter, 64 columns each) — or 16 (32 columns each) for the GELU epilogue,
 // which is issue-bound and needs more warps in flight to fill the issue slots (measured on the fused FFN: IPC 1.9 -> 2.2+)
 template <int EPI> struct G2Warps {
-  static constexpr int EPI_WARPS = (EPI == EPI_GELU_BF16) ? 16 : 8;
+  static constexpr int EPI_WARPS = (EPI == EPI_GELU_BF16 || EPI == EPI_SWIGLU_BF16) ? 16 : 8;
   static constexpr int THREADS = (2 + EPI_WARPS + 1) * 32;
 };
 constexpr int G2_BN = 128, G2_BK = 64;            // G2_BN: the narrow instantiation (and the epilogue sub-tile width)
@@ -40,8 +40,10 @@ constexpr int G2_BOX_BYTES = 128 * 128;           // one staged box: 128 rows x 
 template <int EPI, bool DEEP, int BN>
 struct Gemm2Cfg {
   static_assert(BN == 64 || BN == 128 || BN == 256, "tile width");
-  static constexpr bool OUT_BF16 = (EPI == EPI_GELU_BF16);
+  static constexpr bool OUT_BF16 = (EPI == EPI_GELU_BF16 || EPI == EPI_SWIGLU_BF16);
   static_assert(BN != 64 || !OUT_BF16, "the 64-wide tile has fp32 epilogues only");
+  static_assert(EPI != EPI_SWIGLU_BF16 || BN == 256, "the SwiGLU epilogue pairs the two halves of a 256-wide tile");
+  static constexpr int OUTW = (EPI == EPI_SWIGLU_BF16) ? BN / 2 : BN;   // output columns one MMA tile produces
   static constexpr int COLS_PER_BOX = OUT_BF16 ? 64 : 32;
   // epilogue sub-tile: 128 columns, or 64 for the fp32 epilogues of the wide tile (32 KB of staging instead of 64 KB
   // buys a 4th ring stage for long K loops, or a second staging slot for short ones)
@@ -49,7 +51,7 @@ struct Gemm2Cfg {
 #define VV_G2_SUBW128_NARROW 0     // 1: 128-column fp32 sub-tiles on the 128-wide tile (the earlier layout; A/B: the
 #endif                             //    64 -> 128-channel upsampler runs 4.2 ms with it, 3.15 ms without)
   static constexpr int SUBW = (!OUT_BF16 && (BN != 128 || !VV_G2_SUBW128_NARROW)) ? 64 : 128;
-  static constexpr int NSUB = BN / SUBW;                             // sub-tiles per MMA tile: 1, 2 or 4
+  static constexpr int NSUB = OUTW / SUBW;                           // sub-tiles per MMA tile: 1, 2 or 4
   static constexpr int BOXES = SUBW / COLS_PER_BOX;                  // per sub-tile: 2 or 4
   static constexpr int STG_BYTES = BOXES * G2_BOX_BYTES;             // 32 KB or 64 KB
   static constexpr int B_BYTES = BN * G2_BK * 2;                     // 16 KB or 32 KB
@@ -203,7 +205,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       for (int h = 0; h < NSUB; ++h) {                    // 128-column sub-tiles of the accumulator
       const long long e = it * NSUB + h;
       const int ss = (int)(e % NSTG);
-      const int n0 = tile_n * BN + h * SUBW + colgrp * CPW;
+      const int n0 = tile_n * Cfg::OUTW + h * SUBW + colgrp * CPW;
       if (EPI == EPI_RESID) mbar_wait(&stg_full[ss], (uint32_t)((e / NSTG) & 1));
       else mbar_wait(&stg_empty[ss], (uint32_t)(((e / NSTG) & 1) ^ 1));
       tc_fence_after();
@@ -215,7 +217,26 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         tmem_ld_wait();
         const int n = n0 + c * 32;                        // global column of v[0]
         const int nl = colgrp * CPW + c * 32;             // column inside the sub-tile
-        if (EPI == EPI_GELU_BF16) {
+        if (EPI == EPI_SWIGLU_BF16) {
+          // v = gate columns; the matching up columns sit 128 accumulator columns further.  silu(g) * u -> bf16
+          uint32_t u[32];
+          tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(ab * BN + 128 + colgrp * CPW + c * 32), u);
+          tmem_ld_wait();
+          uint8_t* box = stg + (nl >> 6) * G2_BOX_BYTES;
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            uint32_t pkv[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const float g0 = __uint_as_float(v[i * 8 + 2 * j]), g1 = __uint_as_float(v[i * 8 + 2 * j + 1]);
+              const float h0 = g0 / (1.0f + __expf(-g0)) * __uint_as_float(u[i * 8 + 2 * j]);
+              const float h1 = g1 / (1.0f + __expf(-g1)) * __uint_as_float(u[i * 8 + 2 * j + 1]);
+              pkv[j] = pack_bf16x2(h0, h1);
+            }
+            const int chunk = (((nl & 63) >> 3) + i) ^ (r & 7);
+            *reinterpret_cast<uint4*>(box + chunk * 16) = make_uint4(pkv[0], pkv[1], pkv[2], pkv[3]);
+          }
+        } else if (EPI == EPI_GELU_BF16) {
           uint8_t* box = stg + (nl >> 6) * G2_BOX_BYTES;  // 64 bf16 columns per box
 #pragma unroll
           for (int i = 0; i < 4; ++i) {
@@ -293,7 +314,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       auto sub_coords = [&](long long e, int& col, int& t0, int& b0) {
         int tile_n, tile_t, tile_b, slice;
         tile_coords(e / NSUB, tile_n, tile_t, tile_b, slice);
-        col = tile_n * BN + (int)(e % NSUB) * SUBW;
+        col = tile_n * Cfg::OUTW + (int)(e % NSUB) * SUBW;
         t0 = tile_t * bt;
         b0 = tile_b * bb + slice;          // k_slices > 1 only with nbatch == 1: the output's third coordinate is the plane
       };

@@ -7,8 +7,9 @@
 //   mod = sc  x [adaLN_0 | ... | adaLN_{L-1} | adaLN_final]^T                 one tcgen05 GEMM, N = (3L + 2) H
 //   x   = bf16(latent, both halves) x noisy_images_proj^T                     samp_dup_latent_kernel + GEMM (K = 64)
 //   per layer:  [x += gate * f of the previous layer;]  a = bf16( RMSNorm(x) w (1 + scale) + shift )   samp_norm_mod_kernel
-//               gu = a x [gate_proj ; up_proj]^T   (GEMM, N = 2F);   h = bf16( silu(g) * u )           samp_swiglu_kernel
-//               f  = h x down_proj^T               (GEMM, K = F)
+//               h = bf16( silu(g) * u ),  [g | u] = a x [gate_proj ; up_proj]^T   one GEMM (N = 2F, weights interleaved in
+//                   128-unit blocks) with the SwiGLU in its epilogue (EPI_SWIGLU_BF16); samp_swiglu_kernel is the unfused form
+//               f  = h x down_proj^T               (GEMM, K = F, as K slices: partial-sum planes added by the next norm)
 //   final:      x += gate * f;  a = bf16( RMSNorm(x) (1 + scale_f) + shift_f );  v = a x linear^T (GEMM, N = 64)
 //   solver:     eps = v_u + s (v_c - v_u);  m0 = alpha_s x - sigma_s eps;  x' = A x + B m0 + D (m0 - m1)   samp_solver_kernel
 // Everything between GEMMs is fp32; GEMM operands are bf16 (like the tokenizer path).  All kernels are HBM-trivial

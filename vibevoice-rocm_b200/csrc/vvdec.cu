@@ -673,7 +673,14 @@ int launch_gemm_impl(vv_decoder* d, const __nv_bfloat16* A, long long a_rpb, int
     CUtensorMap tmR, tmO;
     const uint32_t bt = 1u << best_log2, bb = 128u >> best_log2;
     const uint64_t odims[3] = {(uint64_t)w.N, (uint64_t)rows, (uint64_t)nbatch * KS};   // KS > 1: planes of partial sums
-    if (e.epi == EPI_GELU_BF16) {
+    if (e.epi == EPI_SWIGLU_BF16) {                     // [rows, N / 2] bf16: a 256-wide tile yields 128 output columns
+      if (!w.has_tm256 || KS != 1) { set_error("internal: the SwiGLU epilogue needs N %% 256 == 0"); return VV_ERR_UNSUPPORTED; }
+      const uint64_t sdims[3] = {(uint64_t)w.N / 2, (uint64_t)rows, (uint64_t)nbatch};
+      const uint64_t ostr[2] = {(uint64_t)w.N, (uint64_t)rows * w.N};
+      const uint32_t obox[3] = {64u, bt, bb};
+      rc = encode_map(&tmO, e.out_bf16, 3, sdims, ostr, obox, false);
+      tmR = tmO;
+    } else if (e.epi == EPI_GELU_BF16) {
       const uint64_t ostr[2] = {(uint64_t)w.N * 2, (uint64_t)rows * w.N * 2};
       const uint32_t obox[3] = {64u, bt, bb};
       rc = encode_map(&tmO, e.out_bf16, 3, odims, ostr, obox, false);
@@ -694,9 +701,10 @@ int launch_gemm_impl(vv_decoder* d, const __nv_bfloat16* A, long long a_rpb, int
     // ... or when the wide tiles fit ONE wave where the 128-wide ones would need two (a 256-wide tile costs 1.5-1.8x a
     // 128-wide one: the sampler's [gate; up] GEMM at 256 streams is 144 wide tiles against 288)
     const long long ntiles128 = best_tiles * (w.N / w.BN);
-    const bool wide = w.has_tm256 && d->opt_bn256 > 0 &&
-                      (d->opt_bn256 == 2 || ntiles256 >= (long long)d->opt_bn256_waves * num_sms ||
-                       (ntiles128 > num_sms && ntiles256 <= num_sms));
+    const bool wide = e.epi == EPI_SWIGLU_BF16 ||
+                      (w.has_tm256 && d->opt_bn256 > 0 &&
+                       (d->opt_bn256 == 2 || ntiles256 >= (long long)d->opt_bn256_waves * num_sms ||
+                        (ntiles128 > num_sms && ntiles256 <= num_sms)));
     // few tiles (streaming: a frame step of 256 streams has 256 rows at stage 0, i.e. 2 x 16 tiles of 128 x 128 for linear2,
     // each streaming 2 MB of weights through ONE SM): the 64-wide tile doubles the CTAs pulling weights.  Every output
     // element still accumulates its k-blocks in the same order, so results are bit-identical to the 128 / 256-wide tiles
@@ -718,7 +726,17 @@ int launch_gemm_impl(vv_decoder* d, const __nv_bfloat16* A, long long a_rpb, int
         launch_k(gemm_tc2_kernel<E, D, 128>, dim3(grid2), dim3(G2Warps<E>::THREADS), Gemm2Cfg<E, D, 128>::TOTAL, s, tmA, w.tm, tmR, tmO, g);  \
       }                                                                                                       \
     } while (0)
-    if (small64 && e.epi == EPI_BIAS_F32) {     // fp32-out epilogues on the 64-wide tile
+    if (e.epi == EPI_SWIGLU_BF16) {
+      if (deep) {
+        rc = ensure_smem(gemm_tc2_kernel<EPI_SWIGLU_BF16, true, 256>, (int)Gemm2Cfg<EPI_SWIGLU_BF16, true, 256>::TOTAL, d->cfg.device);
+        if (rc != VV_OK) return rc;
+        launch_k(gemm_tc2_kernel<EPI_SWIGLU_BF16, true, 256>, dim3(grid2), dim3(G2Warps<EPI_SWIGLU_BF16>::THREADS), Gemm2Cfg<EPI_SWIGLU_BF16, true, 256>::TOTAL, s, tmA, w.tm256, tmR, tmO, g);
+      } else {
+        rc = ensure_smem(gemm_tc2_kernel<EPI_SWIGLU_BF16, false, 256>, (int)Gemm2Cfg<EPI_SWIGLU_BF16, false, 256>::TOTAL, d->cfg.device);
+        if (rc != VV_OK) return rc;
+        launch_k(gemm_tc2_kernel<EPI_SWIGLU_BF16, false, 256>, dim3(grid2), dim3(G2Warps<EPI_SWIGLU_BF16>::THREADS), Gemm2Cfg<EPI_SWIGLU_BF16, false, 256>::TOTAL, s, tmA, w.tm256, tmR, tmO, g);
+      }
+    } else if (small64 && e.epi == EPI_BIAS_F32) {     // fp32-out epilogues on the 64-wide tile
       if (deep) {
         rc = ensure_smem(gemm_tc2_kernel<EPI_BIAS_F32, true, 64>, (int)Gemm2Cfg<EPI_BIAS_F32, true, 64>::TOTAL, d->cfg.device);
         if (rc != VV_OK) return rc;

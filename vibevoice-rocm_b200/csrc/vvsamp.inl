@@ -115,7 +115,7 @@ SampBufs samp_bufs(const vv_sampler* sp, long long R) {
   long long off = 0;
   auto take = [&](long long bytes) { const long long o = off; off += align_up(bytes, 1024); return o; };
   b.cond = take(R * H * 2); b.cproj = take(R * H * 4); b.sc = take(R * H * 2); b.mod = take(R * NM * 4);
-  b.xin = take(R * Ld * 2); b.x = take(R * H * 4); b.a = take(R * H * 2); b.gu = take(R * 2 * F * 4);
+  b.xin = take(R * Ld * 2); b.x = take(R * H * 4); b.a = take(R * H * 2); b.gu = take(1024);   // (the [gate | up] tensor no longer exists: SwiGLU runs in the GEMM epilogue)
   b.hsw = take(R * F * 2); b.f = take(SAMP_MAX_KS * R * H * 4); b.v = take(R * Ld * 4); b.xlat = take(R * Ld * 4); b.mprev = take(R * Ld * 4);
   b.total = off + 1024;
   return b;
@@ -135,13 +135,12 @@ unsigned samp_grid(long long work, int block) { return (unsigned)std::max<long l
 // One head forward on R rows whose bf16 inputs (xin [R, latent]) and modulation input (sc [R, H]) are in the workspace.
 int samp_head_pass(vv_sampler* sp, uint8_t* ws, const SampBufs& b, int R, cudaStream_t s) {
   vv_decoder* d = &sp->core;
-  const int H = sp->scfg.hidden, F = sp->scfg.ffn, L = sp->scfg.layers;
+  const int H = sp->scfg.hidden, L = sp->scfg.layers;
   __nv_bfloat16* SC = reinterpret_cast<__nv_bfloat16*>(ws + b.sc);
   float* MOD = reinterpret_cast<float*>(ws + b.mod);
   __nv_bfloat16* XIN = reinterpret_cast<__nv_bfloat16*>(ws + b.xin);
   float* X = reinterpret_cast<float*>(ws + b.x);
   __nv_bfloat16* A = reinterpret_cast<__nv_bfloat16*>(ws + b.a);
-  float* GU = reinterpret_cast<float*>(ws + b.gu);
   __nv_bfloat16* HS = reinterpret_cast<__nv_bfloat16*>(ws + b.hsw);
   float* Fo = reinterpret_cast<float*>(ws + b.f);
   float* V = reinterpret_cast<float*>(ws + b.v);
@@ -164,11 +163,9 @@ int samp_head_pass(vv_sampler* sp, uint8_t* ws, const SampBufs& b, int R, cudaSt
     d->launches++;
     VV_LAUNCH_OK();
     if (l == L) break;
-    e.out_f32 = GU;
-    if ((rc = launch_gemm(d, A, R, R, 1, sp->w_gu[(size_t)l], e, s)) != VV_OK) return rc;
-    launch_k(samp_swiglu_kernel, dim3(samp_grid((long long)R * F / 4, 256)), dim3(256), 0, s, (const float*)GU, HS, R, F);
-    d->launches++;
-    VV_LAUNCH_OK();
+    EpiOut eg;                                                 // [gate; up] GEMM with the SwiGLU in its epilogue: h = bf16
+    eg.epi = EPI_SWIGLU_BF16; eg.out_bf16 = HS;
+    if ((rc = launch_gemm(d, A, R, R, 1, sp->w_gu[(size_t)l], eg, s)) != VV_OK) return rc;
     e.out_f32 = Fo;                                            // ks planes of partial sums; the next norm kernel adds them
     e.k_slices = ks;
     if ((rc = launch_gemm(d, HS, R, R, 1, sp->w_down[(size_t)l], e, s)) != VV_OK) return rc;
@@ -186,10 +183,10 @@ int samp_head_pass(vv_sampler* sp, uint8_t* ws, const SampBufs& b, int R, cudaSt
 extern "C" int32_t vv_sampler_create(const vv_sampler_config* cfg, vv_sampler** out) {
   if (cfg == nullptr || out == nullptr) { set_error("null argument"); return VV_ERR_INVALID_ARG; }
   *out = nullptr;
-  if (cfg->hidden < 128 || cfg->hidden % 128 != 0 || cfg->hidden > 4096 || cfg->ffn < 64 || cfg->ffn % 64 != 0 ||
+  if (cfg->hidden < 128 || cfg->hidden % 128 != 0 || cfg->hidden > 4096 || cfg->ffn < 128 || cfg->ffn % 128 != 0 ||
       cfg->latent != 64 || cfg->layers < 1 || cfg->layers > 16 || cfg->train_steps < 2) {
     set_error("unsupported diffusion head: hidden=%d ffn=%d latent=%d layers=%d (kernels take hidden %% 128 == 0 <= 4096, "
-              "ffn %% 64 == 0, latent == 64)", cfg->hidden, cfg->ffn, cfg->latent, cfg->layers);
+              "ffn %% 128 == 0, latent == 64)", cfg->hidden, cfg->ffn, cfg->latent, cfg->layers);
     return VV_ERR_UNSUPPORTED;
   }
   int ndev = 0;
@@ -254,9 +251,13 @@ extern "C" int32_t vv_sampler_finalize(vv_sampler* sp) {
     const auto* nw = pk.get(p + "norm.weight", {H});
     const auto* ad = pk.get(p + "adaLN_modulation.1.weight", {3 * H, H});
     if (pk.status != VV_OK) break;
+    // rows interleaved in blocks of 128 hidden units: [gate 0..127 | up 0..127 | gate 128..255 | up 128..255 | ...], so a
+    // 256-wide GEMM tile holds gate and up of the same units and its epilogue applies SwiGLU (EPI_SWIGLU_BF16)
     std::vector<float> gu((size_t)2 * F * H);
-    memcpy(gu.data(), g->data(), sizeof(float) * (size_t)F * H);
-    memcpy(gu.data() + (size_t)F * H, u->data(), sizeof(float) * (size_t)F * H);
+    for (int t = 0; t < F / 128; ++t) {
+      memcpy(gu.data() + (size_t)(2 * t) * 128 * H, g->data() + (size_t)t * 128 * H, sizeof(float) * (size_t)128 * H);
+      memcpy(gu.data() + (size_t)(2 * t + 1) * 128 * H, u->data() + (size_t)t * 128 * H, sizeof(float) * (size_t)128 * H);
+    }
     vv::DenseW wgu, wdn;
     pk.dense(wgu, to_bf16(gu), zeros(2 * F), 2 * F, H, 1);
     pk.dense(wdn, to_bf16(*dn), zeros(H), H, F, 1);
