@@ -1,4 +1,5 @@
-"""Timeline of block_ws_kernel (build with -DVV_BW_TRACE, VVDEC_LIB=that build): clock64 stamps of CTA 0, tiles 8..23."""
+"""Timeline of block_ws_kernel / block_tma_kernel (build with -DVV_BW_TRACE, VVDEC_LIB=that build): clock64 stamps of CTA 0,
+tiles 8..23.   python tools/micro/bw_trace.py [stage]"""
 import ctypes as C, os, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 for p in (ROOT, os.path.join(ROOT, "vibevoice-rocm_b200")):
@@ -10,11 +11,13 @@ dec = vvdec.B200AcousticDecoder(g, device=0)
 dec.load_state_dict(random_state_dict(g))
 lib, h = dec._lib, dec._h
 st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
-rows = 5760 * 800
+stage = int(sys.argv[1]) if len(sys.argv) > 1 else 4          # 4: block_ws_kernel; 5 / 6: block_tma_kernel
+Cc = g.stage_channels(stage)
+rows = 5760 * (102400 // Cc)
 P = lambda t: C.c_void_p(t.data_ptr())
-x = torch.randn(1, rows, 128, device="cuda"); out = torch.empty_like(x)
+x = torch.randn(1, rows, Cc, device="cuda"); out = torch.empty_like(x)
 for _ in range(3):
-    assert lib.vv_kernel_block(h, 4, 0, P(x), P(out), 1, rows, st) == 0
+    assert lib.vv_kernel_block(h, stage, 0, P(x), P(out), 1, rows, st) == 0
 torch.cuda.synchronize()
 buf = (C.c_longlong * 512)()
 raw = C.CDLL(os.environ["VVDEC_LIB"])

@@ -42,16 +42,27 @@ namespace vv {
 #define VV_BT_HC 64         // hidden units per GEMM-1 chunk (64, or 128 at C = 64 with two D2 buffers)
 #endif
 #ifndef VV_BT_NX64
-#define VV_BT_NX64 4        // x/y ring slots at C = 64 (34 KB each).  A slot is held from its TMA load until its TMA store has
-                            // drained (~3 tile times): with 3 slots the pipeline starved (ncu: nothing saturated, issue 51 %);
-                            // 4 slots + ONE a tile: 1.371 -> 1.240 ms per 5760 frames (same box, profiles/block_tma_nx4_ab_r02.txt)
+#define VV_BT_NX64 3        // x/y ring slots at C = 64 (34 KB each).  Third build: a slot is released as soon as the S3 warps hold
+                            // its y rows (the clock64 timeline of the second build, profiles/block_tma_timeline_r02.txt, showed a
+                            // slot's life of 17 500 clocks = 4 tile periods with 4 slots, 9 000 of them spent waiting for the GEMM
+                            // phase only to receive the output at its end); the output goes through a separate ring of staging
+                            // boxes.  History: 3 slots held to the store 1.371 ms, 4 slots 1.240 ms per 5760 frames
+#endif
+#ifndef VV_BT_NSTG
+#define VV_BT_NSTG 2        // output staging boxes of [128 rows, 32 fp32] (16 KB each) at C = 64; 4 at C = 32
 #endif
 #ifndef VV_BT_NX32
 #define VV_BT_NX32 6        // at C = 32 (17 KB each)
 #endif
-#ifndef VV_BT_NA64
-#define VV_BT_NA64 1        // GEMM-1 operand (a) tiles at C = 64 (16 KB each): GEMM 1 has read the tile half a tile time before
-                            // E1 is done with its last chunk, so S3 refills a single tile in time; 1 frees room for the 4th slot
+
+#ifdef VV_BW_TRACE     // timeline instrumentation (A/B builds only): clock64 stamps of CTA 0 for its tiles [8, 24)
+__device__ long long vv_bw_trace[16 * 32];
+#define VV_BWT(slot, it)                                                                                 \
+  do {                                                                                                   \
+    if (blockIdx.x == 0 && (it) >= 8 && (it) < 24) vv_bw_trace[((it) - 8) * 32 + (slot)] = clock64();    \
+  } while (0)
+#else
+#define VV_BWT(slot, it) do { } while (0)
 #endif
 
 struct BlockTmaArgs {
@@ -83,7 +94,7 @@ struct BlockTmaCfg {
   static constexpr int XBOX_BYTES = XROWS * 128;     // 17 408 = 17 KB: box bases stay 1 KB aligned
   static constexpr int XY_BYTES = NBOX * XBOX_BYTES;
   static constexpr int NX = (C == 64) ? VV_BT_NX64 : VV_BT_NX32;
-  static constexpr int NA = (C == 64) ? VV_BT_NA64 : 4;
+  static constexpr int NA = 2;                        // GEMM-1 operand buffers, in TENSOR memory (C / 2 packed columns each)
   static constexpr int E1W = 8, E2W = 4, S1W = 4, S3W = 4, S2W = 4, CTRL = 4;
   static constexpr int STRIPS = S2W * 32 / LPR;      // 8 (C = 64) or 16 (C = 32)
   static constexpr int R = 128 / STRIPS;             // rows per strip: 16 or 8
@@ -91,26 +102,29 @@ struct BlockTmaCfg {
   static constexpr int THREADS = WARPS * 32;
   static constexpr int W1_BYTES = 4 * C * ROWB;
   static constexpr int W2_BYTES = (4 * C / 64) * C * 128;   // K-blocks of [C rows, 64]
-  static constexpr int A_BYTES = 128 * ROWB;
   static constexpr int RSTD_STRIDE = 144;            // floats per slot (row + 2 is the index: 16 B aligned strip windows)
   static constexpr int OFF_W1 = 0;
   static constexpr int OFF_W2 = OFF_W1 + W1_BYTES;
-  static constexpr int OFF_A = OFF_W2 + W2_BYTES;
-  static constexpr int OFF_XY = OFF_A + NA * A_BYTES;
-  static constexpr int OFF_RSTD = OFF_XY + NX * XY_BYTES;
+  static constexpr int OFF_XY = OFF_W2 + W2_BYTES;
+  static constexpr int NSTG = (C == 64) ? VV_BT_NSTG : 4;     // output staging boxes, used round-robin box by box
+  static constexpr int OBOX_BYTES = 128 * 128;
+  static constexpr int OFF_STG = OFF_XY + NX * XY_BYTES;
+  static constexpr int OFF_RSTD = OFF_STG + NSTG * OBOX_BYTES;
   static constexpr int OFF_BAR = OFF_RSTD + NX * RSTD_STRIDE * 4;
   static constexpr int ND2 = (3 * HC + 4 * C <= 512) ? 4 : 2;      // D2 accumulators (S3 preloads one while E2 drains another)
-  static constexpr int NBARS = 1 + 5 * NX + 2 * NA + 8 + 3 * ND2;
+  static constexpr int NBARS = 1 + 4 * NX + 2 * NSTG + 2 * NA + 8 + 3 * ND2;
+  static_assert(OFF_STG % 1024 == 0, "swizzled staging boxes need 1 KB aligned bases");
   static constexpr int TOTAL = OFF_BAR + 512 + 1024;
   static_assert(NBARS * 8 + 8 <= 512, "barrier block");
   static_assert(OFF_XY % 1024 == 0 && XBOX_BYTES % 1024 == 0, "swizzled boxes need 1 KB aligned bases");
   static_assert(TOTAL <= 232448, "exceeds the 227 KB dynamic shared memory limit");
-  static constexpr uint32_t TMEM_COLS = 512;         // D1: 2 x HC at 0; H: 2 x HC/2 at 2 HC; D2: ND2 x C at 3 HC
-  static constexpr uint32_t H_COL0 = 2 * HC, D2_COL0 = 3 * HC;
+  static constexpr uint32_t TMEM_COLS = 512;         // D1: 2 x HC at 0; H: 2 x HC/2 at 2 HC; D2: ND2 x C at 3 HC; a: NA x C/2
+  static constexpr uint32_t H_COL0 = 2 * HC, D2_COL0 = 3 * HC, A_COL0 = 3 * HC + ND2 * C;
+  static_assert(A_COL0 + NA * (C / 2) <= 512, "tensor memory columns (HC = 128 leaves no room for the operand: use HC = 64)");
   static_assert(3 * HC + ND2 * C <= 512, "tensor memory columns");
   // register budgets (setmaxnreg draws from the CTA's launch allocation: threads x launch registers)
   static constexpr int REG_LAUNCH = (65536 / THREADS) / 8 * 8;
-  static constexpr int REG_E1 = 64, REG_E2 = 64, REG_S1 = 40, REG_S3 = (C == 64) ? 96 : 64, REG_S2 = 112, REG_CTRL = 32;
+  static constexpr int REG_E1 = 64, REG_E2 = 72, REG_S1 = 48, REG_S3 = (C == 64) ? 104 : 64, REG_S2 = 112, REG_CTRL = 32;
   static_assert(32 * (E1W * REG_E1 + E2W * REG_E2 + S1W * REG_S1 + S3W * REG_S3 + S2W * REG_S2 + CTRL * REG_CTRL) <=
                     THREADS * REG_LAUNCH, "setmaxnreg budget exceeds the CTA's launch allocation");
 };
@@ -134,17 +148,19 @@ block_tma_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
   uint8_t* smem = smem_align_1k(smem_raw);
   uint8_t* sW1 = smem + L::OFF_W1;
   uint8_t* sW2 = smem + L::OFF_W2;
-  uint8_t* sA = smem + L::OFF_A;
   uint8_t* sXY = smem + L::OFF_XY;
+  uint8_t* sStg = smem + L::OFF_STG;
   float* sRstd = (float*)(smem + L::OFF_RSTD);
   uint64_t* bars = (uint64_t*)(smem + L::OFF_BAR);
   uint64_t* w_full = bars;                 // [1]
   uint64_t* x_full = bars + 1;             // [NX] TMA landed the x tile
   uint64_t* st_ready = x_full + NX;        // [NX] S1 wrote rstd[] (and patched / saved the stream context)
   uint64_t* y_full = st_ready + NX;        // [NX] S2 wrote y in place
-  uint64_t* y_ready = y_full + NX;         // [NX] E2 turned it into the block output
-  uint64_t* y_empty = y_ready + NX;        // [NX] the TMA store has read it (and S3 is done with it: S3 precedes E2)
-  uint64_t* a_full = y_empty + NX;         // [NA] S3 wrote the a tile
+  uint64_t* x_free = y_full + NX;          // [NX] S3 holds the slot's y rows in registers: the loader may refill it
+  constexpr int NSTG = L::NSTG;
+  uint64_t* out_ready = x_free + NX;       // [NSTG] E2 wrote a staging box
+  uint64_t* out_free = out_ready + NSTG;   // [NSTG] the TMA store has read it
+  uint64_t* a_full = out_free + NSTG;      // [NA] S3 wrote the a tile
   uint64_t* a_empty = a_full + NA;         // [NA] GEMM 1 has read it
   uint64_t* d1_full = a_empty + NA;        // [2]
   uint64_t* d1_empty = d1_full + 2;        // [2]
@@ -180,9 +196,9 @@ block_tma_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
       mbar_init(&x_full[i], 1);
       mbar_init(&st_ready[i], L::S1W);
       mbar_init(&y_full[i], L::S2W);
-      mbar_init(&y_ready[i], L::E2W);
-      mbar_init(&y_empty[i], 1);
+      mbar_init(&x_free[i], L::S3W);
     }
+    for (int i = 0; i < NSTG; ++i) { mbar_init(&out_ready[i], L::E2W); mbar_init(&out_free[i], 1); }
     for (int i = 0; i < NA; ++i) { mbar_init(&a_full[i], L::S3W); mbar_init(&a_empty[i], 1); }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&d1_full[i], 1);
@@ -226,7 +242,8 @@ block_tma_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
           const int s = it % NX;
           int b, t0;
           tile_of(it, b, t0);
-          mbar_wait_sleep(&y_empty[s], (uint32_t)(((it / NX) & 1) ^ 1), 64);
+          mbar_wait_sleep(&x_free[s], (uint32_t)(((it / NX) & 1) ^ 1), 64);
+          VV_BWT(0, it);
           mbar_expect_tx(&x_full[s], L::XY_BYTES);
 #pragma unroll
           for (int c = 0; c < NBOX; ++c)
@@ -237,14 +254,14 @@ block_tma_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
       // ===== GEMM 1 issuer: D1[g & 1] = a * W1_chunk^T ========================================================
       if (elect_one()) {
         constexpr uint32_t idesc1 = umma_idesc_bf16(128, HC);
-        const uint64_t da0 = umma_smem_desc<L::ROWB>(smem_u32(sA));
         const uint64_t dw0 = umma_smem_desc<L::ROWB>(smem_u32(sW1));
         mbar_wait(w_full, 0);
         int g = 0;
         for (int it = 0; it < my_tiles; ++it) {
           const int sa = it % NA;
           mbar_wait_sleep(&a_full[sa], (uint32_t)((it / NA) & 1), 64);
-          const uint64_t da = da0 + (uint64_t)((sa * L::A_BYTES) >> 4);
+          VV_BWT(8, it);
+          const uint32_t aa = tmem_base + L::A_COL0 + (uint32_t)(sa * (C / 2));   // A operand from tensor memory
 #pragma unroll 1
           for (int j = 0; j < NCH; ++j, ++g) {
             const int db = g & 1;
@@ -254,10 +271,11 @@ block_tma_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
             const uint32_t d = tmem_base + (uint32_t)(db * HC);
 #pragma unroll
             for (int kk = 0; kk < C / 16; ++kk)
-              umma_bf16(d, da + (uint64_t)(kk * 2), dw + (uint64_t)(kk * 2), idesc1, kk != 0);
+              umma_bf16_ts(d, aa + (uint32_t)(kk * 8), dw + (uint64_t)(kk * 2), idesc1, kk != 0);
             umma_commit(&d1_full[db]);
           }
           umma_commit(&a_empty[sa]);
+          VV_BWT(9, it);
         }
       }
     } else if (role == 2) {
@@ -287,22 +305,27 @@ block_tma_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
             umma_commit(&h_empty[hb]);
           }
           umma_commit(&d2_full[d2b]);
+          VV_BWT(10, it);
         }
       }
     } else {
-      // ===== TMA store issuer: finished slot -> global, then the slot goes back to the loader =====================
+      // ===== TMA store issuer: finished staging boxes -> global, box by box ===========================================
       if (elect_one()) {
+        int k = 0;
         for (int it = 0; it < my_tiles; ++it) {
-          const int s = it % NX;
           int b, t0;
           tile_of(it, b, t0);
-          mbar_wait_sleep(&y_ready[s], (uint32_t)((it / NX) & 1), 128);
-#pragma unroll
-          for (int c = 0; c < NBOX; ++c)
-            tma_store_3d(&tmO, sXY + s * L::XY_BYTES + c * L::XBOX_BYTES + L::HALO * 128, c * 32, t0, b);
-          tma_store_commit();
-          tma_store_wait_read<0>();
-          mbar_arrive(&y_empty[s]);
+#pragma unroll 1
+          for (int c = 0; c < NBOX; ++c, ++k) {
+            const int o = k % NSTG;
+            mbar_wait_sleep(&out_ready[o], (uint32_t)((k / NSTG) & 1), 64);
+            if (c == 0) VV_BWT(13, it);
+            tma_store_3d(&tmO, sStg + o * L::OBOX_BYTES, c * 32, t0, b);
+            tma_store_commit();
+            tma_store_wait_read<0>();
+            mbar_arrive(&out_free[o]);
+          }
+          VV_BWT(14, it);
         }
         tma_store_wait_all<0>();
       }
@@ -353,31 +376,32 @@ block_tma_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
       if (lane == 0) mbar_arrive(&h_full[grp]);
     }
   } else if (warp < WARP_S1) {
-    // ===== E2: the accumulator already holds out = (y + gb2) + H W2^T: tcgen05.ld -> slot (thread = row) -> TMA store ====
+    // ===== E2: the accumulator already holds out = (y + gb2) + H W2^T: tcgen05.ld -> staging box (thread = row) -> TMA store
     reg_set<L::REG_LAUNCH, L::REG_E2>();
     const int q = warp & 3;
     const int r = q * 32 + lane;
+    int k = 0;
     for (int it = 0; it < my_tiles; ++it) {
-      const int d2b = it % ND2, s = it % NX;
+      const int d2b = it % ND2;
       int b, t0;
       tile_of(it, b, t0);
       const int t = t0 + r;
       const bool valid = t < p.rows_pb;
       const long long brow = (long long)b * p.ob_rpb + p.ob_off + t;
-      // d2_full implies that S3 is done with the slot's y rows (its preload of this accumulator came after it read them,
-      // and GEMM 2 waited for the preload), so the slot can be overwritten with the block output
       mbar_wait(&d2_full[d2b], (uint32_t)((it / ND2) & 1));
+      if (threadIdx.x == WARP_E2 * 32) VV_BWT(11, it);
       tc_fence_after();
-      uint8_t* slot = sXY + s * L::XY_BYTES;
-#pragma unroll
-      for (int c = 0; c < NBOX; ++c) {
+#pragma unroll 1
+      for (int c = 0; c < NBOX; ++c, ++k) {
+        const int o = k % NSTG;
         uint32_t v[32];
         tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + L::D2_COL0 + (uint32_t)(d2b * C + c * 32), v);
+        mbar_wait(&out_free[o], (uint32_t)(((k / NSTG) & 1) ^ 1));        // the store of the box's previous tenant has read it
         tmem_ld_wait();
-        uint8_t* box = slot + c * L::XBOX_BYTES;
+        uint8_t* box = sStg + o * L::OBOX_BYTES;
 #pragma unroll
         for (int i = 0; i < 8; ++i)
-          *reinterpret_cast<uint4*>(box + xy_cell(L::HALO + r, i)) = make_uint4(v[i * 4], v[i * 4 + 1], v[i * 4 + 2], v[i * 4 + 3]);
+          *reinterpret_cast<uint4*>(box + xy_cell(r, i)) = make_uint4(v[i * 4], v[i * 4 + 1], v[i * 4 + 2], v[i * 4 + 3]);
         if (valid && p.out_bf16 != nullptr) {
           __nv_bfloat16* bp = p.out_bf16 + brow * C + c * 32;
 #pragma unroll
@@ -390,14 +414,15 @@ block_tma_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
             *reinterpret_cast<uint4*>(bp + i * 8) = pk;
           }
         }
+        if (c == NBOX - 1) tc_fence_before();
+        fence_proxy_async_smem();               // staged box -> visible to the TMA store
+        __syncwarp();
+        if (lane == 0) {
+          if (c == NBOX - 1) mbar_arrive(&d2_empty[d2b]);
+          mbar_arrive(&out_ready[o]);
+        }
       }
-      tc_fence_before();
-      fence_proxy_async_smem();                 // staged tile -> visible to the TMA store
-      __syncwarp();
-      if (lane == 0) {
-        mbar_arrive(&d2_empty[d2b]);
-        mbar_arrive(&y_ready[s]);
-      }
+      if (threadIdx.x == WARP_E2 * 32) VV_BWT(12, it);
     }
   } else if (warp < WARP_S3) {
     // ===== S1: thread = row: rstd of the raw row (first RMSNorm), stream context in / out ===========================
@@ -405,19 +430,22 @@ block_tma_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
     const int r = (warp - WARP_S1) * 32 + lane;           // tile row 0..127 -> slot row HALO + r
     const float inv_c = 1.0f / (float)C;
     auto row_rstd = [&](const uint8_t* slot, int srow) -> float {
-      f32x2 acc = 0ull;
+      f32x2 acc[4] = {0ull, 0ull, 0ull, 0ull};            // four independent chains
 #pragma unroll
       for (int c = 0; c < NBOX; ++c) {
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
           const ulonglong2 v = *reinterpret_cast<const ulonglong2*>(slot + c * L::XBOX_BYTES + xy_cell(srow, i));
-          acc = f2_fma(v.x, v.x, acc);
-          acc = f2_fma(v.y, v.y, acc);
+          acc[(i & 1) * 2] = f2_fma(v.x, v.x, acc[(i & 1) * 2]);
+          acc[(i & 1) * 2 + 1] = f2_fma(v.y, v.y, acc[(i & 1) * 2 + 1]);
         }
       }
-      float s0, s1;
-      f2_unpack(acc, s0, s1);
-      return rstd_of(s0 + s1, inv_c, p.eps);
+      float s0, s1, s2, s3, s4, s5, s6, s7;
+      f2_unpack(acc[0], s0, s1);
+      f2_unpack(acc[1], s2, s3);
+      f2_unpack(acc[2], s4, s5);
+      f2_unpack(acc[3], s6, s7);
+      return rstd_of(((s0 + s1) + (s2 + s3)) + ((s4 + s5) + (s6 + s7)), inv_c, p.eps);
     };
     for (int it = 0; it < my_tiles; ++it) {
       const int s = it % NX;
@@ -431,6 +459,7 @@ block_tma_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
       uint8_t* wr8 = nullptr;
       if (STATE && p.st.base != nullptr && (t0 == 0 || t0 + 128 > p.rows_pb - 6)) p.st.resolve(b, rd8, wr8);
       mbar_wait(&x_full[s], (uint32_t)((it / NX) & 1));
+      if (threadIdx.x == WARP_S1 * 32) VV_BWT(1, it);
       if (warp == WARP_S1 && lane < L::HALO) {
         // halo rows (slot rows 0..7 = t0 - 8 .. t0 - 1): at the item start rows 2..7 are the stream's cached raw rows
         // (TMA delivered zeros = the offline causal pad, :398-403)
@@ -475,50 +504,56 @@ block_tma_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
       }
       __syncwarp();
       if (lane == 0) mbar_arrive(&st_ready[s]);
+      if (threadIdx.x == WARP_S1 * 32) VV_BWT(2, it);
     }
   } else if (warp < WARP_S2) {
-    // ===== S3: thread = row: second RMSNorm statistic, a = bf16(y * rstd2) -> swizzled GEMM-1 operand tile ============
+    // ===== S3: thread = row: second RMSNorm statistic, a = bf16(y * rstd2) -> tensor memory, D2 preload ==================
     reg_set<L::REG_LAUNCH, L::REG_S3>();
     const int r = (warp - WARP_S3) * 32 + lane;
     const float inv_c = 1.0f / (float)C;
     for (int it = 0; it < my_tiles; ++it) {
       const int s = it % NX, sa = it % NA;
       const uint8_t* slot = sXY + s * L::XY_BYTES;
-      uint8_t* arow = sA + sa * L::A_BYTES + r * L::ROWB;
       mbar_wait(&y_full[s], (uint32_t)((it / NX) & 1));
+      if (threadIdx.x == WARP_S3 * 32) VV_BWT(5, it);
       ulonglong2 y[C / 4];
-      f32x2 acc = 0ull;
+      f32x2 acc[4] = {0ull, 0ull, 0ull, 0ull};
 #pragma unroll
       for (int c = 0; c < NBOX; ++c)
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
           y[c * 8 + i] = *reinterpret_cast<const ulonglong2*>(slot + c * L::XBOX_BYTES + xy_cell(L::HALO + r, i));
-          acc = f2_fma(y[c * 8 + i].x, y[c * 8 + i].x, acc);
-          acc = f2_fma(y[c * 8 + i].y, y[c * 8 + i].y, acc);
+          acc[(i & 1) * 2] = f2_fma(y[c * 8 + i].x, y[c * 8 + i].x, acc[(i & 1) * 2]);
+          acc[(i & 1) * 2 + 1] = f2_fma(y[c * 8 + i].y, y[c * 8 + i].y, acc[(i & 1) * 2 + 1]);
         }
-      float s0, s1;
-      f2_unpack(acc, s0, s1);
-      const float rstd2 = rstd_of(s0 + s1, inv_c, p.eps);
+      float s0, s1, s2, s3, s4, s5, s6, s7;
+      f2_unpack(acc[0], s0, s1);
+      f2_unpack(acc[1], s2, s3);
+      f2_unpack(acc[2], s4, s5);
+      f2_unpack(acc[3], s6, s7);
+      const float rstd2 = rstd_of(((s0 + s1) + (s2 + s3)) + ((s4 + s5) + (s6 + s7)), inv_c, p.eps);
       const f32x2 rr = f2_pack(rstd2, rstd2);
+      // a = bf16(y * rstd2) -> tensor memory (thread = row = TMEM lane; pair (k, k+1) -> one 32-bit column): GEMM 1 takes its
+      // A operand from there, so the operand tile costs no shared memory, no swizzled stores and no proxy fence
       mbar_wait(&a_empty[sa], (uint32_t)(((it / NA) & 1) ^ 1));
+      tc_fence_after();
+      const uint32_t aaddr = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + L::A_COL0 + (uint32_t)(sa * (C / 2));
 #pragma unroll
-      for (int k = 0; k < C / 8; ++k) {                  // 16-byte chunk k of the row = channels [8k, 8k + 8)
-        float a0, a1, a2, a3, a4, a5, a6, a7;
-        f2_unpack(f2_mul(y[2 * k].x, rr), a0, a1);
-        f2_unpack(f2_mul(y[2 * k].y, rr), a2, a3);
-        f2_unpack(f2_mul(y[2 * k + 1].x, rr), a4, a5);
-        f2_unpack(f2_mul(y[2 * k + 1].y, rr), a6, a7);
-        uint4 pk;
-        pk.x = pack_bf16x2(a0, a1);
-        pk.y = pack_bf16x2(a2, a3);
-        pk.z = pack_bf16x2(a4, a5);
-        pk.w = pack_bf16x2(a6, a7);
-        const int sw = (L::ROWB == 128) ? (k ^ (r & 7)) : (k ^ ((r >> 1) & 3));
-        *reinterpret_cast<uint4*>(arow + (sw << 4)) = pk;
+      for (int hcol = 0; hcol < C / 32; ++hcol) {        // 16 packed columns = 32 channels = 8 cells per tcgen05.st
+        uint32_t w[16];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          float a0, a1, a2, a3;
+          f2_unpack(f2_mul(y[hcol * 8 + i].x, rr), a0, a1);
+          f2_unpack(f2_mul(y[hcol * 8 + i].y, rr), a2, a3);
+          w[i * 2 + 0] = pack_bf16x2(a0, a1);
+          w[i * 2 + 1] = pack_bf16x2(a2, a3);
+        }
+        tmem_st_32x16(aaddr + (uint32_t)(hcol * 16), w);
       }
-      fence_proxy_async_smem();                 // a tile (generic-proxy stores) -> visible to tcgen05.mma
       __syncwarp();
-      if (lane == 0) mbar_arrive(&a_full[sa]);
+      if (lane == 0) mbar_arrive(&x_free[s]);   // this warp's y rows are in registers: nothing reads the slot after S3
+      if (threadIdx.x == WARP_S3 * 32) VV_BWT(6, it);
       // D2[it % ND2] = y + gb2 (thread = row = TMEM lane; this warp's lane quarter is warp % 4): GEMM 2 accumulates on it
       const int d2b = it % ND2;
       mbar_wait(&d2_empty[d2b], (uint32_t)(((it / ND2) & 1) ^ 1));
@@ -543,7 +578,11 @@ block_tma_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
       tmem_st_wait();
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&d2_init[d2b]);
+      if (lane == 0) {
+        mbar_arrive(&a_full[sa]);
+        mbar_arrive(&d2_init[d2b]);
+      }
+      if (threadIdx.x == WARP_S3 * 32) VV_BWT(7, it);
     }
   } else {
     // ===== S2: depthwise causal conv k7 over the normalised rows; lane = 4 channels, strip = R consecutive rows =======
@@ -573,41 +612,50 @@ block_tma_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
       uint8_t* bx = sXY + s * L::XY_BYTES + box * L::XBOX_BYTES;
       const float* rs = sRstd + s * L::RSTD_STRIDE + sr0 - 4;      // rs[i] = rstd of slot row sr0 - 6 + i  (16 B aligned)
       mbar_wait(&st_ready[s], (uint32_t)((it / NX) & 1));
-      float rv[R + 8];
-#pragma unroll
-      for (int i = 0; i < (R + 8) / 4; ++i) {
-        const float4 t4 = *reinterpret_cast<const float4*>(rs + i * 4);
-        rv[i * 4] = t4.x; rv[i * 4 + 1] = t4.y; rv[i * 4 + 2] = t4.z; rv[i * 4 + 3] = t4.w;
-      }
+      if (threadIdx.x == WARP_S2 * 32) VV_BWT(3, it);
       P4 win[7];
 #pragma unroll
       for (int i = 0; i < 6; ++i) {                                  // warm-up rows: a load and a multiply each
         const ulonglong2 v = *reinterpret_cast<const ulonglong2*>(bx + xy_cell(sr0 - 6 + i, qc));
-        const f32x2 rr = f2_pack(rv[i], rv[i]);
+        const float rsi = rs[i];
+        const f32x2 rr = f2_pack(rsi, rsi);
         win[i].lo = f2_mul(v.x, rr);
         win[i].hi = f2_mul(v.y, rr);
       }
       // y is written in place: every strip must hold its warm-up rows (its neighbour's last rows) before anyone stores
       named_bar_sync(1, L::S2W * 32);
+      // rows are LOADED NB at a time: a load may not be moved above the previous row's in-place store (same buffer), so a
+      // row-by-row loop serialises load -> math -> store per row (clock64 timeline of block_ws_kernel: 4 500 clocks per tile)
+      constexpr int NB = 8;
 #pragma unroll
-      for (int k = 0; k < R; ++k) {
-        ulonglong2* cell = reinterpret_cast<ulonglong2*>(bx + xy_cell(sr0 + k, qc));
-        const ulonglong2 v = *cell;
-        const f32x2 rr = f2_pack(rv[6 + k], rv[6 + k]);
-        win[(6 + k) % 7].lo = f2_mul(v.x, rr);
-        win[(6 + k) % 7].hi = f2_mul(v.y, rr);
-        P4 acc;
-        acc.lo = f2_add(v.x, gb.lo);
-        acc.hi = f2_add(v.y, gb.hi);
+      for (int k0 = 0; k0 < R; k0 += NB) {
+        ulonglong2 xv[NB];
+        float rv[NB];
 #pragma unroll
-        for (int j = 0; j < 7; ++j) {                                // tap j reads n[t - 6 + j] = win[(k + j) % 7]
-          acc.lo = f2_fma(wq[j].lo, win[(k + j) % 7].lo, acc.lo);
-          acc.hi = f2_fma(wq[j].hi, win[(k + j) % 7].hi, acc.hi);
+        for (int k = 0; k < NB; ++k) {
+          xv[k] = *reinterpret_cast<const ulonglong2*>(bx + xy_cell(sr0 + k0 + k, qc));
+          rv[k] = rs[6 + k0 + k];
         }
-        *cell = make_ulonglong2(acc.lo, acc.hi);
+#pragma unroll
+        for (int k = 0; k < NB; ++k) {
+          const int kk = k0 + k;
+          const f32x2 rr = f2_pack(rv[k], rv[k]);
+          win[(6 + kk) % 7].lo = f2_mul(xv[k].x, rr);
+          win[(6 + kk) % 7].hi = f2_mul(xv[k].y, rr);
+          P4 acc;
+          acc.lo = f2_add(xv[k].x, gb.lo);
+          acc.hi = f2_add(xv[k].y, gb.hi);
+#pragma unroll
+          for (int j = 0; j < 7; ++j) {                              // tap j reads n[t - 6 + j] = win[(kk + j) % 7]
+            acc.lo = f2_fma(wq[j].lo, win[(kk + j) % 7].lo, acc.lo);
+            acc.hi = f2_fma(wq[j].hi, win[(kk + j) % 7].hi, acc.hi);
+          }
+          *reinterpret_cast<ulonglong2*>(bx + xy_cell(sr0 + kk, qc)) = make_ulonglong2(acc.lo, acc.hi);
+        }
       }
       __syncwarp();
       if (lane == 0) mbar_arrive(&y_full[s]);
+      if (threadIdx.x == WARP_S2 * 32) VV_BWT(4, it);
     }
   }
   tc_fence_before();

@@ -56,16 +56,6 @@ struct BlockWsArgs {
 #define VV_BW_NW2 2
 #endif
 
-#ifdef VV_BW_TRACE     // timeline instrumentation (A/B builds only): clock64 stamps of CTA 0 for its tiles [8, 24)
-__device__ long long vv_bw_trace[16 * 32];
-#define VV_BWT(slot, it)                                                                                 \
-  do {                                                                                                   \
-    if (blockIdx.x == 0 && (it) >= 8 && (it) < 24) vv_bw_trace[((it) - 8) * 32 + (slot)] = clock64();    \
-  } while (0)
-#else
-#define VV_BWT(slot, it) do { } while (0)
-#endif
-
 struct BlockWsCfg {
   static constexpr int C = 128;
   static constexpr int HC = 64;                      // hidden units per chunk
