@@ -26,6 +26,8 @@ names = ["load", "R:x_full", "R:st_rdy", "S2:start", "S2:y_full", "R:y_seen", "R
          "G2:commit", "E2:d2full", "E2:done", "XY:y_rdy", "XY:st_read"]
 t0 = min(v for v in buf if v > 0)
 e1 = ["c0:wait", "c0:d1full", "c0:ld0", "c0:st0", "c0:ld1", "c0:st1", "c0:hfull", "", "c2:wait", "c2:d1full"]
+if stage != 4:
+    e1 = ["wait", "d1full", "gelu0 done", "h_empty", "", "", "hfull"]
 for ti in range(16):
     row = [buf[ti * 32 + s] - t0 if buf[ti * 32 + s] else -1 for s in range(15)]
     print(f"it={8 + ti:3d} " + " ".join(f"{n}={v:6d}" for n, v in zip(names, row)))

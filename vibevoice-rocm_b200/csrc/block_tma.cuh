@@ -48,6 +48,14 @@ namespace vv {
                             // phase only to receive the output at its end); the output goes through a separate ring of staging
                             // boxes.  History: 3 slots held to the store 1.371 ms, 4 slots 1.240 ms per 5760 frames
 #endif
+#ifndef VV_BT_NGRP
+#define VV_BT_NGRP 2        // E1 groups (4 warps each; group G owns D1 buffer G and H buffer G, chunks go round-robin).  The clock64
+                            // timelines show the chunk chain G1 -> E1 -> G2 as the pace-setter of all fused kernels at ~1 000
+                            // clocks per chunk (one group needs ~1 600 per chunk).  A THIRD group fits the tensor memory at C <= 64
+                            // and was measured (profiles/block_tma_e1groups_ab_r02.txt): each E1 warp then takes ~2 900 clocks per
+                            // chunk instead of 1 600 -- the sub-partition's FMA / MUFU / issue mix is what saturates, at ~60 % of
+                            // the pure-GELU rate -- and the kernel is no faster (1.200 / 1.197 ms against 1.213 / 1.178), so 2 stays
+#endif
 #ifndef VV_BT_NSTG
 #define VV_BT_NSTG 2        // output staging boxes of [128 rows, 32 fp32] (16 KB each) at C = 64; 4 at C = 32
 #endif
@@ -95,7 +103,12 @@ struct BlockTmaCfg {
   static constexpr int XY_BYTES = NBOX * XBOX_BYTES;
   static constexpr int NX = (C == 64) ? VV_BT_NX64 : VV_BT_NX32;
   static constexpr int NA = 2;                        // GEMM-1 operand buffers, in TENSOR memory (C / 2 packed columns each)
-  static constexpr int E1W = 8, E2W = 4, S1W = 4, S3W = 4, S2W = 4, CTRL = 4;
+  static constexpr int NG = VV_BT_NGRP;              // E1 groups
+#ifndef VV_BT_EC
+#define VV_BT_EC 32
+#endif
+  static constexpr int EC = VV_BT_EC;                // accumulator columns an E1 warp holds at a time (32, or 16 to save registers)
+  static constexpr int E1W = 4 * NG, E2W = 4, S1W = 4, S3W = 4, S2W = 4, CTRL = 4;
   static constexpr int STRIPS = S2W * 32 / LPR;      // 8 (C = 64) or 16 (C = 32)
   static constexpr int R = 128 / STRIPS;             // rows per strip: 16 or 8
   static constexpr int WARPS = E1W + E2W + S1W + S3W + S2W + CTRL;
@@ -111,20 +124,23 @@ struct BlockTmaCfg {
   static constexpr int OFF_STG = OFF_XY + NX * XY_BYTES;
   static constexpr int OFF_RSTD = OFF_STG + NSTG * OBOX_BYTES;
   static constexpr int OFF_BAR = OFF_RSTD + NX * RSTD_STRIDE * 4;
-  static constexpr int ND2 = (3 * HC + 4 * C <= 512) ? 4 : 2;      // D2 accumulators (S3 preloads one while E2 drains another)
-  static constexpr int NBARS = 1 + 4 * NX + 2 * NSTG + 2 * NA + 8 + 3 * ND2;
+  static constexpr int D2_FIT = (512 - NG * HC - NG * HC / 2 - NA * (C / 2)) / C;
+  static constexpr int ND2 = D2_FIT > 4 ? 4 : D2_FIT;              // D2 accumulators (S3 preloads one while E2 drains another)
+  static_assert(ND2 >= 2, "tensor memory: two D2 accumulators");
+  static constexpr int NBARS = 1 + 4 * NX + 2 * NSTG + 2 * NA + 4 * NG + 3 * ND2;
   static_assert(OFF_STG % 1024 == 0, "swizzled staging boxes need 1 KB aligned bases");
   static constexpr int TOTAL = OFF_BAR + 512 + 1024;
   static_assert(NBARS * 8 + 8 <= 512, "barrier block");
   static_assert(OFF_XY % 1024 == 0 && XBOX_BYTES % 1024 == 0, "swizzled boxes need 1 KB aligned bases");
   static_assert(TOTAL <= 232448, "exceeds the 227 KB dynamic shared memory limit");
-  static constexpr uint32_t TMEM_COLS = 512;         // D1: 2 x HC at 0; H: 2 x HC/2 at 2 HC; D2: ND2 x C at 3 HC; a: NA x C/2
-  static constexpr uint32_t H_COL0 = 2 * HC, D2_COL0 = 3 * HC, A_COL0 = 3 * HC + ND2 * C;
+  static constexpr uint32_t TMEM_COLS = 512;         // D1: NG x HC at 0; H: NG x HC/2; D2: ND2 x C; a: NA x C/2
+  static constexpr uint32_t H_COL0 = NG * HC, D2_COL0 = NG * HC + NG * HC / 2, A_COL0 = D2_COL0 + ND2 * C;
   static_assert(A_COL0 + NA * (C / 2) <= 512, "tensor memory columns (HC = 128 leaves no room for the operand: use HC = 64)");
-  static_assert(3 * HC + ND2 * C <= 512, "tensor memory columns");
   // register budgets (setmaxnreg draws from the CTA's launch allocation: threads x launch registers)
   static constexpr int REG_LAUNCH = (65536 / THREADS) / 8 * 8;
-  static constexpr int REG_E1 = 64, REG_E2 = 72, REG_S1 = 48, REG_S3 = (C == 64) ? 104 : 64, REG_S2 = 112, REG_CTRL = 32;
+  static constexpr int REG_E1 = (EC == 16) ? 48 : (NG >= 3 ? 56 : 64), REG_E2 = (NG >= 3) ? 64 : 72, REG_S1 = 48, REG_S3 = (C == 64) ? 104 : 64,
+                       REG_S2 = (NG >= 3) ? 96 : 112, REG_CTRL = 32;
+  static_assert(WARPS % 4 == 0, "registers are allocated per SM sub-partition: every one must hold the same warp mix");
   static_assert(32 * (E1W * REG_E1 + E2W * REG_E2 + S1W * REG_S1 + S3W * REG_S3 + S2W * REG_S2 + CTRL * REG_CTRL) <=
                     THREADS * REG_LAUNCH, "setmaxnreg budget exceeds the CTA's launch allocation");
 };
@@ -162,12 +178,13 @@ block_tma_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
   uint64_t* out_free = out_ready + NSTG;   // [NSTG] the TMA store has read it
   uint64_t* a_full = out_free + NSTG;      // [NA] S3 wrote the a tile
   uint64_t* a_empty = a_full + NA;         // [NA] GEMM 1 has read it
-  uint64_t* d1_full = a_empty + NA;        // [2]
-  uint64_t* d1_empty = d1_full + 2;        // [2]
-  uint64_t* h_full = d1_empty + 2;         // [2]
-  uint64_t* h_empty = h_full + 2;          // [2]
+  constexpr int NG = L::NG;
+  uint64_t* d1_full = a_empty + NA;        // [NG]
+  uint64_t* d1_empty = d1_full + NG;       // [NG]
+  uint64_t* h_full = d1_empty + NG;        // [NG]
+  uint64_t* h_empty = h_full + NG;         // [NG]
   constexpr int ND2 = L::ND2;
-  uint64_t* d2_full = h_empty + 2;         // [ND2] GEMM 2 finished the tile's accumulator
+  uint64_t* d2_full = h_empty + NG;        // [ND2] GEMM 2 finished the tile's accumulator
   uint64_t* d2_empty = d2_full + ND2;      // [ND2] E2 has read it
   uint64_t* d2_init = d2_empty + ND2;      // [ND2] S3 preloaded it with y + gb2
   uint32_t* tmem_slot = (uint32_t*)(d2_init + ND2);
@@ -200,10 +217,10 @@ block_tma_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
     }
     for (int i = 0; i < NSTG; ++i) { mbar_init(&out_ready[i], L::E2W); mbar_init(&out_free[i], 1); }
     for (int i = 0; i < NA; ++i) { mbar_init(&a_full[i], L::S3W); mbar_init(&a_empty[i], 1); }
-    for (int i = 0; i < 2; ++i) {
+    for (int i = 0; i < NG; ++i) {
       mbar_init(&d1_full[i], 1);
-      mbar_init(&d1_empty[i], L::E1W / 2);
-      mbar_init(&h_full[i], L::E1W / 2);
+      mbar_init(&d1_empty[i], 4);
+      mbar_init(&h_full[i], 4);
       mbar_init(&h_empty[i], 1);
     }
     for (int i = 0; i < ND2; ++i) {
@@ -264,8 +281,8 @@ block_tma_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
           const uint32_t aa = tmem_base + L::A_COL0 + (uint32_t)(sa * (C / 2));   // A operand from tensor memory
 #pragma unroll 1
           for (int j = 0; j < NCH; ++j, ++g) {
-            const int db = g & 1;
-            mbar_wait(&d1_empty[db], (uint32_t)(((g >> 1) & 1) ^ 1));
+            const int db = g % NG;
+            mbar_wait(&d1_empty[db], (uint32_t)(((g / NG) & 1) ^ 1));
             tc_fence_after();
             const uint64_t dw = dw0 + (uint64_t)((j * HC * L::ROWB) >> 4);
             const uint32_t d = tmem_base + (uint32_t)(db * HC);
@@ -292,8 +309,8 @@ block_tma_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
           const uint32_t d = tmem_base + L::D2_COL0 + (uint32_t)(d2b * C);
 #pragma unroll 1
           for (int j = 0; j < NCH; ++j, ++g) {
-            const int hb = g & 1;
-            mbar_wait(&h_full[hb], (uint32_t)((g >> 1) & 1));
+            const int hb = g % NG;
+            mbar_wait(&h_full[hb], (uint32_t)((g / NG) & 1));
             tc_fence_after();
             const uint32_t ah = tmem_base + L::H_COL0 + (uint32_t)(hb * (HC / 2));
 #pragma unroll
@@ -332,48 +349,58 @@ block_tma_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
     }
   } else if (warp < WARP_E2) {
     // ===== E1: D1 -> + b1 -> GELU -> bf16 pairs -> H in tensor memory ===========================================
-    // Two groups of 4 warps alternate chunks (group G owns D1 buffer G and H buffer G); a warp owns 32 rows.
+    // NG groups of 4 warps take chunks round-robin (group G owns D1 buffer G and H buffer G); a warp owns 32 rows and walks
+    // the chunk's 64 columns EC at a time.
     reg_set<L::REG_LAUNCH, L::REG_E1>();
+    constexpr int EC = L::EC;
     const int q = warp & 3;
     const int grp = warp >> 2;
     const uint32_t lane_base = (uint32_t)(q * 32) << 16;
     const uint32_t d1addr = tmem_base + lane_base + (uint32_t)(grp * HC);
     const uint32_t haddr = tmem_base + lane_base + L::H_COL0 + (uint32_t)(grp * (HC / 2));
-    for (int g = grp; g < total_g; g += 2) {
+    for (int g = grp; g < total_g; g += NG) {
       const int j = g % NCH;
-      const uint32_t ph = (uint32_t)((g >> 1) & 1);
+      const uint32_t ph = (uint32_t)((g / NG) & 1);
       const float* bp = p.b1c + j * HC;                  // constant bank (by-value kernel argument)
+      if (threadIdx.x == 0) VV_BWT(16, g / NCH);          // (the last chunk of the tile that group 0 handles wins)
       mbar_wait(&d1_full[grp], ph);
+      if (threadIdx.x == 0) VV_BWT(17, g / NCH);
       tc_fence_after();
 #pragma unroll
-      for (int hf = 0; hf < HC / 32; ++hf) {
-        uint32_t v[32];
-        tmem_ld_32x32(d1addr + (uint32_t)(hf * 32), v);
+      for (int hf = 0; hf < HC / EC; ++hf) {
+        uint32_t v[EC];
+        if constexpr (EC == 32) tmem_ld_32x32(d1addr + (uint32_t)(hf * EC), v);
+        else tmem_ld_32x16(d1addr + (uint32_t)(hf * EC), v);
         tmem_ld_wait();
-        if (hf == HC / 32 - 1) {                     // whole accumulator is in registers: the next G1 may overwrite it
+        if (hf == HC / EC - 1) {                     // whole accumulator is in registers: the next G1 may overwrite it
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(&d1_empty[grp]);
         }
-        uint32_t hv[16];
+        uint32_t hv[EC / 2];
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          const float* bq = bp + hf * 32 + i * 8;
+        for (int i = 0; i < EC / 8; ++i) {
+          const float* bq = bp + hf * EC + i * 8;
           hv[i * 4 + 0] = gelu2_bias_pack(__uint_as_float(v[i * 8 + 0]), __uint_as_float(v[i * 8 + 1]), bq[0], bq[1]);
           hv[i * 4 + 1] = gelu2_bias_pack(__uint_as_float(v[i * 8 + 2]), __uint_as_float(v[i * 8 + 3]), bq[2], bq[3]);
           hv[i * 4 + 2] = gelu2_bias_pack(__uint_as_float(v[i * 8 + 4]), __uint_as_float(v[i * 8 + 5]), bq[4], bq[5]);
           hv[i * 4 + 3] = gelu2_bias_pack(__uint_as_float(v[i * 8 + 6]), __uint_as_float(v[i * 8 + 7]), bq[6], bq[7]);
         }
         if (hf == 0) {
+          if (threadIdx.x == 0) VV_BWT(18, g / NCH);
           mbar_wait(&h_empty[grp], ph ^ 1);          // GEMM 2 has consumed this group's previous H chunk
+          if (threadIdx.x == 0) VV_BWT(19, g / NCH);
           tc_fence_after();
         }
-        tmem_st_32x16(haddr + (uint32_t)(hf * 16), hv);   // thread = row: pair (k, k+1) -> one 32-bit column
+        // thread = row: pair (k, k+1) -> one 32-bit column
+        if constexpr (EC == 32) tmem_st_32x16(haddr + (uint32_t)(hf * (EC / 2)), hv);
+        else tmem_st_32x8(haddr + (uint32_t)(hf * (EC / 2)), hv);
       }
       tmem_st_wait();
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&h_full[grp]);
+      if (threadIdx.x == 0) VV_BWT(22, g / NCH);
     }
   } else if (warp < WARP_S1) {
     // ===== E2: the accumulator already holds out = (y + gb2) + H W2^T: tcgen05.ld -> staging box (thread = row) -> TMA store
@@ -551,8 +578,13 @@ block_tma_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
         }
         tmem_st_32x16(aaddr + (uint32_t)(hcol * 16), w);
       }
+      tmem_st_wait();                           // GEMM 1 must not wait for the D2 preload below (which may have to wait for E2)
+      tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&x_free[s]);   // this warp's y rows are in registers: nothing reads the slot after S3
+      if (lane == 0) {
+        mbar_arrive(&a_full[sa]);
+        mbar_arrive(&x_free[s]);                // this warp's y rows are in registers: nothing reads the slot after S3
+      }
       if (threadIdx.x == WARP_S3 * 32) VV_BWT(6, it);
       // D2[it % ND2] = y + gb2 (thread = row = TMEM lane; this warp's lane quarter is warp % 4): GEMM 2 accumulates on it
       const int d2b = it % ND2;
@@ -578,10 +610,7 @@ block_tma_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
       tmem_st_wait();
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) {
-        mbar_arrive(&a_full[sa]);
-        mbar_arrive(&d2_init[d2b]);
-      }
+      if (lane == 0) mbar_arrive(&d2_init[d2b]);
       if (threadIdx.x == WARP_S3 * 32) VV_BWT(7, it);
     }
   } else {
@@ -626,7 +655,7 @@ block_tma_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
       named_bar_sync(1, L::S2W * 32);
       // rows are LOADED NB at a time: a load may not be moved above the previous row's in-place store (same buffer), so a
       // row-by-row loop serialises load -> math -> store per row (clock64 timeline of block_ws_kernel: 4 500 clocks per tile)
-      constexpr int NB = 8;
+      constexpr int NB = (L::NG >= 3) ? 4 : 8;
 #pragma unroll
       for (int k0 = 0; k0 < R; k0 += NB) {
         ulonglong2 xv[NB];

@@ -272,6 +272,14 @@ __device__ __forceinline__ void tmem_st_32x16(uint32_t taddr, const uint32_t (&v
       : "memory");
 }
 
+__device__ __forceinline__ void tmem_st_32x8(uint32_t taddr, const uint32_t (&v)[8]) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};"
+      :
+      : "r"(taddr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7])
+      : "memory");
+}
+
 // ---- descriptors ------------------------------------------------------------------------------
 // K-major operand tile in shared memory, rows of ROW_BYTES (= the swizzle span: 128 or 64 bytes),
 // 8-row swizzle atoms stacked every 8*ROW_BYTES.  Bit layout: start>>4 [0,14), LBO>>4 [16,30),
