@@ -110,8 +110,10 @@ int64_t vv_decoder_param_count(const vv_decoder* dec);
  *   "block_kernel"     1 (default) = block_tma_kernel for whole Block1Ds at C <= 64, 0 = block_fused_kernel
  *   "block_ws"         1 (default) = block_ws_kernel (whole Block1D in one kernel) at C = 128, 0 = mixer_kernel +
  *                      ffn_stream_kernel
+ *   "ffn_stream256"    1 (default) = FFN half at C = 256 in one kernel with the hidden activation on chip
+ *                      (ffn_stream_kernel<256>), 0 = two GEMMs with the hidden tensor through HBM
  * Unknown keys / values out of range: VV_ERR_INVALID_ARG.  The environment variables VV_GEMM_BN256,
- * VV_GEMM_BN256_WAVES, VV_GEMM_BN64, VV_BLOCK_KERNEL, VV_BLOCK_WS set the defaults a decoder is created with.
+ * VV_GEMM_BN256_WAVES, VV_GEMM_BN64, VV_BLOCK_KERNEL, VV_BLOCK_WS, VV_FFN_STREAM256 set the defaults a decoder is created with.
  */
 int32_t vv_decoder_set_option(vv_decoder* dec, const char* key, int64_t value);
 /* samples produced per latent frame (prod(ratios) = 3200) and causal receptive field in frames (58) */

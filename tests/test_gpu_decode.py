@@ -198,6 +198,31 @@ def test_block_ws_on_and_off_stream_equal_offline(full_decoder):
     assert m["snr_db"] > 48.0 and m["rel_max"] < 1e-2, m
 
 
+def test_ffn_stream256_on_and_off_stream_equal_offline(full_decoder):
+    """Stage 3's FFN half as ffn_stream_kernel<256> (default) and as two GEMMs: each setting reproduces its own offline
+    decode bit for bit when streamed, and the two agree to well inside the path's tolerance (same bf16 operands; only the
+    order of the fp32 operations around the hidden activation differs)."""
+    dec, _ = full_decoder
+    lat = torch.from_numpy(make_latents(2, 8, 64, 59)).cuda()
+    outs = {}
+    try:
+        for k in (0, 1):
+            dec.set_option("ffn_stream256", k)
+            off = dec.decode(lat)
+            cache = dec.new_cache(3)
+            idx = torch.tensor([2, 0], device="cuda")
+            parts, t = [], 0
+            for n in (1, 3, 4):
+                parts.append(dec.decode(lat[:, t:t + n], cache=cache, sample_indices=idx, use_cache=True))
+                t += n
+            assert torch.equal(torch.cat(parts, -1), off), k
+            outs[k] = off
+    finally:
+        dec.set_option("ffn_stream256", 1)
+    m = parity_metrics(outs[1].cpu().numpy(), outs[0].cpu().numpy())
+    assert m["snr_db"] > 55.0 and m["rel_max"] < 5e-3, m
+
+
 def test_state_zero_export_import(full_decoder):
     dec, _ = full_decoder
     lat = torch.from_numpy(make_latents(1, 4, 64, 43)).cuda()

@@ -238,6 +238,23 @@ def _ffn_case(dec, w, stage, B, rows, seed, sample=None):
     return O.parity_metrics(o[idx], ref)
 
 
+@pytest.mark.parametrize("mode", [1, 0])
+@pytest.mark.parametrize("B,rows", [(1, 1), (1, 127), (1, 128), (2, 129), (3, 257), (1, 160 * 128 + 5), (1, 51200)])
+def test_ffn_half_c256_hidden_on_chip(full_decoder, B, rows, mode):
+    """FFN half at C = 256 (stage 3): ffn_stream_kernel<256> (option ffn_stream256 = 1, the default: hidden activation on
+    chip, W1 / W2 streamed in 32 KB chunks, one 256-column D2 accumulator, a tile single-buffered behind its own loader
+    thread) and the two-GEMM form (0), both against the oracle.  Shapes: single row, tile edges, more tiles than SMs (the
+    single a slot / D2 accumulator are reused many times per CTA), a K4 frame step's row count (256 streams x 200)."""
+    dec, w = full_decoder
+    sample = None if B * rows <= 4096 else np.unique(_rng(rows).integers(0, B * rows, 1024))
+    try:
+        dec.set_option("ffn_stream256", mode)
+        m = _ffn_case(dec, w, 3, B, rows, 29000 + rows + B, sample=sample)
+    finally:
+        dec.set_option("ffn_stream256", 1)
+    assert m["snr_db"] > 50 and m["rel_max"] < 5e-3, m
+
+
 @pytest.mark.parametrize("stage,B,rows", [(0, 1, 7), (0, 2, 150), (1, 1, 20), (1, 3, 100), (2, 1, 70), (2, 1, 300),
                                           (3, 1, 130), (3, 2, 257), (3, 1, 1)])
 def test_ffn_half_wide_tile_forced(full_decoder, stage, B, rows):

@@ -40,9 +40,9 @@ struct FfnFusedArgs {
   // ffn_stream_kernel (C = 128) reads the three per-channel vectors from the CONSTANT bank (by-value argument) instead of
   // warp-uniform __ldg loads: ncu of block_tma_kernel showed such loads costing ~4 LSU data-pipe wavefronts each, a third
   // of that kernel's LSU traffic (profiles/block_tma_s6_r02.txt).  Filled by the host when C == 128.
-  float b1c[512];          // = b1 (pre-scaled by 0.5)
-  float b2c[128];
-  float gammac[128];
+  float b1c[1024];         // = b1 (pre-scaled by 0.5); sized for C = 256
+  float b2c[256];
+  float gammac[256];
 };
 
 template <int C>

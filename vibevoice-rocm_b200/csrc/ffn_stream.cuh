@@ -1,5 +1,8 @@
-// ffn_stream.cuh — kernel class (b) for the middle stage (C = 128): the whole Block1D FFN half in ONE persistent
-// tcgen05 kernel with the hidden activation kept on chip and the weights STREAMED through shared memory.
+// ffn_stream.cuh — kernel class (b) for C = 128 (when block_ws is off) and C = 256: the whole Block1D FFN half in ONE
+// persistent tcgen05 kernel with the hidden activation kept on chip and the weights STREAMED through shared memory.
+// (C = 256, added after the clock64 timelines of the whole-block kernels: the two-GEMM form there moves 26 bytes per
+// element and its second GEMM runs at 90 % of HBM speed on the hidden tensor's round trip; here the tile's budget is one
+// 64 KB a tile, two 32 KB stages per weight ring, two staging boxes and ONE 256-column D2 accumulator.)
 //
 //   out = resid + ffn_gamma * ( W2 * gelu_erf( W1 * a + b1 ) + b2 )         (reference :592-596, :937-942)
 //
@@ -49,16 +52,18 @@ __device__ long long vv_fs_trace[32 * 16];
 constexpr int FS_GROUPS = VV_FS_GROUPS;
 constexpr int FS_E1_WARPS = 16;
 constexpr int FS_E2_WARPS = 4;
-constexpr int FS_THREADS = (4 + FS_E1_WARPS + FS_E2_WARPS) * 32;
+constexpr int FS_CTRL = 8;                         // control warps: weights, G1, G2, residual / store ring, a tiles (+ 3 idle: the
+constexpr int FS_THREADS = (FS_CTRL + FS_E1_WARPS + FS_E2_WARPS) * 32;   // warp count stays a multiple of 4)
 
 template <int C>
 struct FfnStreamCfg {
-  static_assert(C == 128, "ffn_stream_kernel is laid out for C = 128");
+  static_assert(C == 128 || C == 256, "ffn_stream_kernel is laid out for C = 128 / 256");
   static constexpr int HC = 64;                    // hidden units per chunk
   static constexpr int NCH = 4 * C / HC;           // chunks per tile
   static constexpr int KB = C / 64;                // 64-wide K blocks of the a tile / a W1 chunk
   static constexpr int NBOX = C / 32;              // residual / output boxes per tile
-  static constexpr int NA = 2, S1 = 4, S2 = 2, NY = 4, ND1 = 2;
+  static constexpr int NA = (C == 128) ? 2 : 1, S1 = (C == 128) ? 4 : 2, S2 = 2, NY = (C == 128) ? 4 : 2, ND1 = 2;
+  static constexpr int ND2 = (C == 128) ? 2 : 1;   // D2 accumulators of C columns at tensor-memory column 256
   static constexpr int WLAG = 2;                   // the producer issues W2 chunk g - WLAG after W1 chunk g
   static constexpr int A_BYTES = 128 * C * 2;      // KB blocks of [128 rows x 128 B]
   static constexpr int W1_BYTES = HC * C * 2;      // KB blocks of [64 rows x 128 B]
@@ -72,6 +77,7 @@ struct FfnStreamCfg {
   static constexpr int OFF_Y = OFF_H;              // H lives in tensor memory (no shared-memory copy)
   static constexpr int OFF_BAR = OFF_Y + NY * Y_BYTES;
   static constexpr int NBARS = 2 * NA + 2 * S1 + 2 * S2 + ND1 + 3 * FS_GROUPS + 4 + 2 * NY;
+  static_assert(256 + ND2 * C <= 512, "tensor memory columns");
   static constexpr int TOTAL = OFF_BAR + 512 + 1024;   // + alignment slack
   static_assert(NBARS * 8 + 8 <= 512, "barrier block");
   static_assert(TOTAL <= 232448, "exceeds the 227 KB dynamic shared memory limit");
@@ -88,7 +94,7 @@ ffn_stream_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
                   const __grid_constant__ CUtensorMap tmW2, const FfnFusedArgs p) {
   using L = FfnStreamCfg<C>;
   constexpr int NA = L::NA, S1 = L::S1, S2 = L::S2, NY = L::NY, NCH = L::NCH, KB = L::KB, NBOX = L::NBOX;
-  constexpr int ND1 = L::ND1;
+  constexpr int ND1 = L::ND1, ND2 = L::ND2;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = smem_align_1k(smem_raw);
   uint8_t* sA = smem + L::OFF_A;
@@ -118,7 +124,7 @@ ffn_stream_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   // The SM's warp arbiter favours higher warp ids; with the issuers in warps 0..3 they lost most issue slots to
   // the E1 warps of their scheduler and needed ~950 cycles per chunk for ~100 instructions (clock64 timeline).
   const int hw_warp = threadIdx.x >> 5;
-  const int warp = (hw_warp >= FS_E1_WARPS + FS_E2_WARPS) ? hw_warp - (FS_E1_WARPS + FS_E2_WARPS) : hw_warp + 4;
+  const int warp = (hw_warp >= FS_E1_WARPS + FS_E2_WARPS) ? hw_warp - (FS_E1_WARPS + FS_E2_WARPS) : hw_warp + FS_CTRL;
   const int lane = threadIdx.x & 31;
   const long long ntiles = (p.R + 127) / 128;
   const int my_tiles = (ntiles > blockIdx.x) ? (int)((ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x) : 0;
@@ -160,7 +166,7 @@ ffn_stream_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   pdl_wait();
 
   if (warp == 0) {
-    // ===== TMA producer: a tiles and weight chunks ===================================================
+    // ===== TMA producer: weight chunks (the a tiles have their own thread, role 4) ============================
     // W2 chunks trail W1 by WLAG chunks (GEMM 2 runs behind GEMM 1); the single in-order producer cannot
     // deadlock: every wait below depends only on loads issued earlier in this same order.
     if (elect_one()) {
@@ -170,19 +176,9 @@ ffn_stream_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         mbar_expect_tx(&w2_full[s2], L::W2_BYTES);
         tma_load_2d(sW2 + s2 * L::W2_BYTES, &tmW2, &w2_full[s2], (gp & (NCH - 1)) * L::HC, 0);
       };
-      auto load_a = [&](int it) {               // a tiles are requested one whole tile ahead of their first use
-        const int sa = it & (NA - 1);
-        mbar_wait(&a_empty[sa], (uint32_t)(((it / NA) & 1) ^ 1));
-        mbar_expect_tx(&a_full[sa], L::A_BYTES);
-#pragma unroll
-        for (int kb = 0; kb < KB; ++kb)
-          tma_load_2d(sA + sa * L::A_BYTES + kb * (128 * 128), &tmA, &a_full[sa], kb * 64, row0 + it * tile_step);
-      };
       int g = 0;
-      if (my_tiles > 0) load_a(0);
       for (int it = 0; it < my_tiles; ++it) {
         for (int j = 0; j < NCH; ++j, ++g) {
-          if (j == 1 && it + 1 < my_tiles) load_a(it + 1);
           const int s1 = g & (S1 - 1);
           mbar_wait(&w1_empty[s1], (uint32_t)(((g / S1) & 1) ^ 1));
           mbar_expect_tx(&w1_full[s1], L::W1_BYTES);
@@ -233,8 +229,8 @@ ffn_stream_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       const uint64_t dw0 = umma_smem_desc<128>(smem_u32(sW2));
       int g = 0;
       for (int it = 0; it < my_tiles; ++it) {
-        const int d2b = it & 1;
-        mbar_wait(&d2_empty[d2b], (uint32_t)(((it >> 1) & 1) ^ 1));
+        const int d2b = it % ND2;
+        mbar_wait(&d2_empty[d2b], (uint32_t)(((it / ND2) & 1) ^ 1));
         const uint32_t d = tmem_base + L::D2_COL0 + (uint32_t)(d2b * C);
         for (int j = 0; j < NCH; ++j, ++g) {
           const int hb = g & (FS_GROUPS - 1), s2 = g & (S2 - 1);
@@ -273,15 +269,29 @@ ffn_stream_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       }
       tma_store_wait_all<0>();
     }
-  } else if (warp < 4 + FS_E1_WARPS) {
+  } else if (warp == 4) {
+    // ===== a tiles: [128, C] bf16 in KB blocks, requested as soon as GEMM 1 has read the slot's previous tenant ===========
+    if (elect_one()) {
+      for (int it = 0; it < my_tiles; ++it) {
+        const int sa = it & (NA - 1);
+        mbar_wait(&a_empty[sa], (uint32_t)(((it / NA) & 1) ^ 1));
+        mbar_expect_tx(&a_full[sa], L::A_BYTES);
+#pragma unroll
+        for (int kb = 0; kb < KB; ++kb)
+          tma_load_2d(sA + sa * L::A_BYTES + kb * (128 * 128), &tmA, &a_full[sa], kb * 64, row0 + it * tile_step);
+      }
+    }
+  } else if (warp < FS_CTRL) {
+    // idle control warps (keep the warp count a multiple of 4)
+  } else if (warp < FS_CTRL + FS_E1_WARPS) {
     // ===== E1: D1 -> bias + GELU -> bf16 -> swizzled smem (A operand of GEMM 2) ============================
     // Two groups of 8 warps alternate chunks (group G owns H buffer G), so one group's TMEM-load / MUFU /
     // barrier latency overlaps the other's math; within a chunk a warp owns 32 rows x 32 columns.
     const int q = warp & 3;                   // TMEM lane quarter
     constexpr int WPG = FS_E1_WARPS / FS_GROUPS;          // warps per group: 8 (two column halves) or 4
     constexpr int NHF = 8 / WPG;                          // 32-column halves a warp walks per chunk: 1 or 2
-    const int grp = (warp - 4) / WPG;                     // chunks g = grp (mod FS_GROUPS)
-    const int ch0 = (WPG == 8) ? (((warp - 4) >> 2) & 1) : 0;
+    const int grp = (warp - FS_CTRL) / WPG;               // chunks g = grp (mod FS_GROUPS)
+    const int ch0 = (WPG == 8) ? (((warp - FS_CTRL) >> 2) & 1) : 0;
     const uint32_t haddr = tmem_base + ((uint32_t)(q * 32) << 16) + L::H_COL0 + (uint32_t)(grp * 32);
     const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16);
     for (int g = grp; g < total_g; g += FS_GROUPS) {
@@ -336,7 +346,7 @@ ffn_stream_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     const int r = q * 32 + lane;
     int k = 0;
     for (int it = 0; it < my_tiles; ++it) {
-      const int d2b = it & 1;
+      const int d2b = it % ND2;
       const long long m = (long long)row0 + (long long)it * tile_step + r;
       const bool valid = m < p.R;
       long long brow = 0;
@@ -344,7 +354,7 @@ ffn_stream_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         const long long b = m / p.rows_pb;
         brow = b * p.ob_rpb + p.ob_off + (m - b * p.rows_pb);
       }
-      mbar_wait(&d2_full[d2b], (uint32_t)((it >> 1) & 1));
+      mbar_wait(&d2_full[d2b], (uint32_t)((it / ND2) & 1));
       tc_fence_after();
 #pragma unroll 1
       for (int c = 0; c < NBOX; ++c, ++k) {

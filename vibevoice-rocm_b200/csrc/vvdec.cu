@@ -235,6 +235,7 @@ static int32_t init_core(const vv_config* cfg, vv_decoder* d) {
   if (const char* ev = getenv("VV_GEMM_BN64")) d->opt_bn64 = atoi(ev);
   if (const char* ev = getenv("VV_BLOCK_KERNEL")) d->opt_block_kernel = atoi(ev) != 0;
   if (const char* ev = getenv("VV_BLOCK_WS")) d->opt_block_ws = atoi(ev) != 0;
+  if (const char* ev = getenv("VV_FFN_STREAM256")) d->opt_ffn_stream256 = atoi(ev) != 0;
   d->hop = 1;
   for (int i = 0; i + 1 < cfg->n_stages; ++i) d->hop *= cfg->ratios[i];
   // causal receptive field in latent frames: sum of left taps / layer input rate
@@ -277,6 +278,7 @@ extern "C" int32_t vv_decoder_set_option(vv_decoder* d, const char* key, int64_t
   if (strcmp(key, "gemm_bn64_small") == 0 && value >= 0 && value <= 1) { d->opt_bn64_small = (int)value; return VV_OK; }
   if (strcmp(key, "block_kernel") == 0 && value >= 0 && value <= 1) { d->opt_block_kernel = (int)value; return VV_OK; }
   if (strcmp(key, "block_ws") == 0 && value >= 0 && value <= 1) { d->opt_block_ws = (int)value; return VV_OK; }
+  if (strcmp(key, "ffn_stream256") == 0 && value >= 0 && value <= 1) { d->opt_ffn_stream256 = (int)value; return VV_OK; }
   set_error("unknown option '%s' or value %lld out of range", key, (long long)value);
   return VV_ERR_INVALID_ARG;
 }
@@ -427,7 +429,7 @@ bool Packer::block(const std::string& p, int C, BlockW& bw) {
     dense(bw.lin1, to_bf16(w1h), b1h, 4 * C, C, 1);
   }
   dense(bw.lin2, to_bf16(*w2), *b2, C, 4 * C, 1);
-  if (C == 128) {                      // host copies for ffn_stream_kernel's by-value constants
+  if (C == 128 || C == 256) {          // host copies for ffn_stream_kernel's by-value constants
     bw.h_b1 = *b1;
     for (float& v : bw.h_b1) v *= 0.5f;
     bw.h_b2 = *b2;
@@ -454,7 +456,7 @@ bool Packer::block(const std::string& p, int C, BlockW& bw) {
       status = encode_map(&bw.tm_w1fs, bw.lin1f.w, 2, dims, strides, box);
     }
   }
-  if (status == VV_OK && C == 128) {   // ffn_stream_kernel reads linear1 in chunks of 64 hidden units
+  if (status == VV_OK && (C == 128 || C == 256)) {   // ffn_stream_kernel reads linear1 in chunks of 64 hidden units
     const uint64_t dims[2] = {(uint64_t)C, (uint64_t)(4 * C)};
     const uint64_t strides[1] = {(uint64_t)C * 2};
     const uint32_t box[2] = {64u, 64u};
@@ -816,7 +818,8 @@ int launch_ffn_fused_inst(vv_decoder* d, const CUtensorMap& tmA, const CUtensorM
 }
 
 bool ffn_fused_supported(const vv_decoder* d, int C) {
-  return (d->cfg.gemm_path == 0 || d->cfg.gemm_path == 4) && (C == 32 || C == 64 || C == 128);
+  return (d->cfg.gemm_path == 0 || d->cfg.gemm_path == 4) &&
+         (C == 32 || C == 64 || C == 128 || (C == 256 && d->opt_ffn_stream256 != 0));
 }
 
 struct PadOut { long long rpb = 0; int off = 1; };   // padded bf16 copy geometry; rpb 0 = rows_pb + off
@@ -844,18 +847,25 @@ int launch_ffn_fused(vv_decoder* d, int C, const BlockW& bw, const __nv_bfloat16
   d->launches++;
   if (C == 32) return launch_ffn_fused_inst<32>(d, tmA, tmR, tmO, bw, fa, s);
   if (C == 64) return launch_ffn_fused_inst<64>(d, tmA, tmR, tmO, bw, fa, s);
-  // C = 128: hidden on chip, weights streamed (ffn_stream.cuh); a is read in [128 rows x 64] K blocks
-  if (bw.h_b1.size() != 512 || bw.h_b2.size() != 128 || bw.h_fgamma.size() != 128) { set_error("ffn_stream: constants missing"); return VV_ERR_NOT_FINALIZED; }
-  memcpy(fa.b1c, bw.h_b1.data(), sizeof(fa.b1c));
-  memcpy(fa.b2c, bw.h_b2.data(), sizeof(fa.b2c));
-  memcpy(fa.gammac, bw.h_fgamma.data(), sizeof(fa.gammac));
-  rc = ensure_smem(ffn_stream_kernel<128>, (int)FfnStreamCfg<128>::TOTAL, d->cfg.device);
-  if (rc != VV_OK) return rc;
+  // C = 128 / 256: hidden on chip, weights streamed (ffn_stream.cuh); a is read in [128 rows x 64] K blocks
+  if (bw.h_b1.size() != (size_t)4 * C || bw.h_b2.size() != (size_t)C || bw.h_fgamma.size() != (size_t)C) { set_error("ffn_stream: constants missing"); return VV_ERR_NOT_FINALIZED; }
+  memcpy(fa.b1c, bw.h_b1.data(), sizeof(float) * 4 * C);
+  memcpy(fa.b2c, bw.h_b2.data(), sizeof(float) * C);
+  memcpy(fa.gammac, bw.h_fgamma.data(), sizeof(float) * C);
   const int num_sms = d->num_sms;
   const long long ntiles = (R + 127) / 128;
   const unsigned grid = (unsigned)std::min<long long>(ntiles, num_sms);
   if (R + 256LL * num_sms >= (1LL << 31)) { set_error("ffn_stream: %lld rows exceed the 31-bit row index", R); return VV_ERR_BAD_SHAPE; }
-  launch_k(ffn_stream_kernel<128>, dim3(grid), dim3(FS_THREADS), FfnStreamCfg<128>::TOTAL, s, tmA, tmR, tmO, bw.tm_w1s, bw.lin2.tm, fa);
+  if (C == 128) {
+    rc = ensure_smem(ffn_stream_kernel<128>, (int)FfnStreamCfg<128>::TOTAL, d->cfg.device);
+    if (rc != VV_OK) return rc;
+    launch_k(ffn_stream_kernel<128>, dim3(grid), dim3(FS_THREADS), FfnStreamCfg<128>::TOTAL, s, tmA, tmR, tmO, bw.tm_w1s, bw.lin2.tm, fa);
+  } else {
+    if (!bw.lin2.has_tm256) { set_error("ffn_stream: no 256-row map for linear2"); return VV_ERR_NOT_FINALIZED; }
+    rc = ensure_smem(ffn_stream_kernel<256>, (int)FfnStreamCfg<256>::TOTAL, d->cfg.device);
+    if (rc != VV_OK) return rc;
+    launch_k(ffn_stream_kernel<256>, dim3(grid), dim3(FS_THREADS), FfnStreamCfg<256>::TOTAL, s, tmA, tmR, tmO, bw.tm_w1s, bw.lin2.tm256, fa);
+  }
   VV_LAUNCH_OK();
   return VV_OK;
 }

@@ -47,7 +47,7 @@ struct BlockW {
   // lin2f = diag(ffn_gamma) * W2, gb2 = ffn_gamma * b2  (lin1f.bias = 0.5 * b1 as in lin1)
   DenseW lin1f, lin2f;
   float* gb2 = nullptr;
-  std::vector<float> h_b1, h_b2, h_fgamma;   // C == 128: 0.5 * b1, b2, ffn_gamma for ffn_stream_kernel's constant-bank arguments
+  std::vector<float> h_b1, h_b2, h_fgamma;   // C == 128 / 256: 0.5 * b1, b2, ffn_gamma for ffn_stream_kernel's constant-bank arguments
   std::vector<float> h_b1c, h_gb2c;   // host copies: block_tma_kernel takes 0.5 * b1 and gb2 as by-value (constant-bank) arguments
   long long state_off = 0;      // fp32 [6][C]
 };
@@ -81,6 +81,7 @@ struct vv_decoder {
   int opt_bn256_waves = 2;
   int opt_bn64 = 1;                 // N = 64 layers on the persistent kernel's 64-wide tile (0: one-tile-per-CTA kernel)
   int opt_bn64_small = 1;           // residual-epilogue GEMMs whose 128-wide tiles would occupy fewer than half the SMs use the 64-wide tile
+  int opt_ffn_stream256 = 1;        // FFN half at C = 256: 1 = ffn_stream_kernel<256> (hidden on chip), 0 = two GEMMs through HBM
   int opt_block_ws = 1;             // whole-Block1D kernel at C = 128: 1 = block_ws_kernel, 0 = mixer_kernel + ffn_stream_kernel
   int opt_block_kernel = 1;         // whole-Block1D kernel at C <= 64: 1 = block_tma_kernel (x tile staged by TMA), 0 = block_fused_kernel
   // optional per-launch timing (vv_decoder_set_profiling): CUDA events recorded on the decode stream

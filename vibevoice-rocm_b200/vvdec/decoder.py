@@ -251,7 +251,7 @@ class B200AcousticDecoder:
 
     def set_option(self, key: str, value: int) -> None:
         """vv_decoder_set_option: "gemm_bn256" (0 never / 1 auto / 2 always), "gemm_bn256_waves", "gemm_bn64",
-        "gemm_bn64_small", "block_kernel", "block_ws" (include/vvdec.h)."""
+        "gemm_bn64_small", "block_kernel", "block_ws", "ffn_stream256" (include/vvdec.h)."""
         _capi.check(self._lib.vv_decoder_set_option(self._h, key.encode(), int(value)), f"vv_decoder_set_option({key})")
 
     # -- helpers -----------------------------------------------------------------------------------
