@@ -255,6 +255,39 @@ def test_ffn_half_c256_hidden_on_chip(full_decoder, B, rows, mode):
     assert m["snr_db"] > 50 and m["rel_max"] < 5e-3, m
 
 
+@pytest.mark.parametrize("rows", [1, 128, 129, 700, 170 * 128 + 5])
+def test_ffn_half_c256_in_place(full_decoder, rows):
+    """ffn_stream_kernel<256> with out == resid (how the decode / encode passes call it for every block but a stage's
+    last): the SM never reads the residual; each finished staging box holds ffn_gamma * (acc + b2) and is ADDED to y in global
+    memory by a TMA reduction (cp.reduce.async.bulk.tensor ... add).  Against the oracle, and against the out-of-place form
+    of the same kernel (one fp32 rounding apart: y + round(gamma * v) instead of fma(gamma, v, y))."""
+    dec, w = full_decoder
+    Cc = FULL.stage_channels(3)
+    g = _rng(33000 + rows)
+    a = round_to_bf16(g.standard_normal((rows, Cc), dtype=np.float32))
+    resid = g.standard_normal((rows, Cc), dtype=np.float32)
+    p = "decoder.stages.3.0."
+    idx = np.arange(rows) if rows <= 4096 else np.unique(g.integers(0, rows, 1024))
+    f = O.ffn(a[None, idx], w[p + "ffn.linear1.weight"], w[p + "ffn.linear1.bias"], w[p + "ffn.linear2.weight"],
+              w[p + "ffn.linear2.bias"])[0]
+    ref = resid[idx] + f * w[p + "ffn_gamma"][None, :]
+    at = torch.from_numpy(a).cuda().to(torch.bfloat16)
+    y = torch.from_numpy(resid).cuda()                      # residual in, block output out
+    out2 = torch.full_like(y, float("nan"))
+    hid = torch.empty(16, dtype=torch.bfloat16, device="cuda")
+    rc = dec._lib.vv_kernel_ffn(dec._h, 3, 0, _ptr(at), _ptr(y), _ptr(out2), _ptr(hid), 1, rows, _stream())
+    _check(dec, rc, "vv_kernel_ffn")
+    rc = dec._lib.vv_kernel_ffn(dec._h, 3, 0, _ptr(at), _ptr(y), _ptr(y), _ptr(hid), 1, rows, _stream())
+    _check(dec, rc, "vv_kernel_ffn (in place)")
+    torch.cuda.synchronize()
+    o = y.cpu().numpy()
+    assert np.isfinite(o).all()
+    m = O.parity_metrics(o[idx], ref)
+    assert m["snr_db"] > 50 and m["rel_max"] < 5e-3, m
+    d = (y - out2).abs().max().item()
+    assert d <= 2e-6 * max(1.0, out2.abs().max().item()), d
+
+
 @pytest.mark.parametrize("stage,B,rows", [(0, 1, 7), (0, 2, 150), (1, 1, 20), (1, 3, 100), (2, 1, 70), (2, 1, 300),
                                           (3, 1, 130), (3, 2, 257), (3, 1, 1)])
 def test_ffn_half_wide_tile_forced(full_decoder, stage, B, rows):

@@ -25,6 +25,7 @@ def main():
     ap.add_argument("--frames", type=int, default=2048)
     ap.add_argument("--iters", type=int, default=5)
     ap.add_argument("--gemm-path", type=int, default=0)
+    ap.add_argument("--inplace", action="store_true", help="ffn: out == resid (C = 256: TMA reduce-add mode)")
     a = ap.parse_args()
     g = vvdec.Geometry()
     # only the stage under test needs real depth; keep the load fast
@@ -49,6 +50,8 @@ def main():
         res = torch.randn(rows, Cc, device="cuda")
         out = torch.empty_like(res)
         hid = torch.empty(rows, 4 * Cc, device="cuda", dtype=torch.bfloat16)
+        if a.inplace:
+            out = res
         call = lambda: lib.vv_kernel_ffn(h, a.stage, 0, P(ab), P(res), P(out), P(hid), 1, rows, st)
         moved = rows * Cc * 10
     elif a.kind == "block":

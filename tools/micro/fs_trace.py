@@ -10,13 +10,15 @@ dec = vvdec.B200AcousticDecoder(g, device=0)
 dec.load_state_dict(random_state_dict(g))
 lib, h = dec._lib, dec._h
 st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
-rows = 5760 * 800
+stage = int(sys.argv[1]) if len(sys.argv) > 1 else 4            # 4: C = 128 (set VV_BLOCK_WS irrelevant: vv_kernel_ffn), 3: C = 256
+Cc = g.stage_channels(stage)
+rows = 5760 * (102400 // Cc) if stage >= 4 else 5760 * 200
 P = lambda t: C.c_void_p(t.data_ptr())
-ab = torch.randn(rows, 128, device="cuda").to(torch.bfloat16)
-res = torch.randn(rows, 128, device="cuda"); out = torch.empty_like(res)
+ab = torch.randn(rows, Cc, device="cuda").to(torch.bfloat16)
+res = torch.randn(rows, Cc, device="cuda"); out = torch.empty_like(res)
 hid = torch.empty(16, device="cuda")
 for _ in range(3):
-    assert lib.vv_kernel_ffn(h, 4, 0, P(ab), P(res), P(out), P(hid), 1, rows, st) == 0
+    assert lib.vv_kernel_ffn(h, stage, 0, P(ab), P(res), P(out), P(hid), 1, rows, st) == 0
 torch.cuda.synchronize()
 buf = (C.c_longlong * 512)()
 raw = C.CDLL(os.environ["VVDEC_LIB"])

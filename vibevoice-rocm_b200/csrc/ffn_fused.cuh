@@ -34,6 +34,8 @@ struct FfnFusedArgs {
   const float* gamma;      // [C]
   const float* resid;      // [R, C] fp32
   float* out;              // [R, C] fp32 (may alias resid)
+  int inplace_add;         // ffn_stream_kernel only: out == resid and the kernel ADDS gamma * (acc + b2) to it with TMA
+                           // reductions (no residual is read by the SM; out_bf16 must be null)
   __nv_bfloat16* out_bf16; // optional padded bf16 copy: [batch, ob_rpb, C], row t of an item lands at row ob_off + t
   long long ob_rpb;        //   (decoder: ob_rpb = rows_pb + 1, ob_off = 1 = the upsampler halo row)
   int ob_off;

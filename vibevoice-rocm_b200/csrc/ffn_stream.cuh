@@ -251,21 +251,36 @@ ffn_stream_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     }
   } else if (warp == 3) {
     // ===== residual boxes in, finished boxes out (one thread owns the Y ring) =================================
+    // p.inplace_add (out == resid): nothing is loaded; a finished box holds gamma * (acc + b2) and is ADDED to the residual
+    // in global memory by a TMA reduction, y_full then means "the reduction has read the box: it is free".  Why: the
+    // chunk-level timeline of the first C = 256 build showed ~11 000 idle clocks per tile behind the single D2 accumulator,
+    // the chain store -> read wait -> residual reload (DRAM latency) -> E2 running once per pair of staging boxes.
     if (elect_one()) {
       const int total_k = my_tiles * NBOX;
-      auto load_box = [&](int k) {
-        const int sy = k & (NY - 1);
-        mbar_expect_tx(&y_full[sy], L::Y_BYTES);
-        tma_load_2d(sY + sy * L::Y_BYTES, &tmR, &y_full[sy], (k & (NBOX - 1)) * 32, row0 + (k / NBOX) * tile_step);
-      };
-      for (int k = 0; k < NY && k < total_k; ++k) load_box(k);
-      for (int k = 0; k < total_k; ++k) {
-        const int sy = k & (NY - 1);
-        mbar_wait(&y_ready[sy], (uint32_t)((k / NY) & 1));
-        tma_store_2d(&tmO, sY + sy * L::Y_BYTES, (k & (NBOX - 1)) * 32, row0 + (k / NBOX) * tile_step);
-        tma_store_commit();
-        tma_store_wait_read<0>();               // the store has read the slot: refill it
-        if (k + NY < total_k) load_box(k + NY);
+      if (p.inplace_add) {
+        for (int k = 0; k < total_k; ++k) {
+          const int sy = k & (NY - 1);
+          mbar_wait(&y_ready[sy], (uint32_t)((k / NY) & 1));
+          tma_reduce_add_2d(&tmO, sY + sy * L::Y_BYTES, (k & (NBOX - 1)) * 32, row0 + (k / NBOX) * tile_step);
+          tma_store_commit();
+          tma_store_wait_read<0>();
+          mbar_arrive(&y_full[sy]);
+        }
+      } else {
+        auto load_box = [&](int k) {
+          const int sy = k & (NY - 1);
+          mbar_expect_tx(&y_full[sy], L::Y_BYTES);
+          tma_load_2d(sY + sy * L::Y_BYTES, &tmR, &y_full[sy], (k & (NBOX - 1)) * 32, row0 + (k / NBOX) * tile_step);
+        };
+        for (int k = 0; k < NY && k < total_k; ++k) load_box(k);
+        for (int k = 0; k < total_k; ++k) {
+          const int sy = k & (NY - 1);
+          mbar_wait(&y_ready[sy], (uint32_t)((k / NY) & 1));
+          tma_store_2d(&tmO, sY + sy * L::Y_BYTES, (k & (NBOX - 1)) * 32, row0 + (k / NBOX) * tile_step);
+          tma_store_commit();
+          tma_store_wait_read<0>();               // the store has read the slot: refill it
+          if (k + NY < total_k) load_box(k + NY);
+        }
       }
       tma_store_wait_all<0>();
     }
@@ -361,7 +376,8 @@ ffn_stream_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         const int sy = k & (NY - 1);
         uint32_t v[32];
         tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + L::D2_COL0 + (uint32_t)(d2b * C + c * 32), v);
-        mbar_wait(&y_full[sy], (uint32_t)((k / NY) & 1));
+        // (in-place mode: wait for the reduction of the box's previous tenant; the first NY waits pass on fresh barriers)
+        mbar_wait(&y_full[sy], (uint32_t)(((k / NY) & 1) ^ (p.inplace_add ? 1 : 0)));
         tmem_ld_wait();
         uint8_t* rrow = sY + sy * L::Y_BYTES + r * 128;
         float x[32];
@@ -369,7 +385,7 @@ ffn_stream_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         for (int i = 0; i < 8; ++i) {
           const int col = c * 32 + i * 4;
           float4* cell = reinterpret_cast<float4*>(rrow + ((i ^ (r & 7)) * 16));
-          const float4 rv = *cell;
+          const float4 rv = p.inplace_add ? make_float4(0.f, 0.f, 0.f, 0.f) : *cell;
 #if VV_FS_CONST
           const float* bv = p.b2c + col;                  // constant bank, same arithmetic as before
           const float* gv = p.gammac + col;

@@ -830,6 +830,8 @@ int launch_ffn_fused(vv_decoder* d, int C, const BlockW& bw, const __nv_bfloat16
   fa.ob_rpb = po.rpb > 0 ? po.rpb : rows_pb + po.off; fa.ob_off = po.off;
   fa.R = R; fa.rows_pb = rows_pb; fa.b1 = bw.lin1.bias; fa.b2 = bw.lin2.bias; fa.gamma = bw.ffn_gamma;
   fa.resid = resid; fa.out = out; fa.out_bf16 = out_bf16;
+  // C = 256, out == resid and no bf16 copy: the kernel adds its result to the residual in place with TMA reductions
+  fa.inplace_add = (C == 256 && out == resid && out_bf16 == nullptr) ? 1 : 0;
   CUtensorMap tmA;
   const uint64_t dims[2] = {(uint64_t)C, (uint64_t)R};
   const uint64_t strides[1] = {(uint64_t)C * 2};
@@ -1192,7 +1194,12 @@ int run_pass(vv_decoder* d, const LatView& lat, int nb, int T, void* audio, int 
       d->mark(VV_K_MIXER, i, s);
       const bool feeds_up = (j == nblk - 1) && (i + 1 < S);
       if (ffn_fused_supported(d, C)) {
-        rc = launch_ffn_fused(d, C, bw, A, Y, X, feeds_up ? XB : nullptr, (long long)nb * rows_pb, rows_pb, s);
+        if (C == 256 && !feeds_up) {     // in place: y += gamma_f * ffn(a) by TMA reductions; y becomes the block output
+          rc = launch_ffn_fused(d, C, bw, A, Y, Y, nullptr, (long long)nb * rows_pb, rows_pb, s);
+          std::swap(X, Y);
+        } else {
+          rc = launch_ffn_fused(d, C, bw, A, Y, X, feeds_up ? XB : nullptr, (long long)nb * rows_pb, rows_pb, s);
+        }
         if (rc != VV_OK) return rc;
         d->mark(VV_K_FFN_FUSED, i, s);
         continue;

@@ -127,7 +127,12 @@ int enc_run_pass(vv_encoder* e, const void* audio, int audio_is_bf16, long long 
       if (rc != VV_OK) return rc;
       d->mark(VV_K_MIXER, i, s);
       if (ffn_fused_supported(d, C)) {
-        rc = launch_ffn_fused(d, C, bw, A, Y, X, last ? XB : nullptr, (long long)nb * rows_pb, rows_pb, s, po);
+        if (C == 256 && !last) {         // in place (see run_pass): y becomes the block output
+          rc = launch_ffn_fused(d, C, bw, A, Y, Y, nullptr, (long long)nb * rows_pb, rows_pb, s, po);
+          std::swap(X, Y);
+        } else {
+          rc = launch_ffn_fused(d, C, bw, A, Y, X, last ? XB : nullptr, (long long)nb * rows_pb, rows_pb, s, po);
+        }
         if (rc != VV_OK) return rc;
         d->mark(VV_K_FFN_FUSED, i, s);
         continue;
