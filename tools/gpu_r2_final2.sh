@@ -16,9 +16,10 @@ BARGS="--steps 1 --warmup 3 --no-cpu-baseline --no-streaming --no-encoder --no-l
 step z_bench_short 240 python bench.py $BARGS
 step z_ncu_launches 500 ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file $O/z_launches.csv python bench.py $BARGS
 for S in 4 5 6; do
-  step z_ncu_bt_s$S 300 ncu --set full --clock-control none --import-source on -k regex:block_ -c 1 -f -o $O/block_tma4_s$S python tools/kbench.py --kind block --stage $S --frames 5760 --iters 1
+  step z_ncu_bt_s$S 300 ncu --set full --clock-control none --import-source on -k regex:block_ -c 1 -f -o $O/block_r02c_s$S python tools/kbench.py --kind block --stage $S --frames 5760 --iters 1
 done
-for KS in "block 4" "block 5" "block 6" "ffn 4" "mixer 4"; do set -- $KS; python tools/kbench.py --kind $1 --stage $2 --frames 5760 --iters 20; done > $O/z_kbench.txt 2>&1
+for KS in "block 4" "block 5" "block 6" "ffn 3" "mixer 3"; do set -- $KS; python tools/kbench.py --kind $1 --stage $2 --frames 5760 --iters 20; done > $O/z_kbench.txt 2>&1
+python tools/kbench.py --kind ffn --stage 3 --frames 5760 --iters 20 --inplace >> $O/z_kbench.txt 2>&1
 python tools/sampler_step.py >> $O/z_kbench.txt 2>&1
 python tools/stream_step.py --streams 256 --steps 20 --profile >> $O/z_kbench.txt 2>&1
 cat $O/z_kbench.txt $O/steps.txt
