@@ -84,6 +84,24 @@ def test_sampler_matches_oracle_larger_batch_and_is_deterministic():
     assert ms["snr_db"] >= 60.0, ms
 
 
+@pytest.mark.parametrize("hidden,n", [(2048, 5), (3584, 3)])
+def test_sampler_wide_heads(hidden, n):
+    """Heads wider than the 1.5B model's 1536 (3584 = the 7B model's): K >= 2048 makes the GEMMs take their long-K (DEEP)
+    instantiations -- gemm_tc2_kernel<EPI_SWIGLU_BF16, true, 256> for [gate; up], the bias epilogue for adaLN / cond_proj --
+    and the down projection (K = 3 x hidden) its K-slice planes with more k-blocks per slice.  One layer, 4 steps."""
+    g = SamplerGeometry(hidden=hidden, layers=1)
+    w = make_sampler_weights(g, 300 + hidden)
+    smp = build(g, w, 4)
+    cond, neg = inputs(g, n, 40 + n)
+    noise = np.random.Generator(np.random.Philox(key=[9, hidden])).standard_normal((n, g.latent), dtype=np.float32)
+    ref = OracleSampler(w, g).sample(cond, neg, noise, cfg_scale=1.7, steps=4)
+    out = smp.sample_speech_tokens(torch.from_numpy(cond).cuda(), torch.from_numpy(neg).cuda(), cfg_scale=1.7,
+                                   noise=torch.from_numpy(noise).cuda())
+    m = parity_metrics(out.cpu().numpy(), ref)
+    print(hidden, m)
+    assert m["snr_db"] >= SAMPLE_SNR_MIN and m["rel_max"] <= SAMPLE_REL_MAX, m
+
+
 def test_sampler_errors_and_default_noise():
     import vvdec
     with pytest.raises(ValueError):

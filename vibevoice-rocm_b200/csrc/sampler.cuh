@@ -8,7 +8,7 @@
 //   x   = bf16(latent, both halves) x noisy_images_proj^T                     samp_dup_latent_kernel + GEMM (K = 64)
 //   per layer:  [x += gate * f of the previous layer;]  a = bf16( RMSNorm(x) w (1 + scale) + shift )   samp_norm_mod_kernel
 //               h = bf16( silu(g) * u ),  [g | u] = a x [gate_proj ; up_proj]^T   one GEMM (N = 2F, weights interleaved in
-//                   128-unit blocks) with the SwiGLU in its epilogue (EPI_SWIGLU_BF16); samp_swiglu_kernel is the unfused form
+//                   128-unit blocks) with the SwiGLU in its epilogue (EPI_SWIGLU_BF16, gemm_tc2.cuh)
 //               f  = h x down_proj^T               (GEMM, K = F, as K slices: partial-sum planes added by the next norm)
 //   final:      x += gate * f;  a = bf16( RMSNorm(x) (1 + scale_f) + shift_f );  v = a x linear^T (GEMM, N = 64)
 //   solver:     eps = v_u + s (v_c - v_u);  m0 = alpha_s x - sigma_s eps;  x' = A x + B m0 + D (m0 - m1)   samp_solver_kernel
@@ -132,26 +132,6 @@ __global__ void __launch_bounds__(SAMP_NORM_THREADS) samp_norm_mod_kernel(const 
       pk.y = *reinterpret_cast<uint32_t*>(&hi);
       reinterpret_cast<uint2*>(p.a + (long long)r * p.H)[i] = pk;
     }
-  }
-}
-
-// h[r][j] = bf16( silu(gu[r][j]) * gu[r][F + j] )      (FeedForwardNetwork.forward :117-124; gu = [gate | up])
-__global__ void samp_swiglu_kernel(const float* __restrict__ gu, __nv_bfloat16* __restrict__ h, int rows, int F) {
-  pdl_launch();
-  pdl_wait();
-  const int fv = F / 4;
-  const long long total = (long long)rows * fv;
-  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
-    const long long r = i / fv;
-    const int j = (int)(i - r * fv);
-    const float4 g = reinterpret_cast<const float4*>(gu + r * 2 * F)[j];
-    const float4 u = reinterpret_cast<const float4*>(gu + r * 2 * F + F)[j];
-    __nv_bfloat162 lo = __floats2bfloat162_rn(samp_silu(g.x) * u.x, samp_silu(g.y) * u.y);
-    __nv_bfloat162 hi = __floats2bfloat162_rn(samp_silu(g.z) * u.z, samp_silu(g.w) * u.w);
-    uint2 pk;
-    pk.x = *reinterpret_cast<uint32_t*>(&lo);
-    pk.y = *reinterpret_cast<uint32_t*>(&hi);
-    reinterpret_cast<uint2*>(h + r * F)[j] = pk;
   }
 }
 
