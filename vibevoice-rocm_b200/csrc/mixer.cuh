@@ -100,8 +100,18 @@ __device__ __forceinline__ void reduce7(float (&s)[7], float* xchg, int buf) {
 #ifndef VV_MIXER_PREFETCH
 #define VV_MIXER_PREFETCH 1
 #endif
+#ifndef VV_MIXER_PREFETCH_MAXLPR
+#define VV_MIXER_PREFETCH_MAXLPR 128   // groups wider than this do not keep a second 7-row batch in registers (measured on
+                                       // B200, 5760 frames: C = 2048 75 -> 57 us, C = 1024 with two resident CTAs 157 -> 138 us)
+#endif
+#ifndef VV_MIXER_MINBLOCKS256
+#define VV_MIXER_MINBLOCKS256 2        // resident CTAs per SM the compiler must allow for the 256-thread group (C = 1024)
+#endif
+#ifndef VV_MIXER_MINBLOCKS128
+#define VV_MIXER_MINBLOCKS128 3        // ... for the 128-thread group (C = 512): 326 -> 273 us per 5760 frames
+#endif
 template <int LPR>
-__global__ void __launch_bounds__((LPR <= 32) ? 128 : LPR, (LPR <= 32) ? VV_MIXER_MINBLOCKS : 1)
+__global__ void __launch_bounds__((LPR <= 32) ? 128 : LPR, (LPR <= 32) ? VV_MIXER_MINBLOCKS : (LPR == 256 ? VV_MIXER_MINBLOCKS256 : (LPR == 128 ? VV_MIXER_MINBLOCKS128 : 1)))
 mixer_kernel(const MixerArgs p) {
   pdl_launch();
   pdl_wait();
@@ -160,20 +170,19 @@ mixer_kernel(const MixerArgs p) {
       }
     }
   };
-#if VV_MIXER_PREFETCH
+  constexpr bool PREFETCH = VV_MIXER_PREFETCH && (LPR <= VV_MIXER_PREFETCH_MAXLPR);
   float4 xn[7];                                     // the NEXT batch is always in flight while this one is computed
-  load7(t_begin - 6, xn);
-#endif
+  if constexpr (PREFETCH) load7(t_begin - 6, xn);
   for (int g7 = 0; g7 < ngroups7; ++g7) {
     const int tbase = t_begin - 6 + g7 * 7;
     float4 xr[7];
-#if VV_MIXER_PREFETCH
+    if constexpr (PREFETCH) {
 #pragma unroll
-    for (int i = 0; i < 7; ++i) xr[i] = xn[i];
-    if (g7 + 1 < ngroups7) load7(tbase + 7, xn);
-#else
-    load7(tbase, xr);
-#endif
+      for (int i = 0; i < 7; ++i) xr[i] = xn[i];
+      if (g7 + 1 < ngroups7) load7(tbase + 7, xn);
+    } else {
+      load7(tbase, xr);
+    }
     // streaming: the new context is the last 6 rows of [old context, x]
     if (st_wr != nullptr) {
 #pragma unroll
