@@ -301,7 +301,7 @@ int32_t vv_pcm16_static(const void* wave, int32_t wave_dtype, int32_t B, int64_t
 typedef struct vv_sampler_config {
   int32_t hidden;        /* VibeVoiceDiffusionHeadConfig.hidden_size (1536 / 3584); multiple of 128, <= 4096      */
   int32_t layers;        /* head_layers (4)                                                                      */
-  int32_t ffn;           /* int(hidden_size * head_ffn_ratio) (4608 / 10752); multiple of 64                     */
+  int32_t ffn;           /* int(hidden_size * head_ffn_ratio) (4608 / 10752); multiple of 128                    */
   int32_t latent;        /* latent_size (64; the kernels take exactly 64)                                        */
   float   eps;           /* rms_norm_eps (1e-5)                                                                  */
   int32_t train_steps;   /* ddpm_num_steps (1000)                                                                */
