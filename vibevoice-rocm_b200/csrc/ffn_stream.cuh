@@ -11,11 +11,14 @@
 // W2 (128 KB each) do not fit in shared memory next to the tiles, so per 128-row tile the hidden dimension is
 // walked in NCH chunks of HC = 64 units and the weight chunks arrive through two TMA rings (they are L2-resident:
 // 256 KB per block):
-//   warp 0  TMA : a tile [128, C] bf16 (ring of NA); W1 chunk [64, C] (ring S1); W2 chunk [C, 64] (ring S2)
-//   warp 1  G1  : D1[128, 64] = a * W1_chunk^T                  (tcgen05.mma, 2 accumulators in TMEM)
-//   warp 2  G2  : D2[128, C] += H * W2_chunk^T                  (tcgen05.mma, 2 accumulators in TMEM)
-//   warp 3  TMA : residual boxes [128 rows, 32 fp32] in (ring NY), finished boxes out; the reload of a slot is
-//                 issued by the same thread right after its store has read the slot
+//   role 0  TMA : W1 chunk [64, C] (ring S1); W2 chunk [C, 64] (ring S2)
+//   role 1  G1  : D1[128, 64] = a * W1_chunk^T                  (tcgen05.mma, 2 accumulators in TMEM)
+//   role 2  G2  : D2[128, C] += H * W2_chunk^T                  (tcgen05.mma; 2 accumulators at C = 128, 1 at C = 256)
+//   role 3  TMA : residual boxes [128 rows, 32 fp32] in (ring NY), finished boxes out; the reload of a slot is
+//                 issued by the same thread right after its store has read the slot.  In-place mode (out == resid):
+//                 nothing is loaded, a finished box is ADDED to the residual in global memory by a TMA reduction
+//   role 4  TMA : a tile [128, C] bf16 (ring of NA; ONE slot at C = 256: its own thread, so that waiting for GEMM 1 to
+//                 release the slot cannot stall the weight rings)
 //   E1, 2 x 8 warps alternating chunks: tcgen05.ld D1 -> + b1 -> GELU -> bf16 pairs -> tcgen05.st H (TENSOR memory,
 //       2 buffers): GEMM 2 reads its A operand from TMEM, so H costs no shared memory, no swizzled stores and no
 //       generic->async proxy fence (clock64 timeline: the st.shared + fence + arrive tail was ~500 cycles per chunk)
